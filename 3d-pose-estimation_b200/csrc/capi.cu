@@ -1,0 +1,149 @@
+// C ABI orchestration: workspace carving and the forward call (pose_prep -> blend GEMM -> skinning).
+#include "common.cuh"
+
+namespace smplb {
+
+static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+struct Workspace {
+  float* Xhi;
+  float* Xlo;
+  float* A;
+  float* vposed;
+  float* joints;   // scratch J_transformed when the caller passes none (backward needs it)
+  float* bwd;      // backward scratch (see backward.cu)
+  size_t total;
+};
+
+size_t backward_scratch_bytes(int B);
+
+Workspace carve(void* base, int B, int flags) {
+  Workspace w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    char* p = base ? (char*)base + off : nullptr;
+    off += align_up(bytes);
+    return (float*)p;
+  };
+  const size_t b = (size_t)(B > 0 ? B : 0);
+  w.Xhi = take(b * KPAD * sizeof(float));
+  w.Xlo = take(b * KPAD * sizeof(float));
+  w.A = take(b * NJ * 12 * sizeof(float));
+  w.joints = take(b * NJ * 3 * sizeof(float));
+  w.vposed = (flags & SMPLB_F_NO_SKIN) ? nullptr : take(b * VPP * sizeof(float));
+  w.bwd = (flags & SMPLB_F_KEEP_VPOSED) ? take(backward_scratch_bytes(B)) : nullptr;
+  w.total = off;
+  return w;
+}
+
+}  // namespace smplb
+
+using namespace smplb;
+
+extern "C" size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags) {
+  (void)m;
+  return carve(nullptr, B, flags).total;
+}
+
+static int32_t check_forward(const smplb_model* m, const smplb_forward_io* io, void* ws, size_t ws_bytes,
+                             int32_t flags) {
+  if (!m || !io) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: null model or io");
+  if (io->B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_forward: negative batch");
+  if (io->B == 0) return SMPLB_OK;
+  if (!io->beta || !io->theta) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: beta/theta are required");
+  if (io->cam_pos && !io->cam_rot) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: cam_rot required with cam_pos");
+  if ((io->uv || io->px) && !io->cam_pos) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: uv/px need a camera");
+  if ((flags & SMPLB_F_NO_SKIN) && (io->verts || io->kp))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_forward: SMPLB_F_NO_SKIN excludes verts/kp outputs");
+  if (!ws) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace is required");
+  if (ws_bytes < smplb_workspace_bytes(m, io->B, flags))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace too small (see smplb_workspace_bytes)");
+  if (((uintptr_t)ws & 255) != 0) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace must be 256-byte aligned");
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* io, void* workspace,
+                                 size_t workspace_bytes, int32_t flags, void* stream) {
+  int32_t rc = check_forward(m, io, workspace, workspace_bytes, flags);
+  if (rc != SMPLB_OK || io->B == 0) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = io->B;
+  Workspace w = carve(workspace, B, flags);
+  const bool skin = !(flags & SMPLB_F_NO_SKIN) && (io->verts || io->kp || (flags & SMPLB_F_KEEP_VPOSED));
+
+  PrepParams p;
+  p.B = B;
+  p.beta = io->beta;
+  p.theta = io->theta;
+  p.Jbar = m->Jbar;
+  p.JS = m->JS;
+  p.Xhi = skin ? w.Xhi : nullptr;
+  p.Xlo = skin ? w.Xlo : nullptr;
+  p.joints = io->joints ? io->joints : w.joints;
+  p.Rs = io->Rs;
+  p.A = io->A ? io->A : w.A;
+  p.cam_pos = io->cam_pos;
+  p.cam_rot = io->cam_rot;
+  p.focal = io->focal;
+  p.uv = io->uv;
+  p.px = io->px;
+  p.cfg = io->cfg;
+  p.tree = m->tree;
+  rc = launch_pose_prep(p, st);
+  if (rc != SMPLB_OK) return rc;
+  if (!skin) return SMPLB_OK;
+
+  if (flags & SMPLB_F_BLEND_SIMT)
+    rc = launch_blend_simt(m, B, w.Xhi, w.Xlo, w.vposed, st);
+  else
+    rc = launch_blend_tc(m, B, w.Xhi, w.Xlo, w.vposed, st);
+  if (rc != SMPLB_OK) return rc;
+  if (io->verts || io->kp) rc = launch_skin(m, B, w.vposed, p.A, io->verts, io->kp, st);
+  return rc;
+}
+
+extern "C" int32_t smplb_forward_host(const smplb_model* m, const smplb_forward_io* h,
+                                      const smplb_forward_io* d, void* workspace, size_t workspace_bytes,
+                                      int32_t flags, void* stream) {
+  if (!h || !d) return fail(SMPLB_E_INVALID_ARG, "smplb_forward_host: null io");
+  if (h->B != d->B) return fail(SMPLB_E_BAD_SHAPE, "smplb_forward_host: host/device batch mismatch");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t B = (size_t)(h->B > 0 ? h->B : 0);
+  const int NK = m ? m->NK : 0;
+  auto h2d = [&](const float* dst, const float* src, size_t n) -> cudaError_t {
+    if (!src) return cudaSuccess;
+    if (!dst) return cudaErrorInvalidValue;
+    return cudaMemcpyAsync((void*)dst, src, n * sizeof(float), cudaMemcpyHostToDevice, st);
+  };
+  auto d2h = [&](float* dst, const float* src, size_t n) -> cudaError_t {
+    if (!dst) return cudaSuccess;
+    if (!src) return cudaErrorInvalidValue;
+    return cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToHost, st);
+  };
+  SMPLB_CUDA_CHECK(h2d(d->beta, h->beta, B * NB));
+  SMPLB_CUDA_CHECK(h2d(d->theta, h->theta, B * NJ * 3));
+  SMPLB_CUDA_CHECK(h2d(d->cam_pos, h->cam_pos, B * 3));
+  SMPLB_CUDA_CHECK(h2d(d->cam_rot, h->cam_rot, B * 3));
+  SMPLB_CUDA_CHECK(h2d(d->focal, h->focal, B));
+  smplb_forward_io io = *d;
+  // outputs the host did not ask for are not produced
+  if (!h->verts) io.verts = nullptr;
+  if (!h->kp) io.kp = nullptr;
+  if (!h->Rs) io.Rs = nullptr;
+  if (!h->uv) io.uv = nullptr;
+  if (!h->px) io.px = nullptr;
+  if (!h->cam_pos) { io.cam_pos = nullptr; io.cam_rot = nullptr; io.focal = nullptr; io.uv = nullptr; io.px = nullptr; }
+  if (!h->focal) io.focal = nullptr;
+  io.cfg = h->cfg;
+  int32_t rc = smplb_forward(m, &io, workspace, workspace_bytes, flags, stream);
+  if (rc != SMPLB_OK) return rc;
+  SMPLB_CUDA_CHECK(d2h(h->verts, io.verts, B * NV3));
+  SMPLB_CUDA_CHECK(d2h(h->joints, io.joints, B * NJ * 3));
+  SMPLB_CUDA_CHECK(d2h(h->kp, io.kp, B * NK * 3));
+  SMPLB_CUDA_CHECK(d2h(h->Rs, io.Rs, B * NJ * 9));
+  SMPLB_CUDA_CHECK(d2h(h->A, io.A, B * NJ * 12));
+  SMPLB_CUDA_CHECK(d2h(h->uv, io.uv, B * NJ * 2));
+  SMPLB_CUDA_CHECK(d2h(h->px, io.px, B * NJ * 2));
+  SMPLB_CUDA_CHECK(cudaStreamSynchronize(st));
+  return SMPLB_OK;
+}

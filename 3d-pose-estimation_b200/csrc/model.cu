@@ -1,0 +1,196 @@
+// Model handle: copies the SMPL constants (SMPL.__init__, deps/tf_smpl/batch_smpl.py:17-69) to the
+// device and builds the derived tables the kernels stream: TF32 hi/lo splits of the blend-shape
+// basis, the folded joint regression, compressed LBS weights, CSR keypoint regressor.
+#include <math.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace smplb {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+int32_t fail(int32_t code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+const char* last_error() { return g_err.c_str(); }
+
+template <typename T>
+static cudaError_t upload(T** dptr, const std::vector<T>& h) {
+  size_t bytes = h.size() * sizeof(T);
+  cudaError_t e = cudaMalloc((void**)dptr, bytes ? bytes : sizeof(T));
+  if (e != cudaSuccess) return e;
+  if (bytes) e = cudaMemcpy(*dptr, h.data(), bytes, cudaMemcpyHostToDevice);
+  return e;
+}
+
+}  // namespace smplb
+
+extern "C" const char* smplb_last_error(void) { return smplb::last_error(); }
+extern "C" const char* smplb_version(void) { return "smplb200 0.1 (sm_100a)"; }
+
+extern "C" int32_t smplb_model_nk(const smplb_model* m) { return m ? m->NK : SMPLB_E_INVALID_ARG; }
+
+extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const float* v_template,
+                                      const float* shapedirs, const float* posedirs,
+                                      const float* J_regressor, const float* weights,
+                                      const float* kp_regressor, int32_t NK,
+                                      const int32_t* parents) {
+  using namespace smplb;
+  if (!out || !v_template || !shapedirs || !posedirs || !J_regressor || !weights || !kp_regressor ||
+      !parents)
+    return fail(SMPLB_E_INVALID_ARG, "smplb_model_create: null argument");
+  if (NK < 1 || NK > NKMAX) return fail(SMPLB_E_BAD_SHAPE, "smplb_model_create: NK out of range");
+  *out = nullptr;
+
+  // ---- kinematic tree (kintree_table[0]; parent[i] < i as in batch_lbs.py:122-127) ----
+  Tree tree;
+  tree.max_depth = 0;
+  tree.parent[0] = 0;
+  tree.depth[0] = 0;
+  for (int i = 1; i < NJ; ++i) {
+    int p = parents[i];
+    if (p < 0 || p >= i) return fail(SMPLB_E_INVALID_ARG, "smplb_model_create: parents[i] must be in [0,i)");
+    tree.parent[i] = p;
+    tree.depth[i] = tree.depth[p] + 1;
+    if (tree.depth[i] > tree.max_depth) tree.max_depth = tree.depth[i];
+  }
+
+  // ---- compressed LBS weights (batch_smpl.py:57-60, :120-127) ----
+  std::vector<uint32_t> sidx(NV);
+  std::vector<float4> sw(NV);
+  for (int v = 0; v < NV; ++v) {
+    int n = 0;
+    uint32_t packed = 0;
+    float w4[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j = 0; j < NJ; ++j) {
+      float w = weights[(size_t)v * NJ + j];
+      if (w != 0.0f) {
+        if (n == 4)
+          return fail(SMPLB_E_UNSUPPORTED,
+                      "smplb_model_create: a vertex has more than 4 non-zero LBS weights");
+        packed |= (uint32_t)j << (8 * n);
+        w4[n] = w;
+        ++n;
+      }
+    }
+    sidx[v] = packed;
+    sw[v] = make_float4(w4[0], w4[1], w4[2], w4[3]);
+  }
+
+  // ---- blend-shape basis D = [shapedirs; posedirs], padded; TF32 hi/lo splits ----
+  std::vector<float> D32((size_t)KPAD * VPP, 0.f);
+  for (int k = 0; k < NB; ++k)
+    memcpy(&D32[(size_t)k * VPP], &shapedirs[(size_t)k * NV3], NV3 * sizeof(float));
+  for (int k = 0; k < NP; ++k)
+    memcpy(&D32[(size_t)(NB + k) * VPP], &posedirs[(size_t)k * NV3], NV3 * sizeof(float));
+  std::vector<float> DThi((size_t)VPP * KPAD, 0.f), DTlo((size_t)VPP * KPAD, 0.f);
+  std::vector<float> Dhi((size_t)KPAD * VPP, 0.f), Dlo((size_t)KPAD * VPP, 0.f);
+  for (int k = 0; k < KDIM; ++k)
+    for (int n = 0; n < NV3; ++n) {
+      float x = D32[(size_t)k * VPP + n];
+      float hi = tf32_rna_host(x);
+      float lo = tf32_rna_host(x - hi);
+      DThi[(size_t)n * KPAD + k] = hi;
+      DTlo[(size_t)n * KPAD + k] = lo;
+      Dhi[(size_t)k * VPP + n] = hi;
+      Dlo[(size_t)k * VPP + n] = lo;
+    }
+  std::vector<float> vt(VPP, 0.f);
+  memcpy(vt.data(), v_template, NV3 * sizeof(float));
+
+  // ---- folded joint regression (batch_smpl.py:91-101): J = J_reg^T (v_template + S beta) ----
+  std::vector<double> Jbar64(NJ * 3, 0.0), JS64(NJ * 3 * NB, 0.0);
+  for (int v = 0; v < NV; ++v)
+    for (int j = 0; j < NJ; ++j) {
+      double r = J_regressor[(size_t)v * NJ + j];
+      if (r == 0.0) continue;
+      for (int c = 0; c < 3; ++c) {
+        Jbar64[j * 3 + c] += r * (double)v_template[v * 3 + c];
+        for (int k = 0; k < NB; ++k)
+          JS64[(j * 3 + c) * NB + k] += r * (double)shapedirs[(size_t)k * NV3 + v * 3 + c];
+      }
+    }
+  std::vector<float> Jbar(NJ * 3), JS(NJ * 3 * NB);
+  for (size_t i = 0; i < Jbar.size(); ++i) Jbar[i] = (float)Jbar64[i];
+  for (size_t i = 0; i < JS.size(); ++i) JS[i] = (float)JS64[i];
+
+  // ---- keypoint regressor CSR by vertex (batch_smpl.py:63-69, :134-138) ----
+  std::vector<int> kptr(NV + 1, 0), kcol;
+  std::vector<float> kval;
+  for (int v = 0; v < NV; ++v) {
+    for (int k = 0; k < NK; ++k) {
+      float r = kp_regressor[(size_t)v * NK + k];
+      if (r != 0.0f) {
+        kcol.push_back(k);
+        kval.push_back(r);
+      }
+    }
+    kptr[v + 1] = (int)kcol.size();
+  }
+
+  int prev = 0;
+  cudaGetDevice(&prev);
+  SMPLB_CUDA_CHECK(cudaSetDevice(device));
+  smplb_model* m = new smplb_model();
+  memset(m, 0, sizeof(*m));
+  m->device = device;
+  m->NK = NK;
+  m->tree = tree;
+  m->kp_nnz = (int)kcol.size();
+  cudaError_t e = cudaSuccess;
+  auto chk = [&](cudaError_t x) {
+    if (e == cudaSuccess) e = x;
+  };
+  chk(upload(&m->v_template_pad, vt));
+  chk(upload(&m->D32, D32));
+  chk(upload(&m->DT_hi, DThi));
+  chk(upload(&m->DT_lo, DTlo));
+  chk(upload(&m->D_hi, Dhi));
+  chk(upload(&m->D_lo, Dlo));
+  chk(upload(&m->Jbar, Jbar));
+  chk(upload(&m->JS, JS));
+  chk(upload(&m->skin_idx, sidx));
+  chk(upload(&m->skin_w, sw));
+  chk(upload(&m->kp_ptr, kptr));
+  chk(upload(&m->kp_col, kcol));
+  chk(upload(&m->kp_val, kval));
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    smplb_model_destroy(m);
+    return fail(SMPLB_E_CUDA, std::string("smplb_model_create: ") + cudaGetErrorString(e));
+  }
+  *out = m;
+  return SMPLB_OK;
+}
+
+namespace smplb {
+void free_tmap_cache(smplb_model* m);
+}
+
+extern "C" int32_t smplb_model_destroy(smplb_model* m) {
+  if (!m) return SMPLB_OK;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaSetDevice(m->device);
+  cudaFree(m->v_template_pad);
+  cudaFree(m->D32);
+  cudaFree(m->DT_hi);
+  cudaFree(m->DT_lo);
+  cudaFree(m->D_hi);
+  cudaFree(m->D_lo);
+  cudaFree(m->Jbar);
+  cudaFree(m->JS);
+  cudaFree(m->skin_idx);
+  cudaFree(m->skin_w);
+  cudaFree(m->kp_ptr);
+  cudaFree(m->kp_col);
+  cudaFree(m->kp_val);
+  smplb::free_tmap_cache(m);
+  cudaSetDevice(prev);
+  delete m;
+  return SMPLB_OK;
+}

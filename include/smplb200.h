@@ -1,0 +1,194 @@
+/*
+ * smplb200 — C ABI of the B200-native (sm_100a) batched SMPL + projection hot path.
+ *
+ * The reference (blzq/3D-pose-estimation) reaches this path through plain Python call
+ * signatures inside a TF1 graph, not through an FFI.  Each entry point below
+ * names the reference interface it replaces (paths relative to the reference root).  The
+ * Python drop-ins (`tf_smpl.batch_smpl.SMPL`, `tf_perspective_projection.project.project`,
+ * …) bind these with ctypes; tensors are only carriers (raw device pointers).
+ *
+ * Conventions
+ *   - every function returns an int32 status: SMPLB_OK or a negative SMPLB_E_* code;
+ *     `smplb_last_error()` returns a thread-local message for the last failing call;
+ *   - all `const float*` / `float*` batch arguments are DEVICE pointers (fp32, contiguous)
+ *     unless the name ends in `_host`; model-constant arguments of smplb_model_create are
+ *     HOST pointers and are copied;
+ *   - launches are asynchronous on the given stream (a `cudaStream_t` passed as void*);
+ *     no hidden device synchronisation, no allocation on the hot calls; the caller owns the
+ *     workspace (`smplb_workspace_bytes`);
+ *   - a model handle is immutable after creation: concurrent calls from several host threads /
+ *     streams are legal when each call uses its own workspace.
+ */
+#ifndef SMPLB200_H_
+#define SMPLB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SMPLB_NV 6890      /* vertices            (batch_smpl.py:30)  */
+#define SMPLB_NV3 20670    /* 3*NV                                    */
+#define SMPLB_NJ 24        /* joints              (config.py:7)       */
+#define SMPLB_NB 10        /* betas               (batch_smpl.py:31)  */
+#define SMPLB_NP 207       /* pose-feature width  (batch_smpl.py:109) */
+#define SMPLB_K 217        /* NB + NP: blend-shape contraction length */
+#define SMPLB_KPAD 224     /* K padded to the MMA k-block             */
+#define SMPLB_VP_PITCH 20736 /* row pitch (floats) of the internal v_posed buffer: 81*256 */
+
+enum {
+  SMPLB_OK = 0,
+  SMPLB_E_INVALID_ARG = -1,
+  SMPLB_E_BAD_SHAPE = -2,
+  SMPLB_E_CUDA = -3,
+  SMPLB_E_NOT_FINITE = -4,
+  SMPLB_E_UNSUPPORTED = -5
+};
+
+/* flags for smplb_forward / smplb_workspace_bytes */
+enum {
+  SMPLB_F_BLEND_SIMT = 1 << 0,   /* blend-shape contraction on CUDA cores (fp32 FFMA) instead of
+                                    the tcgen05 3xTF32 kernel — verification / bring-up path   */
+  SMPLB_F_KEEP_VPOSED = 1 << 1,  /* keep v_posed in the workspace for smplb_backward           */
+  SMPLB_F_NO_SKIN = 1 << 2       /* get_skin=False and no keypoints wanted: joints-only path   */
+};
+
+typedef struct smplb_model smplb_model;
+
+/* Camera / image constants of the loss block: deps/pose_3d/config.py:9-12, pose_model_3d.py:41-42 */
+typedef struct {
+  float img_w;       /* 320 */
+  float img_h;       /* 240 */
+  float ss;          /* 0.024 sensor size */
+  float focal_const; /* 0.05; used when the focal pointer is NULL (pose_model_3d.py:209-210) */
+} smplb_camcfg;
+
+/* I/O of one forward call.  Replaces SMPL.__call__ (deps/tf_smpl/batch_smpl.py:71-143) and,
+ * when cam_pos != NULL, the projection of the 24 posed joints + pixel rescale
+ * (deps/tf_perspective_projection/project.py:7-48, deps/pose_3d/pose_model_3d.py:202-231). */
+typedef struct {
+  int32_t B;
+  const float* beta;   /* [B,10]                                                       */
+  const float* theta;  /* [B,72] axis-angle, global rotation first                      */
+  float* verts;        /* [B,6890,3]   nullable                                         */
+  float* joints;       /* [B,24,3]     J_transformed (batch_smpl.py:118), nullable      */
+  float* kp;           /* [B,NK,3]     cocoplus/lsp keypoints (batch_smpl.py:134-138)   */
+  float* Rs;           /* [B,24,3,3]   nullable                                         */
+  float* A;            /* [B,24,3,4]   top three rows of the relative transforms
+                                       (batch_lbs.py:138-142), nullable                 */
+  const float* cam_pos;   /* [B,3] nullable: no projection                              */
+  const float* cam_rot;   /* [B,3] axis-angle                                           */
+  const float* focal;     /* [B]   nullable -> cfg.focal_const                          */
+  float* uv;              /* [B,24,2] project() output, nullable                        */
+  float* px;              /* [B,24,2] pixels, nullable                                  */
+  smplb_camcfg cfg;
+} smplb_forward_io;
+
+/* Loss configuration of the re-projection block (pose_model_3d.py:194-254, config.py:17-23). */
+typedef struct {
+  smplb_camcfg cam;
+  float reproj_scale;   /* 1.0*ss                       (config.py:22)  */
+  float reproj_cap;     /* 1/24, <=0 disables the cap   (pose_model_3d.py:237) */
+  float joint_scale;    /* 2.0                          (config.py:18)  */
+  float mesh_scale;     /* 1.0                          (config.py:17)  */
+} smplb_losscfg;
+
+const char* smplb_last_error(void);
+const char* smplb_version(void);
+
+/* SMPL.__init__ (deps/tf_smpl/batch_smpl.py:17-69).  All pointers HOST, reference layouts:
+ *   v_template [6890*3]; shapedirs [10*20670] (row k = blend shape k, column 3v+c, :34-37);
+ *   posedirs [207*20670] (:46-51); J_regressor [6890*24] dense (:40-43); weights [6890*24]
+ *   (:57-60); kp_regressor [6890*NK] dense (:63-69), NK = 19 or 14; parents [24]
+ *   (kintree_table[0] as int32, entry 0 ignored, :54).
+ * LBS weights must have at most 4 non-zeros per vertex (true of SMPL); otherwise
+ * SMPLB_E_UNSUPPORTED.  Builds the derived constants on `device`. */
+int32_t smplb_model_create(smplb_model** out, int32_t device,
+                           const float* v_template_host, const float* shapedirs_host,
+                           const float* posedirs_host, const float* J_regressor_host,
+                           const float* weights_host, const float* kp_regressor_host,
+                           int32_t NK, const int32_t* parents_host);
+int32_t smplb_model_destroy(smplb_model* m);
+int32_t smplb_model_nk(const smplb_model* m);
+
+/* Caller-owned scratch for one forward (+ backward when SMPLB_F_KEEP_VPOSED) call of batch B. */
+size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags);
+
+/* SMPL.__call__ (+ optional projection).  Kernels: pose_prep -> blend GEMM -> skinning. */
+int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* io, void* workspace,
+                      size_t workspace_bytes, int32_t flags, void* stream);
+
+/* Same call with HOST buffers (pinned or pageable): H2D of beta/theta/camera, the kernels, D2H of
+ * every non-NULL output, then a stream synchronise.  `io` holds HOST pointers here; `dev_io`
+ * holds caller-owned DEVICE staging buffers of the same shapes.  This is the end-to-end entry
+ * the bench times ("e2e"). */
+int32_t smplb_forward_host(const smplb_model* m, const smplb_forward_io* io_host,
+                           const smplb_forward_io* dev_io, void* workspace,
+                           size_t workspace_bytes, int32_t flags, void* stream);
+
+/* batch_rodrigues (deps/tf_smpl/batch_lbs.py:38-57) when variant==0;
+ * rodrigues_batch (deps/tf_perspective_projection/project.py:51-81) when variant==1. */
+int32_t smplb_rodrigues(int32_t N, const float* rvecs, float* R_out, int32_t variant, void* stream);
+
+/* batch_global_rigid_transformation (deps/tf_smpl/batch_lbs.py:84-144): Rs[N,24,3,3], Js[N,24,3]
+ * -> new_J[N,24,3], A[N,24,4,4]. */
+int32_t smplb_global_rigid(int32_t N, const float* Rs, const float* Js, const int32_t* parents_host,
+                           int32_t rotate_base, float* new_J, float* A44, void* stream);
+
+/* project (deps/tf_perspective_projection/project.py:7-48): pts[N,3] -> uv[N,2].
+ * cam_tiled==1: cams_* are per point ([N,3],[N,3],[N]) exactly like the reference call;
+ * cam_tiled==0: cams_* are per group of P consecutive points ([N/P,...]). */
+int32_t smplb_project(int32_t N, int32_t P, const float* pts, const float* cams_pos,
+                      const float* cams_angles, const float* focal_lens, int32_t cam_tiled,
+                      float* uv, void* stream);
+
+/* batch_orth_proj_idrot (deps/tf_smpl/projection.py:10-26): X[N,P,3], camera[N,3] -> [N,P,2]. */
+int32_t smplb_orth_proj(int32_t N, int32_t P, const float* X, const float* camera, float* out,
+                        void* stream);
+
+/* Re-projection loss block (deps/pose_3d/pose_model_3d.py:218-238): px_pred/px_gt [B,24,2] ->
+ * loss_out[0] = scale * mean((px_gt-px_pred)^2) (uncapped), loss_out[1] = capped value. */
+int32_t smplb_reproj_loss(int32_t B, const float* px_pred, const float* px_gt,
+                          const smplb_losscfg* cfg, float* loss_out, void* stream);
+
+/* Backward of smplb_forward (TF autodiff of batch_smpl.py:91-138, pose_model_3d.py:393-400;
+ * adjoint in SURVEY.md appendix A).  Upstream gradients may be NULL (treated as zero).
+ * g_px is the gradient wrt the pixel coordinates produced by the fused projection (camera
+ * treated as constant, pose_model_3d.py:218-221).  Requires the workspace of the matching
+ * forward call made with SMPLB_F_KEEP_VPOSED. */
+typedef struct {
+  int32_t B;
+  const float* beta;
+  const float* theta;
+  const float* g_verts;   /* [B,6890,3] nullable */
+  const float* g_joints;  /* [B,24,3]   nullable */
+  const float* g_kp;      /* [B,NK,3]   nullable */
+  const float* g_px;      /* [B,24,2]   nullable */
+  const float* cam_pos;   /* needed when g_px != NULL */
+  const float* cam_rot;
+  const float* focal;
+  smplb_camcfg cfg;
+  float* g_beta;          /* [B,10] */
+  float* g_theta;         /* [B,72] */
+} smplb_backward_io;
+
+int32_t smplb_backward(const smplb_model* m, const smplb_backward_io* io, void* workspace,
+                       size_t workspace_bytes, int32_t flags, void* stream);
+
+/* Backward of project() wrt points and camera (pose_model_3d.py:243-245 path):
+ * g_uv[N,2] -> g_pts[N,3] (nullable), g_cam_pos / g_cam_angles ([N,3] tiled or [N/P,3]), nullable */
+int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts, const float* cams_pos,
+                               const float* cams_angles, const float* focal_lens,
+                               int32_t cam_tiled, const float* g_uv, float* g_pts,
+                               float* g_cams_pos, float* g_cams_angles, void* stream);
+
+/* tf.train.AdamOptimizer update (pose_model_3d.py:393): eps outside the bias correction. */
+int32_t smplb_adam_step(int64_t n, float* x, const float* g, float* m, float* v, int32_t t,
+                        float lr, float beta1, float beta2, float eps, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMPLB200_H_ */
