@@ -1,4 +1,6 @@
 // C ABI orchestration: workspace carving and the forward call (pose_prep -> blend GEMM -> skinning).
+#include <vector>
+
 #include "common.cuh"
 
 namespace smplb {
@@ -36,9 +38,51 @@ Workspace carve(void* base, int B, int flags) {
   return w;
 }
 
+// ---- optional per-kernel timing (bench.py roofline): events recorded on the launching stream ----
+struct TimingState {
+  std::vector<cudaEvent_t> ev;   // 4 events per forward call: before prep, after prep, after blend, after skin
+  int max_calls = 0;
+  int ncalls = 0;
+};
+static thread_local TimingState g_timing;
+
+static inline void timing_mark(int slot, cudaStream_t st) {
+  TimingState& t = g_timing;
+  if (t.max_calls == 0 || t.ncalls >= t.max_calls) return;
+  cudaEventRecord(t.ev[(size_t)t.ncalls * 4 + slot], st);
+  if (slot == 3) ++t.ncalls;
+}
+
 }  // namespace smplb
 
 using namespace smplb;
+
+extern "C" int32_t smplb_timing_begin(int32_t max_calls) {
+  TimingState& t = g_timing;
+  for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
+  t.ev.clear();
+  t.ncalls = 0;
+  t.max_calls = max_calls > 0 ? max_calls : 0;
+  t.ev.resize((size_t)t.max_calls * 4);
+  for (auto& e : t.ev) SMPLB_CUDA_CHECK(cudaEventCreate(&e));
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_timing_end(float* ms_out, int32_t* ncalls_out) {
+  TimingState& t = g_timing;
+  if (!ncalls_out) return fail(SMPLB_E_INVALID_ARG, "smplb_timing_end: null ncalls_out");
+  *ncalls_out = t.ncalls;
+  for (int i = 0; i < t.ncalls && ms_out; ++i) {
+    SMPLB_CUDA_CHECK(cudaEventSynchronize(t.ev[(size_t)i * 4 + 3]));
+    for (int k = 0; k < 3; ++k)
+      SMPLB_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i * 3 + k], t.ev[(size_t)i * 4 + k], t.ev[(size_t)i * 4 + k + 1]));
+  }
+  for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
+  t.ev.clear();
+  t.max_calls = 0;
+  t.ncalls = 0;
+  return SMPLB_OK;
+}
 
 extern "C" size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags) {
   (void)m;
@@ -89,16 +133,24 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.px = io->px;
   p.cfg = io->cfg;
   p.tree = m->tree;
+  timing_mark(0, st);
   rc = launch_pose_prep(p, st);
   if (rc != SMPLB_OK) return rc;
-  if (!skin) return SMPLB_OK;
+  timing_mark(1, st);
+  if (!skin) {
+    timing_mark(2, st);
+    timing_mark(3, st);
+    return SMPLB_OK;
+  }
 
   if (flags & SMPLB_F_BLEND_SIMT)
     rc = launch_blend_simt(m, B, w.Xhi, w.Xlo, w.vposed, st);
   else
     rc = launch_blend_tc(m, B, w.Xhi, w.Xlo, w.vposed, st);
   if (rc != SMPLB_OK) return rc;
+  timing_mark(2, st);
   if (io->verts || io->kp) rc = launch_skin(m, B, w.vposed, p.A, io->verts, io->kp, st);
+  timing_mark(3, st);
   return rc;
 }
 

@@ -75,6 +75,8 @@ SYMBOLS = {
     'smplb_project_backward': (C.c_int32, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p]),
+    'smplb_timing_begin': (C.c_int32, [C.c_int32]),
+    'smplb_timing_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
     'smplb_adam_step': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_int32, C.c_float, C.c_float, C.c_float, C.c_float,
                                     C.c_void_p]),

@@ -95,7 +95,7 @@ class Model:
 
     def forward(self, beta, theta, cam_pos=None, cam_rot=None, focal=None, want_verts=True,
                 want_kp=True, want_Rs=True, want_A=False, want_uv=True, flags=0, cam_cfg=None,
-                out=None):
+                out=None, ws=None):
         """One smplb_forward call.  Returns a dict of CUDA tensors."""
         dev = self.device
         beta = _dev_f32(beta, dev)
@@ -134,7 +134,8 @@ class Model:
                        _ptr(A), _ptr(cam_pos) if has_cam else None,
                        _ptr(cam_rot) if has_cam else None, _ptr(focal) if has_cam else None,
                        _ptr(uv), _ptr(px), CamCfg(**cfg))
-        ws, need = self.workspace(B, flags)
+        if ws is None:
+            ws, need = self.workspace(B, flags)
         with torch.cuda.device(dev):
             check(_lib.lib().smplb_forward(self._h, C.byref(io), _ptr(ws), ws.numel(), flags,
                                            _stream(dev)))

@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py — SMPL forward + projection throughput on B200 (one JSON line on rank 0).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path (pose_prep -> blend GEMM -> skinning, with the fused
+projection of the 24 posed joints) over one batch of B synthetic samples per GPU, inputs resident
+in HBM.  Default workload: B = 65536 samples per GPU (BASELINE.json configs[3]/north_star target;
+weak scaling: every rank owns its own 65536-sample shard, no collective on the forward path).
+`e2e` times the same step through the C ABI with HOST buffers (smplb_forward_host: H2D of
+beta/theta/camera from pinned memory, kernels, D2H of verts/joints/keypoints/2D keypoints).
+`--impl reference` times the reference's CPU op sequence (oracle/ref_torch.py port of the TF graph,
+all host threads) on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, '3d-pose-estimation_b200')
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = 'smpl_fwd_proj_samples_per_s'
+UNIT = 'samples/s'
+# Algorithmic bytes per sample of the graded skinning pass (SURVEY.md §8d / BASELINE.md §3):
+# read v_posed 82680 + write verts 82680 + read A 1152 + write kp19 228  (px is written by pose_prep)
+SKIN_BYTES_PER_SAMPLE = 82680 + 82680 + 1152 + 228
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            d = json.load(f)
+        return float(d['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {'hw_slowdown': 0x8, 'sw_power_cap': 0x4, 'hw_thermal_slowdown': 0x40,
+                 'sw_thermal_slowdown': 0x20, 'hw_power_brake': 0x80}
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def summary(self):
+        if not self.sm:
+            return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons)}
+        return {'sm_mhz': float(np.median(self.sm)), 'sm_max_mhz': self.max_mhz,
+                'reasons': sorted(self.reasons), 'samples': len(self.sm)}
+
+
+def cpu_reference_rate(B_chunk, min_seconds, max_chunks, seed=1000):
+    """Reference CPU op sequence (tile(W) + [N,6890,4,4] matmul included, batch_smpl.py:120-132)
+    + projection + pixel rescale, fp32, all host threads.  Returns (samples/s, cores, n_samples, s)."""
+    from oracle import ref_torch as rt          # timed CPU baseline only
+    from smplb200 import synthetic as syn
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    dd = syn.make_synthetic_smpl(0)
+    m = rt.load_model(dd, dtype=torch.float32)
+    inp = syn.make_inputs(B_chunk, seed=seed)
+    t = {k: torch.from_numpy(v) for k, v in inp.items()}
+
+    def step():
+        with torch.no_grad():
+            o = rt.smpl_forward(m, t['beta'], t['theta'], tile_W=True)
+            rt.project_joints_px(o['J_transformed'], t['cam_pos'], t['cam_rot'], t['focal'])
+
+    step()  # warm-up
+    n, t0 = 0, time.perf_counter()
+    while True:
+        step()
+        n += 1
+        el = time.perf_counter() - t0
+        if (el >= min_seconds and n >= 2) or n >= max_chunks:
+            break
+    return n * B_chunk / el, cores, n * B_chunk, el, step
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    rate, cores, ns, el, step = cpu_reference_rate(args.ref_chunk, 0.0, 1)
+    for _ in range(max(args.warmup - 1, 0)):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    el = time.perf_counter() - t0
+    val = args.steps * args.ref_chunk / el
+    sample = '%d steps x %d samples of the B=%d/GPU workload, fp32, torch-CPU port of the TF op sequence' % (
+        args.steps, args.ref_chunk, args.batch)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * el / args.steps,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': 'SMPL forward + 24-joint perspective projection, B=%d per GPU '
+                               '(CPU arm: bounded sample, %d samples per step)' % (args.batch, args.ref_chunk),
+                   'model': 'synthetic SMPL-shaped (6890 verts, 24 joints, 10 betas), seed 0'},
+        'cpu_baseline': {'value': val, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': val, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--batch', type=int, default=65536, help='samples per GPU per step')
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--blend', default='tc', choices=['tc', 'simt'])
+    ap.add_argument('--e2e-steps', type=int, default=3)
+    ap.add_argument('--ref-chunk', type=int, default=256)
+    ap.add_argument('--cpu-seconds', type=float, default=12.0)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
+
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if args.impl == 'reference':
+        run_reference(args, rank)
+        return
+
+    assert torch.cuda.is_available(), 'bench.py needs a CUDA device (no CPU fallback)'
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+
+    import smplb200
+    from smplb200 import synthetic as syn, _lib
+    dev = torch.device('cuda', local_rank)
+    dd = syn.make_synthetic_smpl(0)
+    model = smplb200.Model(dd, device=local_rank)
+    B = args.batch
+    flags = _lib.F_BLEND_SIMT if args.blend == 'simt' else 0
+    inp = syn.make_inputs(B, seed=1000 + rank)
+    d = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
+    out = {}
+
+    def step():
+        model.forward(d['beta'], d['theta'], d['cam_pos'], d['cam_rot'], d['focal'], flags=flags, out=out)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    L = _lib.lib()
+    L.smplb_timing_begin(args.steps)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    kms = (C.c_float * (3 * args.steps))()
+    ncalls = C.c_int32(0)
+    L.smplb_timing_end(kms, C.byref(ncalls))
+    kt = np.array(list(kms), dtype=np.float64).reshape(-1, 3)[:ncalls.value]
+
+    # ---- e2e: host buffers through smplb_forward_host --------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        NK = model.NK
+        hb = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
+        ho = {'verts': torch.empty((B, 6890, 3), dtype=torch.float32).pin_memory(),
+              'joints': torch.empty((B, 24, 3), dtype=torch.float32).pin_memory(),
+              'kp': torch.empty((B, NK, 3), dtype=torch.float32).pin_memory(),
+              'px': torch.empty((B, 24, 2), dtype=torch.float32).pin_memory()}
+        CamCfg, FIO = _lib.CamCfg, _lib.ForwardIO
+        cfg = CamCfg(320.0, 240.0, 0.024, 0.05)
+        hio = FIO(B, hb['beta'].data_ptr(), hb['theta'].data_ptr(), ho['verts'].data_ptr(),
+                  ho['joints'].data_ptr(), ho['kp'].data_ptr(), None, None, hb['cam_pos'].data_ptr(),
+                  hb['cam_rot'].data_ptr(), hb['focal'].data_ptr(), None, ho['px'].data_ptr(), cfg)
+        dio = FIO(B, d['beta'].data_ptr(), d['theta'].data_ptr(), out['verts'].data_ptr(),
+                  out['joints'].data_ptr(), out['kp'].data_ptr(), None, None, d['cam_pos'].data_ptr(),
+                  d['cam_rot'].data_ptr(), d['focal'].data_ptr(), None, out['px'].data_ptr(), cfg)
+        ws, need = model.workspace(B, flags)
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+        def e2e_step():
+            _lib.check(L.smplb_forward_host(model._h, C.byref(hio), C.byref(dio), C.c_void_p(ws.data_ptr()),
+                                            ws.numel(), flags, st))
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            e2e_step()          # synchronises its stream before returning
+        barrier()
+        el = time.perf_counter() - t0
+        h2d = sum(hb[k].numel() * 4 for k in hb)
+        d2h = sum(ho[k].numel() * 4 for k in ho)
+        e2e = (el, h2d, d2h)
+    sampler.stop_flag = True
+    sampler.join()
+
+    t_all = torch.tensor([ms, e2e[0] if e2e else 0.0], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
+    ms_max, e2e_max = float(t_all[0]), float(t_all[1])
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        skin_ms = float(kt[:, 2].mean()) if len(kt) else float('nan')
+        achieved = SKIN_BYTES_PER_SAMPLE * B / (skin_ms * 1e-3) / 1e9
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, 'profiles', 'skin_traffic.json')) as f:
+                tj = json.load(f)
+            if int(tj.get('batch', -1)) == B:
+                traffic = tj.get('dram_bytes_per_launch')
+        except Exception:
+            pass
+        line = {
+            'metric': METRIC, 'value': world * B * args.steps / (ms_max * 1e-3), 'unit': UNIT,
+            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+            'ms_per_step': ms_max / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {
+                'workload': 'SMPL forward + 24-joint perspective projection, B=%d samples per GPU per step '
+                            '(BASELINE configs[3] shard size; global batch %d)' % (B, B * world),
+                'model': 'synthetic SMPL-shaped (6890 verts, 24 joints, 10 betas, <=4 LBS weights/vertex), seed 0',
+                'outputs': 'verts[B,6890,3], J_transformed[B,24,3], keypoints[B,19,3], Rs, uv, px[B,24,2]',
+                'blend_gemm': '3xTF32 tcgen05' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
+                'sharding': 'batch shards, one rank per GPU, no forward collective',
+                'l2': 'working set %.2f GB per step exceeds the 126 MB L2 (no flush needed)' % (
+                    B * (82944 + 82680) / 1e9),
+            },
+            'clocks': sampler.summary(),
+            'gpu_launches': 3 * args.steps,
+            'kernel_ms': {'pose_prep': float(kt[:, 0].mean()), 'blend_gemm': float(kt[:, 1].mean()),
+                          'skinning': skin_ms} if len(kt) else None,
+            'roofline': {'bound': 'hbm', 'kernel': 'skin_kernel (LBS + keypoint regression)',
+                         'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                         'traffic': traffic, 'peak_source': peak_src,
+                         'algorithmic_bytes_per_launch': SKIN_BYTES_PER_SAMPLE * B},
+        }
+        if e2e:
+            line['e2e'] = {'value': world * B * args.e2e_steps / e2e_max, 'unit': UNIT,
+                           'h2d_bytes_per_step': e2e[1], 'd2h_bytes_per_step': e2e[2],
+                           'steps': args.e2e_steps, 'note': 'smplb_forward_host, pinned host buffers, PCIe-bound'}
+        if not args.no_cpu_baseline:
+            rate, cores, ns, el, _ = cpu_reference_rate(args.ref_chunk, args.cpu_seconds, 1000)
+            line['cpu_baseline'] = {
+                'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                'sample': '%d samples (%d-sample chunks, %.1f s) of the same workload; torch-CPU fp32 port of '
+                          'the reference TF op sequence incl. tile(W)' % (ns, args.ref_chunk, el)}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -188,6 +188,12 @@ int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts, const flo
 int32_t smplb_adam_step(int64_t n, float* x, const float* g, float* m, float* v, int32_t t,
                         float lr, float beta1, float beta2, float eps, void* stream);
 
+/* Measurement aid (no reference counterpart): while enabled, every smplb_forward on this host thread
+ * records CUDA events on its stream around pose_prep / blend GEMM / skinning.  smplb_timing_end
+ * synchronises those events and writes ms_out[call][3] = {prep, blend, skin} milliseconds. */
+int32_t smplb_timing_begin(int32_t max_calls);
+int32_t smplb_timing_end(float* ms_out_host, int32_t* ncalls_out_host);
+
 #ifdef __cplusplus
 }
 #endif
