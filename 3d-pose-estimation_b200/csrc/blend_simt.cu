@@ -7,8 +7,7 @@ namespace smplb {
 
 constexpr int BS_TM = 64, BS_TN = 64, BS_TK = 32;
 
-__global__ void __launch_bounds__(256) blend_simt_kernel(int B, const float* __restrict__ Xhi,
-                                                         const float* __restrict__ Xlo,
+__global__ void __launch_bounds__(256) blend_simt_kernel(int B, const float* __restrict__ Ximg,
                                                          const float* __restrict__ D32,
                                                          const float* __restrict__ vt,
                                                          float* __restrict__ vposed) {
@@ -27,7 +26,7 @@ __global__ void __launch_bounds__(256) blend_simt_kernel(int B, const float* __r
       const int r = i / BS_TK, k = i % BS_TK;
       const int b = b0 + r;
       float v = 0.f;
-      if (b < B) v = Xhi[(size_t)b * KPAD + k0 + k] + Xlo[(size_t)b * KPAD + k0 + k];
+      if (b < B) v = Ximg[ximg_off(b, k0 + k, 0)] + Ximg[ximg_off(b, k0 + k, 1)];
       Xs[k][r] = v;
     }
     for (int i = threadIdx.x; i < BS_TK * BS_TN; i += 256) {
@@ -59,11 +58,10 @@ __global__ void __launch_bounds__(256) blend_simt_kernel(int B, const float* __r
   }
 }
 
-int32_t launch_blend_simt(const smplb_model* m, int B, const float* Xhi, const float* Xlo, float* vposed,
-                          cudaStream_t st) {
+int32_t launch_blend_simt(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
   dim3 grid(VPP / BS_TN, (B + BS_TM - 1) / BS_TM);
-  blend_simt_kernel<<<grid, 256, 0, st>>>(B, Xhi, Xlo, m->D32, m->v_template_pad, vposed);
+  blend_simt_kernel<<<grid, 256, 0, st>>>(B, Ximg, m->D32, m->v_template_pad, vposed);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

@@ -8,8 +8,7 @@ namespace smplb {
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 struct Workspace {
-  float* Xhi;
-  float* Xlo;
+  float* Ximg;
   float* A;
   float* vposed;
   float* joints;   // scratch J_transformed when the caller passes none (backward needs it)
@@ -28,8 +27,7 @@ Workspace carve(void* base, int B, int flags) {
     return (float*)p;
   };
   const size_t b = (size_t)(B > 0 ? B : 0);
-  w.Xhi = take(b * KPAD * sizeof(float));
-  w.Xlo = take(b * KPAD * sizeof(float));
+  w.Ximg = take(((b + BL_BM - 1) / BL_BM) * BL_XTILE * sizeof(float));
   w.A = take(b * NJ * 12 * sizeof(float));
   w.joints = take(b * NJ * 3 * sizeof(float));
   w.vposed = (flags & SMPLB_F_NO_SKIN) ? nullptr : take(b * VPP * sizeof(float));
@@ -121,8 +119,7 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.theta = io->theta;
   p.Jbar = m->Jbar;
   p.JS = m->JS;
-  p.Xhi = skin ? w.Xhi : nullptr;
-  p.Xlo = skin ? w.Xlo : nullptr;
+  p.Ximg = skin ? w.Ximg : nullptr;
   p.joints = io->joints ? io->joints : w.joints;
   p.Rs = io->Rs;
   p.A = io->A ? io->A : w.A;
@@ -144,9 +141,9 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   }
 
   if (flags & SMPLB_F_BLEND_SIMT)
-    rc = launch_blend_simt(m, B, w.Xhi, w.Xlo, w.vposed, st);
+    rc = launch_blend_simt(m, B, w.Ximg, w.vposed, st);
   else
-    rc = launch_blend_tc(m, B, w.Xhi, w.Xlo, w.vposed, st);
+    rc = launch_blend_tc(m, B, w.Ximg, w.vposed, st);
   if (rc != SMPLB_OK) return rc;
   timing_mark(2, st);
   if (io->verts || io->kp) rc = launch_skin(m, B, w.vposed, p.A, io->verts, io->kp, st);

@@ -17,6 +17,19 @@
 #define VPP SMPLB_VP_PITCH      // v_posed row pitch in floats (81 * 256)
 #define NKMAX 32                // keypoint-regressor columns supported (cocoplus 19 / lsp 14)
 
+// ---- operand images of the blend-shape GEMM (blend_tc.cu) -------------------------------------
+// Both operands are kept in global memory in exactly the byte order the tcgen05 MMA reads them from
+// shared memory (K-major, no swizzle: 16-byte K-chunks, rows contiguous inside a chunk), so that one
+// 1-D bulk copy moves one pipeline stage.  X (samples) : [m_tile][k_block][hi|lo][chunk][row 0..127][4]
+//                                          D (columns) : [n_tile][k_block][hi|lo][chunk][row 0..255][4]
+#define BL_BM 128               // samples per M tile
+#define BL_BN 256               // v_posed columns per N tile (VPP = 81 * 256)
+#define BL_KB 32                // K elements per pipeline stage (k-block) = 8 chunks of 4
+#define BL_NKB (KPAD / BL_KB)   // 7 k-blocks
+#define BL_NT (VPP / BL_BN)     // 81 N tiles
+#define BL_XTILE (BL_NKB * 2 * (BL_KB / 4) * BL_BM * 4)   // floats per X m-tile image (57344)
+#define BL_DTILE (BL_NKB * 2 * (BL_KB / 4) * BL_BN * 4)   // floats per D n-tile image (114688)
+
 namespace smplb {
 
 void set_error(const std::string& msg);
@@ -47,10 +60,7 @@ struct smplb_model {
   float* v_template_pad;  // [VPP]   v_template flattened (3v+c), zero padded
   // blend-shape basis D = [shapedirs; posedirs] : K=217 rows, padded to KPAD x VPP
   float* D32;             // [KPAD][VPP] fp32 (SIMT verification path, backward)
-  float* DT_hi;           // [VPP][KPAD] TF32 high part, K contiguous (tcgen05 B operand, K-major)
-  float* DT_lo;           // [VPP][KPAD] TF32 low part
-  float* D_hi;            // [KPAD][VPP] TF32 high part, N contiguous (backward dX GEMM B operand)
-  float* D_lo;            // [KPAD][VPP]
+  float* Dimg;            // [BL_NT][BL_DTILE] TF32 hi/lo operand image of D (tcgen05 B operand)
   // folded joint regression: J = Jbar + JS * beta  (batch_smpl.py:91-101)
   float* Jbar;            // [24*3]
   float* JS;              // [24*3*10]
@@ -74,8 +84,7 @@ struct PrepParams {
   const float* theta;
   const float* Jbar;
   const float* JS;
-  float* Xhi;     // [B][KPAD] nullable
-  float* Xlo;     // [B][KPAD] nullable
+  float* Ximg;    // [ceil(B/128)][BL_XTILE] TF32 hi/lo operand image of [beta | pose feature], nullable
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
@@ -89,10 +98,19 @@ struct PrepParams {
 };
 
 int32_t launch_pose_prep(const PrepParams& p, cudaStream_t st);
-int32_t launch_blend_simt(const smplb_model* m, int B, const float* Xhi, const float* Xlo,
-                          float* vposed, cudaStream_t st);
-int32_t launch_blend_tc(const smplb_model* m, int B, const float* Xhi, const float* Xlo,
-                        float* vposed, cudaStream_t st);
+int32_t launch_blend_simt(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st);
+int32_t launch_blend_tc(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st);
+
+// float offset of element (row b, k) of the X operand image; hl = 0 (hi) / 1 (lo)
+__host__ __device__ inline size_t ximg_off(int b, int k, int hl) {
+  return (size_t)(b / BL_BM) * BL_XTILE +
+         (size_t)((((k / BL_KB) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (k & 3);
+}
+// float offset of element (column n, k) of the D operand image
+__host__ __device__ inline size_t dimg_off(int n, int k, int hl) {
+  return (size_t)(n / BL_BN) * BL_DTILE +
+         (size_t)((((k / BL_KB) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BN + (n % BL_BN)) * 4 + (k & 3);
+}
 int32_t launch_skin(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
                     float* kp, cudaStream_t st);
 

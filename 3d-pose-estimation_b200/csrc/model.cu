@@ -87,17 +87,13 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
     memcpy(&D32[(size_t)k * VPP], &shapedirs[(size_t)k * NV3], NV3 * sizeof(float));
   for (int k = 0; k < NP; ++k)
     memcpy(&D32[(size_t)(NB + k) * VPP], &posedirs[(size_t)k * NV3], NV3 * sizeof(float));
-  std::vector<float> DThi((size_t)VPP * KPAD, 0.f), DTlo((size_t)VPP * KPAD, 0.f);
-  std::vector<float> Dhi((size_t)KPAD * VPP, 0.f), Dlo((size_t)KPAD * VPP, 0.f);
+  std::vector<float> Dimg((size_t)BL_NT * BL_DTILE, 0.f);
   for (int k = 0; k < KDIM; ++k)
     for (int n = 0; n < NV3; ++n) {
-      float x = D32[(size_t)k * VPP + n];
-      float hi = tf32_rna_host(x);
-      float lo = tf32_rna_host(x - hi);
-      DThi[(size_t)n * KPAD + k] = hi;
-      DTlo[(size_t)n * KPAD + k] = lo;
-      Dhi[(size_t)k * VPP + n] = hi;
-      Dlo[(size_t)k * VPP + n] = lo;
+      const float x = D32[(size_t)k * VPP + n];
+      const float hi = tf32_rna_host(x);
+      Dimg[dimg_off(n, k, 0)] = hi;
+      Dimg[dimg_off(n, k, 1)] = tf32_rna_host(x - hi);
     }
   std::vector<float> vt(VPP, 0.f);
   memcpy(vt.data(), v_template, NV3 * sizeof(float));
@@ -147,10 +143,7 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   };
   chk(upload(&m->v_template_pad, vt));
   chk(upload(&m->D32, D32));
-  chk(upload(&m->DT_hi, DThi));
-  chk(upload(&m->DT_lo, DTlo));
-  chk(upload(&m->D_hi, Dhi));
-  chk(upload(&m->D_lo, Dlo));
+  chk(upload(&m->Dimg, Dimg));
   chk(upload(&m->Jbar, Jbar));
   chk(upload(&m->JS, JS));
   chk(upload(&m->skin_idx, sidx));
@@ -178,10 +171,7 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaSetDevice(m->device);
   cudaFree(m->v_template_pad);
   cudaFree(m->D32);
-  cudaFree(m->DT_hi);
-  cudaFree(m->DT_lo);
-  cudaFree(m->D_hi);
-  cudaFree(m->D_lo);
+  cudaFree(m->Dimg);
   cudaFree(m->Jbar);
   cudaFree(m->JS);
   cudaFree(m->skin_idx);

@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
   }
 
   // GEMM A-operand row: [beta(10) | vec(R_1..23 - I)(207) | 0(7)]
-  if (p.Xhi) {
+  if (p.Ximg) {
     float* x = xs[warp];
     if (lane < NB) x[lane] = beta[lane];
     if (lane < KPAD - KDIM) x[KDIM + lane] = 0.f;
@@ -51,14 +51,13 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       for (int e = 0; e < 9; ++e) f[e] = R[e] - ((e == 0 || e == 4 || e == 8) ? 1.0f : 0.0f);
     }
     __syncwarp();
-    float* xh = p.Xhi + (size_t)b * KPAD;
-    float* xl = p.Xlo + (size_t)b * KPAD;
 #pragma unroll
     for (int i = 0; i < KPAD / 32; ++i) {
-      const float v = x[lane + 32 * i];
+      const int k = lane + 32 * i;
+      const float v = x[k];
       const float hi = tf32_rna(v);
-      xh[lane + 32 * i] = hi;
-      xl[lane + 32 * i] = tf32_rna(v - hi);
+      p.Ximg[ximg_off(b, k, 0)] = hi;
+      p.Ximg[ximg_off(b, k, 1)] = tf32_rna(v - hi);
     }
   }
 
