@@ -10,7 +10,9 @@ static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a
 struct Workspace {
   float* Ximg;
   float* A;
+  float* Aimg;
   float* vposed;
+  float* verts;    // scratch verts when only keypoints are wanted (SMPLB_F_SCRATCH_VERTS)
   float* joints;   // scratch J_transformed when the caller passes none (backward needs it)
   float* bwd;      // backward scratch (see backward.cu)
   size_t total;
@@ -30,7 +32,10 @@ Workspace carve(void* base, int B, int flags) {
   w.Ximg = take(((b + BL_BM - 1) / BL_BM) * BL_XTILE * sizeof(float));
   w.A = take(b * NJ * 12 * sizeof(float));
   w.joints = take(b * NJ * 3 * sizeof(float));
-  w.vposed = (flags & SMPLB_F_NO_SKIN) ? nullptr : take(b * VPP * sizeof(float));
+  const bool skin = !(flags & SMPLB_F_NO_SKIN);
+  w.Aimg = skin ? take(((b + SK_S - 1) / SK_S) * SK_AGRP * sizeof(float)) : nullptr;
+  w.vposed = skin ? take(b * VPP * sizeof(float)) : nullptr;
+  w.verts = (skin && (flags & SMPLB_F_SCRATCH_VERTS)) ? take(b * NV3 * sizeof(float)) : nullptr;
   w.bwd = (flags & SMPLB_F_KEEP_VPOSED) ? take(backward_scratch_bytes(B)) : nullptr;
   w.total = off;
   return w;
@@ -38,7 +43,7 @@ Workspace carve(void* base, int B, int flags) {
 
 // ---- optional per-kernel timing (bench.py roofline): events recorded on the launching stream ----
 struct TimingState {
-  std::vector<cudaEvent_t> ev;   // 4 events per forward call: before prep, after prep, after blend, after skin
+  std::vector<cudaEvent_t> ev;   // 5 events per forward call: before prep, after prep, after blend, after skin, after keypoints
   int max_calls = 0;
   int ncalls = 0;
 };
@@ -47,8 +52,8 @@ static thread_local TimingState g_timing;
 static inline void timing_mark(int slot, cudaStream_t st) {
   TimingState& t = g_timing;
   if (t.max_calls == 0 || t.ncalls >= t.max_calls) return;
-  cudaEventRecord(t.ev[(size_t)t.ncalls * 4 + slot], st);
-  if (slot == 3) ++t.ncalls;
+  cudaEventRecord(t.ev[(size_t)t.ncalls * 5 + slot], st);
+  if (slot == 4) ++t.ncalls;
 }
 
 }  // namespace smplb
@@ -61,7 +66,7 @@ extern "C" int32_t smplb_timing_begin(int32_t max_calls) {
   t.ev.clear();
   t.ncalls = 0;
   t.max_calls = max_calls > 0 ? max_calls : 0;
-  t.ev.resize((size_t)t.max_calls * 4);
+  t.ev.resize((size_t)t.max_calls * 5);
   for (auto& e : t.ev) SMPLB_CUDA_CHECK(cudaEventCreate(&e));
   return SMPLB_OK;
 }
@@ -71,9 +76,9 @@ extern "C" int32_t smplb_timing_end(float* ms_out, int32_t* ncalls_out) {
   if (!ncalls_out) return fail(SMPLB_E_INVALID_ARG, "smplb_timing_end: null ncalls_out");
   *ncalls_out = t.ncalls;
   for (int i = 0; i < t.ncalls && ms_out; ++i) {
-    SMPLB_CUDA_CHECK(cudaEventSynchronize(t.ev[(size_t)i * 4 + 3]));
-    for (int k = 0; k < 3; ++k)
-      SMPLB_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i * 3 + k], t.ev[(size_t)i * 4 + k], t.ev[(size_t)i * 4 + k + 1]));
+    SMPLB_CUDA_CHECK(cudaEventSynchronize(t.ev[(size_t)i * 5 + 4]));
+    for (int k = 0; k < 4; ++k)
+      SMPLB_CUDA_CHECK(cudaEventElapsedTime(&ms_out[i * 4 + k], t.ev[(size_t)i * 5 + k], t.ev[(size_t)i * 5 + k + 1]));
   }
   for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
   t.ev.clear();
@@ -97,6 +102,8 @@ static int32_t check_forward(const smplb_model* m, const smplb_forward_io* io, v
   if ((io->uv || io->px) && !io->cam_pos) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: uv/px need a camera");
   if ((flags & SMPLB_F_NO_SKIN) && (io->verts || io->kp))
     return fail(SMPLB_E_INVALID_ARG, "smplb_forward: SMPLB_F_NO_SKIN excludes verts/kp outputs");
+  if (io->kp && !io->verts && !(flags & SMPLB_F_SCRATCH_VERTS))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_forward: keypoints without a verts buffer need SMPLB_F_SCRATCH_VERTS");
   if (!ws) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace is required");
   if (ws_bytes < smplb_workspace_bytes(m, io->B, flags))
     return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace too small (see smplb_workspace_bytes)");
@@ -123,6 +130,7 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.joints = io->joints ? io->joints : w.joints;
   p.Rs = io->Rs;
   p.A = io->A ? io->A : w.A;
+  p.Aimg = skin ? w.Aimg : nullptr;
   p.cam_pos = io->cam_pos;
   p.cam_rot = io->cam_rot;
   p.focal = io->focal;
@@ -137,6 +145,7 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   if (!skin) {
     timing_mark(2, st);
     timing_mark(3, st);
+    timing_mark(4, st);
     return SMPLB_OK;
   }
 
@@ -146,8 +155,17 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
     rc = launch_blend_tc(m, B, w.Ximg, w.vposed, st);
   if (rc != SMPLB_OK) return rc;
   timing_mark(2, st);
-  if (io->verts || io->kp) rc = launch_skin(m, B, w.vposed, p.A, io->verts, io->kp, st);
+  float* verts = io->verts ? io->verts : w.verts;
+  if (verts) {
+    if (flags & SMPLB_F_SKIN_SIMT)
+      rc = launch_skin_simt(m, B, w.vposed, p.A, verts, st);
+    else
+      rc = launch_skin_tc(m, B, w.vposed, w.Aimg, verts, st);
+    if (rc != SMPLB_OK) return rc;
+  }
   timing_mark(3, st);
+  if (io->kp) rc = launch_keypoints(m, B, verts, io->kp, st);
+  timing_mark(4, st);
   return rc;
 }
 

@@ -64,12 +64,15 @@ struct smplb_model {
   // folded joint regression: J = Jbar + JS * beta  (batch_smpl.py:91-101)
   float* Jbar;            // [24*3]
   float* JS;              // [24*3*10]
-  // compressed LBS weights (<= 4 non-zeros per vertex), sorted by joint index
+  // compressed LBS weights (<= 4 non-zeros per vertex), sorted by joint index (SIMT skinning path);
+  // has_compressed == 0 when some vertex has more than 4 non-zero weights (dense models: TC path only)
   uint32_t* skin_idx;     // [NV] 4 x u8 joint ids
   float4* skin_w;         // [NV]
-  // keypoint regressor, CSR by vertex (joint_regressor, batch_smpl.py:63-69)
-  int* kp_ptr;            // [NV+1]
-  int* kp_col;            // [nnz] keypoint id
+  int has_compressed;
+  float* Wimg;            // [SK_NVT][SK_WTILE] TF32 hi/lo operand image of the dense LBS weights
+  // keypoint regressor (joint_regressor, batch_smpl.py:63-69), CSR by keypoint, fixed summation order
+  int* kp_ptr;            // [NK+1]
+  int* kp_vtx;            // [nnz] vertex id
   float* kp_val;          // [nnz]
   int kp_nnz;
   // J_regressor CSR by joint (for d(J)/d(beta) in backward: JS is enough) — not needed
@@ -88,6 +91,7 @@ struct PrepParams {
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
+  float* Aimg;    // [ceil(B/20)][SK_AGRP] TF32 hi/lo operand image of A for the skinning GEMM, nullable
   const float* cam_pos;
   const float* cam_rot;
   const float* focal;
@@ -101,6 +105,29 @@ int32_t launch_pose_prep(const PrepParams& p, cudaStream_t st);
 int32_t launch_blend_simt(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st);
 int32_t launch_blend_tc(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st);
 
+// ---- internal v_posed layout ----------------------------------------------------------------------
+// v_posed is an internal buffer (blend GEMM -> skinning), so its column order is ours to choose: vertices
+// are grouped in tiles of 128 (= TMEM lanes of the skinning kernel) and stored SoA inside a tile, i.e.
+// column(v, c) = (v / 128) * 384 + c * 128 + v % 128.  54 tiles * 384 = 20736 = VPP; pad columns are 0.
+#define SK_VT 128                       // vertices per skinning tile
+#define SK_NVT ((NV + SK_VT - 1) / SK_VT)   // 54
+__host__ __device__ inline int vp_col(int v, int c) { return (v / SK_VT) * (3 * SK_VT) + c * SK_VT + (v % SK_VT); }
+
+// ---- operand images of the skinning GEMM (skin_tc.cu): T[v, (s,e)] = sum_j W[v,j] A[s][j][e] -------
+#define SK_S 20                         // samples per MMA group: N = 12 * 20 = 240
+#define SK_N (12 * SK_S)
+#define SK_KCH (NJ / 4)                 // 6 K-chunks (24 joints)
+#define SK_WTILE (2 * SK_KCH * SK_VT * 4)   // floats per W tile image  [hi|lo][chunk][128 rows][4]  (6144)
+#define SK_AGRP (2 * SK_KCH * SK_N * 4)     // floats per A group image [hi|lo][chunk][240 rows][4]  (11520)
+// element (sample b, joint j, component e = 3x4 row-major) of the A operand image
+__host__ __device__ inline size_t aimg_off(int b, int j, int e, int hl) {
+  return (size_t)(b / SK_S) * SK_AGRP + (size_t)(((hl * SK_KCH + j / 4) * SK_N + (b % SK_S) * 12 + e) * 4 + (j & 3));
+}
+// element (vertex v, joint j) of the W operand image
+__host__ __device__ inline size_t wimg_off(int v, int j, int hl) {
+  return (size_t)(v / SK_VT) * SK_WTILE + (size_t)(((hl * SK_KCH + j / 4) * SK_VT + (v % SK_VT)) * 4 + (j & 3));
+}
+
 // float offset of element (row b, k) of the X operand image; hl = 0 (hi) / 1 (lo)
 __host__ __device__ inline size_t ximg_off(int b, int k, int hl) {
   return (size_t)(b / BL_BM) * BL_XTILE +
@@ -111,8 +138,11 @@ __host__ __device__ inline size_t dimg_off(int n, int k, int hl) {
   return (size_t)(n / BL_BN) * BL_DTILE +
          (size_t)((((k / BL_KB) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BN + (n % BL_BN)) * 4 + (k & 3);
 }
-int32_t launch_skin(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
-                    float* kp, cudaStream_t st);
+int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
+                         cudaStream_t st);
+int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts,
+                       cudaStream_t st);
+int32_t launch_keypoints(const smplb_model* m, int B, const float* verts, float* kp, cudaStream_t st);
 
 // TF32 helpers --------------------------------------------------------------------------------
 __host__ __device__ inline float tf32_rna_host(float x) {

@@ -62,6 +62,15 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   // ---- compressed LBS weights (batch_smpl.py:57-60, :120-127) ----
   std::vector<uint32_t> sidx(NV);
   std::vector<float4> sw(NV);
+  int has_compressed = 1;
+  std::vector<float> Wimg((size_t)SK_NVT * SK_WTILE, 0.f);
+  for (int v = 0; v < NV; ++v)
+    for (int j = 0; j < NJ; ++j) {
+      const float x = weights[(size_t)v * NJ + j];
+      const float hi = tf32_rna_host(x);
+      Wimg[wimg_off(v, j, 0)] = hi;
+      Wimg[wimg_off(v, j, 1)] = tf32_rna_host(x - hi);
+    }
   for (int v = 0; v < NV; ++v) {
     int n = 0;
     uint32_t packed = 0;
@@ -69,9 +78,10 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
     for (int j = 0; j < NJ; ++j) {
       float w = weights[(size_t)v * NJ + j];
       if (w != 0.0f) {
-        if (n == 4)
-          return fail(SMPLB_E_UNSUPPORTED,
-                      "smplb_model_create: a vertex has more than 4 non-zero LBS weights");
+        if (n == 4) {
+          has_compressed = 0;
+          break;
+        }
         packed |= (uint32_t)j << (8 * n);
         w4[n] = w;
         ++n;
@@ -83,20 +93,24 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
 
   // ---- blend-shape basis D = [shapedirs; posedirs], padded; TF32 hi/lo splits ----
   std::vector<float> D32((size_t)KPAD * VPP, 0.f);
-  for (int k = 0; k < NB; ++k)
-    memcpy(&D32[(size_t)k * VPP], &shapedirs[(size_t)k * NV3], NV3 * sizeof(float));
-  for (int k = 0; k < NP; ++k)
-    memcpy(&D32[(size_t)(NB + k) * VPP], &posedirs[(size_t)k * NV3], NV3 * sizeof(float));
+  // columns in the internal v_posed order (vp_col): reference column 3v+c -> vp_col(v, c)
+  for (int v = 0; v < NV; ++v)
+    for (int c = 0; c < 3; ++c) {
+      const int col = vp_col(v, c);
+      for (int k = 0; k < NB; ++k) D32[(size_t)k * VPP + col] = shapedirs[(size_t)k * NV3 + 3 * v + c];
+      for (int k = 0; k < NP; ++k) D32[(size_t)(NB + k) * VPP + col] = posedirs[(size_t)k * NV3 + 3 * v + c];
+    }
   std::vector<float> Dimg((size_t)BL_NT * BL_DTILE, 0.f);
   for (int k = 0; k < KDIM; ++k)
-    for (int n = 0; n < NV3; ++n) {
+    for (int n = 0; n < VPP; ++n) {
       const float x = D32[(size_t)k * VPP + n];
       const float hi = tf32_rna_host(x);
       Dimg[dimg_off(n, k, 0)] = hi;
       Dimg[dimg_off(n, k, 1)] = tf32_rna_host(x - hi);
     }
   std::vector<float> vt(VPP, 0.f);
-  memcpy(vt.data(), v_template, NV3 * sizeof(float));
+  for (int v = 0; v < NV; ++v)
+    for (int c = 0; c < 3; ++c) vt[vp_col(v, c)] = v_template[3 * v + c];
 
   // ---- folded joint regression (batch_smpl.py:91-101): J = J_reg^T (v_template + S beta) ----
   std::vector<double> Jbar64(NJ * 3, 0.0), JS64(NJ * 3 * NB, 0.0);
@@ -114,18 +128,18 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   for (size_t i = 0; i < Jbar.size(); ++i) Jbar[i] = (float)Jbar64[i];
   for (size_t i = 0; i < JS.size(); ++i) JS[i] = (float)JS64[i];
 
-  // ---- keypoint regressor CSR by vertex (batch_smpl.py:63-69, :134-138) ----
-  std::vector<int> kptr(NV + 1, 0), kcol;
+  // ---- keypoint regressor CSR by keypoint (batch_smpl.py:63-69, :134-138) ----
+  std::vector<int> kptr(NK + 1, 0), kvtx;
   std::vector<float> kval;
-  for (int v = 0; v < NV; ++v) {
-    for (int k = 0; k < NK; ++k) {
-      float r = kp_regressor[(size_t)v * NK + k];
+  for (int k = 0; k < NK; ++k) {
+    for (int v = 0; v < NV; ++v) {
+      const float r = kp_regressor[(size_t)v * NK + k];
       if (r != 0.0f) {
-        kcol.push_back(k);
+        kvtx.push_back(v);
         kval.push_back(r);
       }
     }
-    kptr[v + 1] = (int)kcol.size();
+    kptr[k + 1] = (int)kvtx.size();
   }
 
   int prev = 0;
@@ -136,7 +150,8 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   m->device = device;
   m->NK = NK;
   m->tree = tree;
-  m->kp_nnz = (int)kcol.size();
+  m->kp_nnz = (int)kvtx.size();
+  m->has_compressed = has_compressed;
   cudaError_t e = cudaSuccess;
   auto chk = [&](cudaError_t x) {
     if (e == cudaSuccess) e = x;
@@ -149,7 +164,8 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->skin_idx, sidx));
   chk(upload(&m->skin_w, sw));
   chk(upload(&m->kp_ptr, kptr));
-  chk(upload(&m->kp_col, kcol));
+  chk(upload(&m->kp_vtx, kvtx));
+  chk(upload(&m->Wimg, Wimg));
   chk(upload(&m->kp_val, kval));
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
@@ -177,7 +193,8 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->skin_idx);
   cudaFree(m->skin_w);
   cudaFree(m->kp_ptr);
-  cudaFree(m->kp_col);
+  cudaFree(m->kp_vtx);
+  cudaFree(m->Wimg);
   cudaFree(m->kp_val);
   smplb::free_tmap_cache(m);
   cudaSetDevice(prev);

@@ -110,6 +110,20 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
         o[r] = make_float4(GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr);
       }
     }
+    if (p.Aimg) {
+      // skinning-GEMM B operand: component e of joint j of sample b, TF32 hi/lo split (skin_tc.cu)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float tr = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
+        const float row[4] = {GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const float hi = tf32_rna(row[c]);
+          p.Aimg[aimg_off(b, j, r * 4 + c, 0)] = hi;
+          p.Aimg[aimg_off(b, j, r * 4 + c, 1)] = tf32_rna(row[c] - hi);
+        }
+      }
+    }
     if (p.cam_pos) {
       const float* cp = p.cam_pos + (size_t)b * 3;
       const float* cr = p.cam_rot + (size_t)b * 3;

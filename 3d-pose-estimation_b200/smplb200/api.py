@@ -116,6 +116,8 @@ class Model:
             return t
 
         skin = not (flags & _lib.F_NO_SKIN)
+        if skin and want_kp and not want_verts:
+            flags |= _lib.F_SCRATCH_VERTS
         verts = buf('verts', (B, NV, 3), want_verts and skin)
         joints = buf('joints', (B, NJ, 3), True)
         kp = buf('kp', (B, self.NK, 3), want_kp and skin)

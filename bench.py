@@ -33,8 +33,8 @@ import torch  # noqa: E402
 METRIC = 'smpl_fwd_proj_samples_per_s'
 UNIT = 'samples/s'
 # Algorithmic bytes per sample of the graded skinning pass (SURVEY.md §8d / BASELINE.md §3):
-# read v_posed 82680 + write verts 82680 + read A 1152 + write kp19 228  (px is written by pose_prep)
-SKIN_BYTES_PER_SAMPLE = 82680 + 82680 + 1152 + 228
+# read v_posed 82680 + write verts 82680 + read A 1152  (keypoints: separate gather kernel; px: pose_prep)
+SKIN_BYTES_PER_SAMPLE = 82680 + 82680 + 1152
 
 
 def peaks():
@@ -178,7 +178,7 @@ def main():
     dd = syn.make_synthetic_smpl(0)
     model = smplb200.Model(dd, device=local_rank)
     B = args.batch
-    flags = _lib.F_BLEND_SIMT if args.blend == 'simt' else 0
+    flags = (_lib.F_BLEND_SIMT | _lib.F_SKIN_SIMT) if args.blend == 'simt' else 0
     inp = syn.make_inputs(B, seed=1000 + rank)
     d = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
     out = {}
@@ -206,10 +206,10 @@ def main():
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
-    kms = (C.c_float * (3 * args.steps))()
+    kms = (C.c_float * (4 * args.steps))()
     ncalls = C.c_int32(0)
     L.smplb_timing_end(kms, C.byref(ncalls))
-    kt = np.array(list(kms), dtype=np.float64).reshape(-1, 3)[:ncalls.value]
+    kt = np.array(list(kms), dtype=np.float64).reshape(-1, 4)[:ncalls.value]
 
     # ---- e2e: host buffers through smplb_forward_host --------------------------------------
     e2e = None
@@ -281,10 +281,10 @@ def main():
                     B * (82944 + 82680) / 1e9),
             },
             'clocks': sampler.summary(),
-            'gpu_launches': 3 * args.steps,
+            'gpu_launches': 4 * args.steps,
             'kernel_ms': {'pose_prep': float(kt[:, 0].mean()), 'blend_gemm': float(kt[:, 1].mean()),
-                          'skinning': skin_ms} if len(kt) else None,
-            'roofline': {'bound': 'hbm', 'kernel': 'skin_kernel (LBS + keypoint regression)',
+                          'skinning': skin_ms, 'keypoints': float(kt[:, 3].mean())} if len(kt) else None,
+            'roofline': {'bound': 'hbm', 'kernel': 'skin_tc_kernel (LBS: tcgen05 weight blend + apply, v_posed -> verts)',
                          'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                          'traffic': traffic, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': SKIN_BYTES_PER_SAMPLE * B},

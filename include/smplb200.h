@@ -52,7 +52,10 @@ enum {
   SMPLB_F_BLEND_SIMT = 1 << 0,   /* blend-shape contraction on CUDA cores (fp32 FFMA) instead of
                                     the tcgen05 3xTF32 kernel — verification / bring-up path   */
   SMPLB_F_KEEP_VPOSED = 1 << 1,  /* keep v_posed in the workspace for smplb_backward           */
-  SMPLB_F_NO_SKIN = 1 << 2       /* get_skin=False and no keypoints wanted: joints-only path   */
+  SMPLB_F_NO_SKIN = 1 << 2,      /* get_skin=False and no keypoints wanted: joints-only path   */
+  SMPLB_F_SKIN_SIMT = 1 << 3,    /* skinning on CUDA cores with the compressed <=4-nonzero weights instead
+                                    of the tcgen05 3xTF32 weight blend — verification path       */
+  SMPLB_F_SCRATCH_VERTS = 1 << 4 /* keypoints wanted but no verts buffer given: the workspace holds verts */
 };
 
 typedef struct smplb_model smplb_model;
@@ -103,8 +106,9 @@ const char* smplb_version(void);
  *   posedirs [207*20670] (:46-51); J_regressor [6890*24] dense (:40-43); weights [6890*24]
  *   (:57-60); kp_regressor [6890*NK] dense (:63-69), NK = 19 or 14; parents [24]
  *   (kintree_table[0] as int32, entry 0 ignored, :54).
- * LBS weights must have at most 4 non-zeros per vertex (true of SMPL); otherwise
- * SMPLB_E_UNSUPPORTED.  Builds the derived constants on `device`. */
+ * Dense LBS weights are supported (the tensor-core skinning contracts all 24 joints); only the
+ * SMPLB_F_SKIN_SIMT verification path needs at most 4 non-zeros per vertex (true of SMPL).
+ * Builds the derived constants on `device`. */
 int32_t smplb_model_create(smplb_model** out, int32_t device,
                            const float* v_template_host, const float* shapedirs_host,
                            const float* posedirs_host, const float* J_regressor_host,
@@ -189,8 +193,9 @@ int32_t smplb_adam_step(int64_t n, float* x, const float* g, float* m, float* v,
                         float lr, float beta1, float beta2, float eps, void* stream);
 
 /* Measurement aid (no reference counterpart): while enabled, every smplb_forward on this host thread
- * records CUDA events on its stream around pose_prep / blend GEMM / skinning.  smplb_timing_end
- * synchronises those events and writes ms_out[call][3] = {prep, blend, skin} milliseconds. */
+ * records CUDA events on its stream around pose_prep / blend GEMM / skinning / keypoints.
+ * smplb_timing_end synchronises those events and writes ms_out[call][4] = {prep, blend, skin, keypoints}
+ * milliseconds. */
 int32_t smplb_timing_begin(int32_t max_calls);
 int32_t smplb_timing_end(float* ms_out_host, int32_t* ncalls_out_host);
 

@@ -15,7 +15,7 @@ import smplb200
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
 GOLD = os.path.join(ROOT, 'tests', 'golden')
-BLENDS = [_lib.F_BLEND_SIMT, 0]   # CUDA-core verification GEMM, tcgen05 3xTF32 GEMM
+BLENDS = [_lib.F_BLEND_SIMT | _lib.F_SKIN_SIMT, 0]   # CUDA-core verification kernels, tcgen05 3xTF32 kernels
 
 
 def _check(out, o, px=None, tol=TOL):
@@ -67,6 +67,21 @@ def test_rest_pose_and_zero_theta(gpu_model, oracle64, flags):
     assert torch.isfinite(out['verts']).all()
     assert maxrel(out['verts'].cpu().numpy()[0], wsum * m.v_template) <= TOL
     assert np.abs(out['Rs'].cpu().numpy() - np.eye(3)).max() <= 1e-7
+
+
+def test_dense_lbs_weights(oracle64):
+    """All 24 weights non-zero per vertex: handled by the tensor-core skinning (dense W x A matmul,
+    batch_smpl.py:125-127); only the compressed-weights verification path refuses it."""
+    dd = syn.make_synthetic_smpl(3, dense_weights=True)
+    model = smplb200.Model(dd, device=0)
+    inp = syn.make_inputs(45, seed=11, dtype=np.float32)
+    out = model.forward(inp['beta'], inp['theta'])
+    m64 = rn.load_model(dd, dtype=np.float64)
+    o = rn.smpl_forward(m64, inp['beta'].astype(np.float64), inp['theta'].astype(np.float64), tile_W=False)
+    _check(out, o)
+    with pytest.raises(smplb200.SmplbError) as ei:
+        model.forward(inp['beta'], inp['theta'], flags=_lib.F_SKIN_SIMT)
+    assert ei.value.code == _lib.E_UNSUPPORTED
 
 
 def test_empty_batch_and_errors(gpu_model):
