@@ -114,11 +114,11 @@ int32_t launch_blend_tc(const smplb_model* m, int B, const float* Ximg, float* v
 __host__ __device__ inline int vp_col(int v, int c) { return (v / SK_VT) * (3 * SK_VT) + c * SK_VT + (v % SK_VT); }
 
 // ---- operand images of the skinning GEMM (skin_tc.cu): T[v, (s,e)] = sum_j W[v,j] A[s][j][e] -------
-#define SK_S 20                         // samples per MMA group: N = 12 * 20 = 240
+#define SK_S 16                         // samples per MMA group: N = 12 * 16 = 192
 #define SK_N (12 * SK_S)
 #define SK_KCH (NJ / 4)                 // 6 K-chunks (24 joints)
 #define SK_WTILE (2 * SK_KCH * SK_VT * 4)   // floats per W tile image  [hi|lo][chunk][128 rows][4]  (6144)
-#define SK_AGRP (2 * SK_KCH * SK_N * 4)     // floats per A group image [hi|lo][chunk][240 rows][4]  (11520)
+#define SK_AGRP (2 * SK_KCH * SK_N * 4)     // floats per A group image [hi|lo][chunk][192 rows][4]  (9216)
 // element (sample b, joint j, component e = 3x4 row-major) of the A operand image
 __host__ __device__ inline size_t aimg_off(int b, int j, int e, int hl) {
   return (size_t)(b / SK_S) * SK_AGRP + (size_t)(((hl * SK_KCH + j / 4) * SK_N + (b % SK_S) * 12 + e) * 4 + (j & 3));

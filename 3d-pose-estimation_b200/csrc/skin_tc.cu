@@ -7,12 +7,13 @@
 // The weight blend is the reference's own matmul W[6890,24] x A[24,12]; doing it per thread from shared
 // memory costs 192 B of smem gather per vertex-sample and was 4x off the HBM roofline (profiles/r01), so
 // it runs on the tensor cores instead, in 3xTF32 (fp32-faithful):
-//   MMA: D[128 vertices, 240 = 20 samples x 12] += W_tile[128, 24] . A_group[240, 24]^T   (9 x M128 N240 K8)
+//   MMA: D[128 vertices, 192 = 16 samples x 12] += W_tile[128, 24] . A_group[192, 24]^T   (9 x M128 N192 K8)
 //   accumulator in TMEM: lane = vertex, 12 columns per sample = the 3x4 blended transform of that vertex.
 // CTA = one vertex tile (W tile resident in smem) x a chunk of sample groups, persistent over units:
-//   warp 0    producer : bulk copies (TMA engine): A group image + the 20 v_posed tile rows of the group
-//   warp 1    MMA      : tcgen05.mma.kind::tf32 into one of two 240-column TMEM accumulators
-//   warps 2-5 epilogue : tcgen05.ld T, apply to v_posed (thread = vertex), transpose through smem so the
+//   warp 0    producer : bulk copies (TMA engine): A group image (2-stage ring) + the 16 v_posed tile rows of
+//                        the group (4-stage ring = the HBM prefetch depth)
+//   warp 1    MMA      : tcgen05.mma.kind::tf32 into one of two 192-column TMEM accumulators
+//   warps 2-9 epilogue : tcgen05.ld T, apply to v_posed (thread = vertex), transpose through smem so the
 //                        verts rows are written as contiguous 8-byte-aligned runs (streaming stores)
 #include "tc_common.cuh"
 
@@ -20,16 +21,20 @@ namespace smplb {
 
 using namespace tc;
 
-constexpr int SKT_THREADS = 192;
+constexpr int SKT_EPI_WARPS = 8;
+constexpr int SKT_THREADS = 64 + 32 * SKT_EPI_WARPS;   // producer warp + MMA warp + epilogue warps
 constexpr int SKT_TMEM_COLS = 512;
+constexpr int SKT_ASTAGES = 2;   // A-image ring (released by the MMA)
+constexpr int SKT_VSTAGES = 4;   // v_posed ring (released by the epilogue): HBM prefetch depth
 constexpr uint32_t SKT_VP_ROW_BYTES = 3 * SK_VT * 4;   // 1536
 
 struct SktSmem {
-  float w[SK_WTILE];                 // 24 576 B  W tile image (hi|lo)
-  float a[2][SK_AGRP];               // 46 080 B  per stage: A group image (hi|lo)
-  float vp[2][SK_S][3 * SK_VT];      // 30 720 B  per stage: v_posed tile rows of the group
-  float out[SK_S][3 * SK_VT];        // 30 720 B  verts staging (AoS)
-  uint64_t full[2], empty[2], acc_full[2], acc_empty[2], w_full, w_empty;
+  float w[SK_WTILE];                          // 24 576 B  W tile image (hi|lo)
+  float a[SKT_ASTAGES][SK_AGRP];              // 36 864 B  per stage: A group image (hi|lo)
+  float vp[SKT_VSTAGES][SK_S][3 * SK_VT];     // 24 576 B  per stage: v_posed tile rows of the group
+  float out[SK_S][3 * SK_VT];                 // 24 576 B  verts staging (AoS)
+  uint64_t afull[SKT_ASTAGES], aempty[SKT_ASTAGES], vfull[SKT_VSTAGES], vempty[SKT_VSTAGES];
+  uint64_t acc_full[2], acc_empty[2], w_full, w_empty;
   uint32_t tmem_base;
 };
 
@@ -42,11 +47,17 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
   const int n_units = SK_NVT * n_chunks;
 
   if (warp == 0 && lane == 0) {
+    for (int s = 0; s < SKT_ASTAGES; ++s) {
+      mbar_init(&sm.afull[s], 1);
+      mbar_init(&sm.aempty[s], 1);              // MMA commit
+    }
+    for (int s = 0; s < SKT_VSTAGES; ++s) {
+      mbar_init(&sm.vfull[s], 1);
+      mbar_init(&sm.vempty[s], SKT_EPI_WARPS);
+    }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&sm.full[s], 1);
-      mbar_init(&sm.empty[s], 5);       // MMA commit + 4 epilogue warps
       mbar_init(&sm.acc_full[s], 1);
-      mbar_init(&sm.acc_empty[s], 4);
+      mbar_init(&sm.acc_empty[s], SKT_EPI_WARPS);
     }
     mbar_init(&sm.w_full, 1);
     mbar_init(&sm.w_empty, 1);
@@ -69,13 +80,15 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
         mbar_arrive_expect_tx(&sm.w_full, SK_WTILE * 4);
         bulk_g2s(sm.w, Wimg + (size_t)vt * SK_WTILE, SK_WTILE * 4, &sm.w_full);
         for (int g = g0; g < g1; ++g, ++it) {
-          const int s = it & 1;
-          mbar_wait(&sm.empty[s], ((it >> 1) & 1) ^ 1);
+          const int sv = it % SKT_VSTAGES, sa = it % SKT_ASTAGES;
           const int ns = min(SK_S, B - g * SK_S);
-          mbar_arrive_expect_tx(&sm.full[s], SK_AGRP * 4 + ns * SKT_VP_ROW_BYTES);
-          bulk_g2s(sm.a[s], Aimg + (size_t)g * SK_AGRP, SK_AGRP * 4, &sm.full[s]);
+          mbar_wait(&sm.vempty[sv], ((it / SKT_VSTAGES) & 1) ^ 1);
+          mbar_arrive_expect_tx(&sm.vfull[sv], ns * SKT_VP_ROW_BYTES);
           const float* src = vposed + (size_t)g * SK_S * VPP + (size_t)vt * (3 * SK_VT);
-          for (int i = 0; i < ns; ++i) bulk_g2s(sm.vp[s][i], src + (size_t)i * VPP, SKT_VP_ROW_BYTES, &sm.full[s]);
+          for (int i = 0; i < ns; ++i) bulk_g2s(sm.vp[sv][i], src + (size_t)i * VPP, SKT_VP_ROW_BYTES, &sm.vfull[sv]);
+          mbar_wait(&sm.aempty[sa], ((it / SKT_ASTAGES) & 1) ^ 1);
+          mbar_arrive_expect_tx(&sm.afull[sa], SK_AGRP * 4);
+          bulk_g2s(sm.a[sa], Aimg + (size_t)g * SK_AGRP, SK_AGRP * 4, &sm.afull[sa]);
         }
       }
     }
@@ -93,13 +106,12 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
         const int g0 = (int)((long long)ch * n_groups / n_chunks), g1 = (int)((long long)(ch + 1) * n_groups / n_chunks);
         mbar_wait(&sm.w_full, ul & 1);
         for (int g = g0; g < g1; ++g, ++it) {
-          const int s = it & 1;
-          const uint32_t ph = (it >> 1) & 1;
-          mbar_wait(&sm.acc_empty[s], ph ^ 1);
-          mbar_wait(&sm.full[s], ph);
+          const int sa = it % SKT_ASTAGES, ac = it & 1;
+          mbar_wait(&sm.acc_empty[ac], ((it >> 1) & 1) ^ 1);
+          mbar_wait(&sm.afull[sa], (it / SKT_ASTAGES) & 1);
           tc_fence_after();
-          const uint32_t ab = smem_u32(sm.a[s]);
-          const uint32_t dcol = tmem + (uint32_t)s * SK_N;
+          const uint32_t ab = smem_u32(sm.a[sa]);
+          const uint32_t dcol = tmem + (uint32_t)ac * SK_N;
 #pragma unroll
           for (int ks = 0; ks < NJ / 8; ++ks) {
             const uint64_t wh = umma_desc_kmajor_noswz(wb + ks * 2 * W_LBO, W_LBO, SBO);
@@ -110,36 +122,42 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
             umma_tf32_ss(dcol, wl, ah, idesc, 1);
             umma_tf32_ss(dcol, wh, al, idesc, 1);
           }
-          umma_commit(&sm.empty[s]);
-          umma_commit(&sm.acc_full[s]);
+          umma_commit(&sm.aempty[sa]);
+          umma_commit(&sm.acc_full[ac]);
         }
         umma_commit(&sm.w_empty);   // W tile may be replaced once every MMA of this unit has read it
       }
     }
     __syncwarp();
   } else {
-    // ================= epilogue (warps 2..5): thread = vertex lane =================
+    // ================= epilogue (warps 2..9): thread = vertex lane, two warps per TMEM lane quarter ====
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;             // samples [8*half, 8*half+8) of the group
     const int l4 = q * 32 + lane;                 // TMEM lane = vertex within the tile
-    const int et = (warp - 2) * 32 + lane;        // 0..127 index for the cooperative copy-out
+    const int ew = warp - 2;                      // 0..7: copy-out rows 2*ew, 2*ew+1
     uint32_t it = 0;
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int vt = u % SK_NVT, ch = u / SK_NVT;
       const int g0 = (int)((long long)ch * n_groups / n_chunks), g1 = (int)((long long)(ch + 1) * n_groups / n_chunks);
-      const int nvalid = min(3 * SK_VT, NV3 - vt * 3 * SK_VT);   // floats of this tile that exist in verts
+      const int nvalid2 = min(3 * SK_VT, NV3 - vt * 3 * SK_VT) / 2;   // float2 of this tile that exist in verts
       for (int g = g0; g < g1; ++g, ++it) {
-        const int s = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
-        mbar_wait(&sm.full[s], ph);       // v_posed rows of this group have landed
-        mbar_wait(&sm.acc_full[s], ph);   // blended transforms are in TMEM
+        const int sv = it % SKT_VSTAGES, ac = it & 1;
+        mbar_wait(&sm.vfull[sv], (it / SKT_VSTAGES) & 1);   // v_posed rows of this group have landed
+        mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);         // blended transforms are in TMEM
         tc_fence_after();
-        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)s * SK_N;
-#pragma unroll 1
-        for (int bt = 0; bt < SK_S / 4; ++bt) {
+        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)ac * SK_N + half * (SK_S / 2) * 12;
+#pragma unroll
+        for (int bt = 0; bt < SK_S / 8; ++bt) {
           uint32_t r0[16], r1[16], r2[16];
           tmem_ld16(tbase + bt * 48, r0);
           tmem_ld16(tbase + bt * 48 + 16, r1);
           tmem_ld16(tbase + bt * 48 + 32, r2);
+          float xs[4], ys[4], zs[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float* row = sm.vp[sv][half * (SK_S / 2) + bt * 4 + k];
+            xs[k] = row[l4]; ys[k] = row[SK_VT + l4]; zs[k] = row[2 * SK_VT + l4];
+          }
           tmem_ld_wait();
           float T[48];
 #pragma unroll
@@ -150,31 +168,35 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const int i = bt * 4 + k;
-            const float x = sm.vp[s][i][l4], y = sm.vp[s][i][SK_VT + l4], z = sm.vp[s][i][2 * SK_VT + l4];
+            float* orow = sm.out[half * (SK_S / 2) + bt * 4 + k] + 3 * l4;
             const float* t = T + 12 * k;
 #pragma unroll
             for (int r = 0; r < 3; ++r)
-              sm.out[i][3 * l4 + r] = fmaf(t[4 * r], x, fmaf(t[4 * r + 1], y, fmaf(t[4 * r + 2], z, t[4 * r + 3])));
+              orow[r] = fmaf(t[4 * r], xs[k], fmaf(t[4 * r + 1], ys[k], fmaf(t[4 * r + 2], zs[k], t[4 * r + 3])));
           }
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(&sm.acc_empty[s]);
-          mbar_arrive(&sm.empty[s]);
+          mbar_arrive(&sm.acc_empty[ac]);
+          mbar_arrive(&sm.vempty[sv]);
         }
-        named_bar_sync(1, 128);   // staging complete
+        named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging complete
         const int ns = min(SK_S, B - g * SK_S);
         float* dst = verts + (size_t)g * SK_S * NV3 + (size_t)vt * (3 * SK_VT);
-        for (int idx = et; idx < ns * (3 * SK_VT / 2); idx += 128) {
-          const int i = idx / (3 * SK_VT / 2), p = idx % (3 * SK_VT / 2);
-          if (2 * p < nvalid) {
-            const float2 v = *reinterpret_cast<const float2*>(&sm.out[i][2 * p]);
-            __stcs(reinterpret_cast<float2*>(dst + (size_t)i * NV3 + 2 * p), v);
+#pragma unroll
+        for (int rr = 0; rr < SK_S / SKT_EPI_WARPS; ++rr) {
+          const int i = ew * (SK_S / SKT_EPI_WARPS) + rr;
+          if (i < ns) {
+            float2 v[6];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) v[k] = *reinterpret_cast<const float2*>(&sm.out[i][2 * (lane + 32 * k)]);
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+              if (lane + 32 * k < nvalid2) __stcs(reinterpret_cast<float2*>(dst + (size_t)i * NV3) + lane + 32 * k, v[k]);
           }
         }
-        named_bar_sync(1, 128);   // staging reusable
+        named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging reusable
       }
     }
   }
