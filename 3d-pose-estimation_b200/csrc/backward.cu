@@ -1,12 +1,352 @@
-// Backward pass — placeholder until the kernels land.
-#include "common.cuh"
+// Hand-written backward of the path (TF autodiff of batch_smpl.py:91-138 + project.py, driven by
+// optimizer.minimize in pose_model_3d.py:393-400).  Adjoint derivation: SURVEY.md appendix A.
+//
+//   joint_bwd_kernel (K6)  warp per sample, lane = joint: projection adjoint, A -> G adjoint, reverse
+//                          kinematic chain with warp shuffles, J = Jbar + JS beta adjoint, Rodrigues adjoint
+//   vertex path            skinning adjoint (skin_bwd.cu) + transposed blend GEMM (blend_bwd.cu) feed K6 with
+//                          g_A[B,24,12] and g_X[B,224] = [g_beta | g_pose_feature]
+#include "geom.cuh"
+
 namespace smplb {
-size_t backward_scratch_bytes(int B) { (void)B; return 0; }
+
+struct JointBwdParams {
+  int B;
+  const float* beta;
+  const float* theta;
+  const float* Jbar;
+  const float* JS;
+  const float* g_joints;   // [B,24,3] nullable
+  const float* g_px;       // [B,24,2] nullable
+  const float* cam_pos;
+  const float* cam_rot;
+  const float* focal;
+  const float* g_A;        // [B,24,12] nullable (skinning adjoint)
+  const float* g_X;        // [B,KPAD] nullable (blend adjoint: 10 shape + 207 pose-feature columns)
+  float* g_beta;
+  float* g_theta;
+  smplb_camcfg cfg;
+  Tree tree;
+};
+
+constexpr int JB_WARPS = 4;
+
+__global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwdParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * JB_WARPS + warp;
+  if (b >= p.B) return;
+  const int j = lane < NJ ? lane : 0;
+  const bool act = lane < NJ;
+  const unsigned FULL = 0xffffffffu;
+
+  // ---- recompute the forward quantities of this joint (pose_prep.cu) ----
+  const float* th = p.theta + (size_t)b * (NJ * 3) + j * 3;
+  const float tx = th[0], ty = th[1], tz = th[2];
+  float R[9];
+  rodrigues_smpl(tx, ty, tz, R);
+  float beta[NB];
+#pragma unroll
+  for (int k = 0; k < NB; ++k) beta[k] = __ldg(p.beta + (size_t)b * NB + k);
+  float J[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float acc = __ldg(p.Jbar + j * 3 + c);
+#pragma unroll
+    for (int k = 0; k < NB; ++k) acc = fmaf(__ldg(p.JS + (j * 3 + c) * NB + k), beta[k], acc);
+    J[c] = acc;
+  }
+  float GR[9], Gt[3];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) GR[e] = R[e];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) Gt[c] = J[c];
+  const int par = p.tree.parent[j];
+  const int dep = act ? p.tree.depth[j] : -1;
+  for (int d = 1; d <= p.tree.max_depth; ++d) {
+    float pR[9], pt[3], pJ[3];
+#pragma unroll
+    for (int e = 0; e < 9; ++e) pR[e] = __shfl_sync(FULL, GR[e], par);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      pt[c] = __shfl_sync(FULL, Gt[c], par);
+      pJ[c] = __shfl_sync(FULL, J[c], par);
+    }
+    if (dep == d) {
+      const float r0 = J[0] - pJ[0], r1 = J[1] - pJ[1], r2 = J[2] - pJ[2];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          GR[r * 3 + c] = pR[r * 3 + 0] * R[c] + pR[r * 3 + 1] * R[3 + c] + pR[r * 3 + 2] * R[6 + c];
+        Gt[r] = pR[r * 3 + 0] * r0 + pR[r * 3 + 1] * r1 + pR[r * 3 + 2] * r2 + pt[r];
+      }
+    }
+  }
+
+  // ---- upstream gradients wrt J_transformed (posed joints) ----
+  float gJt[3] = {0.f, 0.f, 0.f};
+  if (act && p.g_joints) {
+    const float* g = p.g_joints + ((size_t)b * NJ + j) * 3;
+    gJt[0] = g[0]; gJt[1] = g[1]; gJt[2] = g[2];
+  }
+  if (act && p.g_px) {
+    // px = uv / ss * H + off (pose_model_3d.py:229-231); camera held constant (:218-221)
+    const float2 gp = reinterpret_cast<const float2*>(p.g_px)[(size_t)b * NJ + j];
+    const float sc = p.cfg.img_h / p.cfg.ss;
+    const float* cp = p.cam_pos + (size_t)b * 3;
+    const float* cr = p.cam_rot + (size_t)b * 3;
+    const float f = p.focal ? __ldg(p.focal + b) : p.cfg.focal_const;
+    float Rc[9], q[3], u, v, gq[3];
+    rodrigues_cam(__ldg(cr), __ldg(cr + 1), __ldg(cr + 2), Rc);
+    project_point(Rc, Gt[0], Gt[1], Gt[2], __ldg(cp), __ldg(cp + 1), __ldg(cp + 2), f, u, v, q);
+    project_bwd_q(q, f, gp.x * sc, gp.y * sc, gq);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) gJt[r] += Rc[r * 3] * gq[0] + Rc[r * 3 + 1] * gq[1] + Rc[r * 3 + 2] * gq[2];
+  }
+
+  // ---- A -> G adjoint: A.R = G.R, A.t = G.t - G.R J (batch_lbs.py:138-142) ----
+  float gGR[9], gGt[3], gJ[3];
+  {
+    float gAR[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, gAt[3] = {0.f, 0.f, 0.f};
+    if (act && p.g_A) {
+      const float4* g = reinterpret_cast<const float4*>(p.g_A + ((size_t)b * NJ + j) * 12);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float4 v = __ldg(g + r);
+        gAR[r * 3] = v.x; gAR[r * 3 + 1] = v.y; gAR[r * 3 + 2] = v.z; gAt[r] = v.w;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) gGR[r * 3 + c] = gAR[r * 3 + c] - gAt[r] * J[c];
+      gGt[r] = gAt[r] + gJt[r];
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) gJ[c] = -(GR[c] * gAt[0] + GR[3 + c] * gAt[1] + GR[6 + c] * gAt[2]);
+  }
+
+  // ---- reverse kinematic chain, deepest level first; parents gather their children's contributions ----
+  float gR[9];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) gR[e] = 0.f;
+  const int c0 = act ? p.tree.child[j][0] : -1, c1 = act ? p.tree.child[j][1] : -1, c2 = act ? p.tree.child[j][2] : -1;
+  for (int d = p.tree.max_depth; d >= 1; --d) {
+    float pR[9], pJ[3];
+#pragma unroll
+    for (int e = 0; e < 9; ++e) pR[e] = __shfl_sync(FULL, GR[e], par);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) pJ[c] = __shfl_sync(FULL, J[c], par);
+    float con[15];   // contribution to the parent: gGR (9), gGt (3), gJ (3)
+#pragma unroll
+    for (int e = 0; e < 15; ++e) con[e] = 0.f;
+    if (dep == d) {
+      // G_i.R = G_p.R R_i ; G_i.t = G_p.R (J_i - J_p) + G_p.t
+      const float dj[3] = {J[0] - pJ[0], J[1] - pJ[1], J[2] - pJ[2]};
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          gR[r * 3 + c] = pR[r] * gGR[c] + pR[3 + r] * gGR[3 + c] + pR[6 + r] * gGR[6 + c];   // G_p.R^T gGR
+          con[r * 3 + c] = gGR[r * 3] * R[c * 3] + gGR[r * 3 + 1] * R[c * 3 + 1] + gGR[r * 3 + 2] * R[c * 3 + 2] +
+                           gGt[r] * dj[c];                                                      // gGR R^T + gGt dj^T
+        }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        con[9 + c] = gGt[c];
+        const float dv = pR[c] * gGt[0] + pR[3 + c] * gGt[1] + pR[6 + c] * gGt[2];             // G_p.R^T gGt
+        gJ[c] += dv;
+        con[12 + c] = -dv;
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 15; ++e) {
+      const float v0 = __shfl_sync(FULL, con[e], c0 >= 0 ? c0 : 0);
+      const float v1 = __shfl_sync(FULL, con[e], c1 >= 0 ? c1 : 0);
+      const float v2 = __shfl_sync(FULL, con[e], c2 >= 0 ? c2 : 0);
+      float add = 0.f;
+      if (c0 >= 0) add += v0;
+      if (c1 >= 0) add += v1;
+      if (c2 >= 0) add += v2;
+      if (e < 9) gGR[e] += add;
+      else if (e < 12) gGt[e - 9] += add;
+      else gJ[e - 12] += add;
+    }
+  }
+  if (dep == 0) {   // root: G_0 = (R_0, J_0)
+#pragma unroll
+    for (int e = 0; e < 9; ++e) gR[e] = gGR[e];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) gJ[c] += gGt[c];
+  }
+
+  // ---- pose feature adjoint (batch_smpl.py:109-110): phi = vec(R_1..23 - I) ----
+  if (act && j >= 1 && p.g_X) {
+    const float* g = p.g_X + (size_t)b * KPAD + NB + (j - 1) * 9;
+#pragma unroll
+    for (int e = 0; e < 9; ++e) gR[e] += __ldg(g + e);
+  }
+
+  // ---- Rodrigues adjoint -> g_theta ----
+  if (act) {
+    float gth[3];
+    rodrigues_smpl_bwd(tx, ty, tz, gR, gth);
+    float* o = p.g_theta + (size_t)b * (NJ * 3) + j * 3;
+    o[0] = gth[0]; o[1] = gth[1]; o[2] = gth[2];
+  }
+
+  // ---- J = Jbar + JS beta adjoint (+ shape-blend columns of g_X) -> g_beta ----
+  float gb[NB];
+#pragma unroll
+  for (int k = 0; k < NB; ++k) {
+    float v = 0.f;
+    if (act) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v = fmaf(__ldg(p.JS + (j * 3 + c) * NB + k), gJ[c], v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    gb[k] = v;
+  }
+  if (lane < NB) {
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < NB; ++k)
+      if (k == lane) v = gb[k];
+    if (p.g_X) v += __ldg(p.g_X + (size_t)b * KPAD + lane);
+    p.g_beta[(size_t)b * NB + lane] = v;
+  }
 }
-extern "C" int32_t smplb_backward(const smplb_model*, const smplb_backward_io*, void*, size_t, int32_t, void*) {
-  return smplb::fail(SMPLB_E_UNSUPPORTED, "smplb_backward: not built yet");
+
+// project() adjoint (project.py:7-48) wrt points and camera position / rotation.  Thread per camera
+// group: loops over its P points so the per-camera sums have a fixed order.
+__global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, const float* __restrict__ cpos,
+                                   const float* __restrict__ cang, const float* __restrict__ foc, int tiled,
+                                   const float* __restrict__ g_uv, float* __restrict__ g_pts,
+                                   float* __restrict__ g_cpos, float* __restrict__ g_cang) {
+  const int ncam = tiled ? N : N / P;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncam) return;
+  const int np = tiled ? 1 : P;
+  float Rc[9];
+  const float ax = cang[3 * c], ay = cang[3 * c + 1], az = cang[3 * c + 2];
+  rodrigues_cam(ax, ay, az, Rc);
+  const float cx = cpos[3 * c], cy = cpos[3 * c + 1], cz = cpos[3 * c + 2], f = foc[c];
+  float gc[3] = {0.f, 0.f, 0.f}, gRc[9];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) gRc[e] = 0.f;
+  for (int k = 0; k < np; ++k) {
+    const int i = tiled ? c : c * P + k;
+    float q[3], u, v, gq[3];
+    project_point(Rc, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cx, cy, cz, f, u, v, q);
+    project_bwd_q(q, f, g_uv[2 * i], g_uv[2 * i + 1], gq);
+    const float d[3] = {pts[3 * i] - cx, pts[3 * i + 1] - cy, pts[3 * i + 2] - cz};
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const float gp = Rc[r * 3] * gq[0] + Rc[r * 3 + 1] * gq[1] + Rc[r * 3 + 2] * gq[2];   // Rc gq
+      if (g_pts) g_pts[3 * i + r] = gp;
+      gc[r] -= gp;
+#pragma unroll
+      for (int cc = 0; cc < 3; ++cc) gRc[r * 3 + cc] += d[r] * gq[cc];   // q_c = sum_r Rc[r][c] d_r
+    }
+  }
+  if (g_cpos) {
+    g_cpos[3 * c] = gc[0]; g_cpos[3 * c + 1] = gc[1]; g_cpos[3 * c + 2] = gc[2];
+  }
+  if (g_cang) {
+    float gr[3];
+    rodrigues_cam_bwd(ax, ay, az, gRc, gr);
+    g_cang[3 * c] = gr[0]; g_cang[3 * c + 1] = gr[1]; g_cang[3 * c + 2] = gr[2];
+  }
 }
-extern "C" int32_t smplb_project_backward(int32_t, int32_t, const float*, const float*, const float*, const float*,
-                                          int32_t, const float*, float*, float*, float*, void*) {
-  return smplb::fail(SMPLB_E_UNSUPPORTED, "smplb_project_backward: not built yet");
+
+size_t backward_scratch_bytes(int B) {
+  const size_t b = (size_t)(B > 0 ? B : 0);
+  auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+  // g_A [B,24,12] + g_X [B,KPAD] + g_vposed [B,VPP] + g_verts_total [B,NV3] (only touched when needed)
+  return al(b * NJ * 12 * 4) + al(b * KPAD * 4) + al(b * VPP * 4) + al(b * NV3 * 4);
+}
+
+int32_t launch_vertex_backward(const smplb_model* m, int B, const float* vposed, const float* A, const float* Aimg,
+                               const float* g_verts, const float* g_kp, float* g_A, float* g_X, float* g_vposed,
+                               float* g_vtot, cudaStream_t st);
+#ifndef SMPLB_HAVE_VERTEX_BWD
+int32_t launch_vertex_backward(const smplb_model*, int, const float*, const float*, const float*, const float*,
+                               const float*, float*, float*, float*, float*, cudaStream_t) {
+  return fail(SMPLB_E_UNSUPPORTED, "smplb_backward: vertex / keypoint gradients not built yet");
+}
+#endif
+
+}  // namespace smplb
+
+using namespace smplb;
+
+extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io* io, void* workspace,
+                                  size_t workspace_bytes, int32_t flags, void* stream) {
+  if (!m || !io) return fail(SMPLB_E_INVALID_ARG, "smplb_backward: null model or io");
+  if (io->B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_backward: negative batch");
+  if (io->B == 0) return SMPLB_OK;
+  if (!io->beta || !io->theta || !io->g_beta || !io->g_theta)
+    return fail(SMPLB_E_INVALID_ARG, "smplb_backward: beta/theta/g_beta/g_theta are required");
+  if (io->g_px && (!io->cam_pos || !io->cam_rot))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_backward: g_px needs the camera of the forward call");
+  const bool vertex_path = io->g_verts || io->g_kp;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = io->B;
+  float *g_A = nullptr, *g_X = nullptr;
+  if (vertex_path) {
+    if (!(flags & SMPLB_F_KEEP_VPOSED) || (flags & SMPLB_F_NO_SKIN))
+      return fail(SMPLB_E_INVALID_ARG, "smplb_backward: vertex gradients need the workspace of a forward call made with SMPLB_F_KEEP_VPOSED");
+    if (!workspace || workspace_bytes < smplb_workspace_bytes(m, B, flags))
+      return fail(SMPLB_E_INVALID_ARG, "smplb_backward: workspace too small (see smplb_workspace_bytes)");
+    Workspace w = carve(workspace, B, flags);
+    auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+    char* s = (char*)w.bwd;
+    g_A = (float*)s;
+    s += al((size_t)B * NJ * 12 * 4);
+    g_X = (float*)s;
+    s += al((size_t)B * KPAD * 4);
+    float* g_vposed = (float*)s;
+    s += al((size_t)B * VPP * 4);
+    float* g_vtot = (float*)s;
+    int32_t rc = launch_vertex_backward(m, B, w.vposed, w.A, w.Aimg, io->g_verts, io->g_kp, g_A, g_X, g_vposed,
+                                        g_vtot, st);
+    if (rc != SMPLB_OK) return rc;
+  }
+  JointBwdParams p;
+  p.B = B;
+  p.beta = io->beta;
+  p.theta = io->theta;
+  p.Jbar = m->Jbar;
+  p.JS = m->JS;
+  p.g_joints = io->g_joints;
+  p.g_px = io->g_px;
+  p.cam_pos = io->cam_pos;
+  p.cam_rot = io->cam_rot;
+  p.focal = io->focal;
+  p.g_A = g_A;
+  p.g_X = g_X;
+  p.g_beta = io->g_beta;
+  p.g_theta = io->g_theta;
+  p.cfg = io->cfg;
+  p.tree = m->tree;
+  joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts, const float* cams_pos,
+                                          const float* cams_angles, const float* focal_lens, int32_t cam_tiled,
+                                          const float* g_uv, float* g_pts, float* g_cams_pos, float* g_cams_angles,
+                                          void* stream) {
+  if (N < 0 || P < 1) return fail(SMPLB_E_BAD_SHAPE, "smplb_project_backward: N >= 0 and P >= 1 required");
+  if (!cam_tiled && N % P != 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_project_backward: N must be a multiple of P");
+  if (N == 0) return SMPLB_OK;
+  if (!pts || !cams_pos || !cams_angles || !focal_lens || !g_uv)
+    return fail(SMPLB_E_INVALID_ARG, "smplb_project_backward: null pointer");
+  const int ncam = cam_tiled ? N : N / P;
+  project_bwd_kernel<<<(ncam + 127) / 128, 128, 0, (cudaStream_t)stream>>>(N, P, pts, cams_pos, cams_angles,
+                                                                           focal_lens, cam_tiled, g_uv, g_pts,
+                                                                           g_cams_pos, g_cams_angles);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
 }

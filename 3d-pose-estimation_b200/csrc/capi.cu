@@ -7,19 +7,6 @@ namespace smplb {
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
-struct Workspace {
-  float* Ximg;
-  float* A;
-  float* Aimg;
-  float* vposed;
-  float* verts;    // scratch verts when only keypoints are wanted (SMPLB_F_SCRATCH_VERTS)
-  float* joints;   // scratch J_transformed when the caller passes none (backward needs it)
-  float* bwd;      // backward scratch (see backward.cu)
-  size_t total;
-};
-
-size_t backward_scratch_bytes(int B);
-
 Workspace carve(void* base, int B, int flags) {
   Workspace w;
   size_t off = 0;

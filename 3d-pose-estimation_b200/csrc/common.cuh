@@ -46,8 +46,10 @@ int32_t fail(int32_t code, const std::string& msg);
 struct Tree {
   int parent[NJ];
   int depth[NJ];
+  int child[NJ][3];   // -1 padded (SMPL: at most 3 children per joint); used by the backward chain
   int max_depth;
 };
+int32_t build_tree(const int32_t* parents, Tree* out, const char* who);
 
 }  // namespace smplb
 
@@ -100,6 +102,20 @@ struct PrepParams {
   smplb_camcfg cfg;
   Tree tree;
 };
+
+// Carving of the caller-owned workspace (capi.cu)
+struct Workspace {
+  float* Ximg;
+  float* A;
+  float* Aimg;
+  float* vposed;
+  float* verts;    // scratch verts when only keypoints are wanted (SMPLB_F_SCRATCH_VERTS)
+  float* joints;   // scratch J_transformed when the caller passes none
+  float* bwd;      // backward scratch (backward.cu)
+  size_t total;
+};
+Workspace carve(void* base, int B, int flags);
+size_t backward_scratch_bytes(int B);
 
 int32_t launch_pose_prep(const PrepParams& p, cudaStream_t st);
 int32_t launch_blend_simt(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st);

@@ -27,6 +27,26 @@ static cudaError_t upload(T** dptr, const std::vector<T>& h) {
   return e;
 }
 
+int32_t build_tree(const int32_t* parents, Tree* t, const char* who) {
+  t->max_depth = 0;
+  t->parent[0] = 0;
+  t->depth[0] = 0;
+  for (int i = 0; i < NJ; ++i)
+    for (int c = 0; c < 3; ++c) t->child[i][c] = -1;
+  for (int i = 1; i < NJ; ++i) {
+    const int p = parents[i];
+    if (p < 0 || p >= i) return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": parents[i] must be in [0,i)");
+    t->parent[i] = p;
+    t->depth[i] = t->depth[p] + 1;
+    if (t->depth[i] > t->max_depth) t->max_depth = t->depth[i];
+    int c = 0;
+    while (c < 3 && t->child[p][c] >= 0) ++c;
+    if (c == 3) return fail(SMPLB_E_UNSUPPORTED, std::string(who) + ": more than 3 children per joint");
+    t->child[p][c] = i;
+  }
+  return SMPLB_OK;
+}
+
 }  // namespace smplb
 
 extern "C" const char* smplb_last_error(void) { return smplb::last_error(); }
@@ -48,15 +68,9 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
 
   // ---- kinematic tree (kintree_table[0]; parent[i] < i as in batch_lbs.py:122-127) ----
   Tree tree;
-  tree.max_depth = 0;
-  tree.parent[0] = 0;
-  tree.depth[0] = 0;
-  for (int i = 1; i < NJ; ++i) {
-    int p = parents[i];
-    if (p < 0 || p >= i) return fail(SMPLB_E_INVALID_ARG, "smplb_model_create: parents[i] must be in [0,i)");
-    tree.parent[i] = p;
-    tree.depth[i] = tree.depth[p] + 1;
-    if (tree.depth[i] > tree.max_depth) tree.max_depth = tree.depth[i];
+  {
+    int32_t rc = build_tree(parents, &tree, "smplb_model_create");
+    if (rc != SMPLB_OK) return rc;
   }
 
   // ---- compressed LBS weights (batch_smpl.py:57-60, :120-127) ----

@@ -307,12 +307,9 @@ extern "C" int32_t smplb_global_rigid(int32_t N, const float* Rs, const float* J
                                       int32_t rotate_base, float* new_J, float* A44, void* stream) {
   if (N < 0 || !parents || (N > 0 && (!Rs || !Js))) return fail(SMPLB_E_INVALID_ARG, "smplb_global_rigid: bad argument");
   Tree t;
-  t.parent[0] = 0; t.depth[0] = 0; t.max_depth = 0;
-  for (int i = 1; i < NJ; ++i) {
-    if (parents[i] < 0 || parents[i] >= i) return fail(SMPLB_E_INVALID_ARG, "smplb_global_rigid: parents[i] must be in [0,i)");
-    t.parent[i] = parents[i];
-    t.depth[i] = t.depth[parents[i]] + 1;
-    if (t.depth[i] > t.max_depth) t.max_depth = t.depth[i];
+  {
+    int32_t rc = build_tree(parents, &t, "smplb_global_rigid");
+    if (rc != SMPLB_OK) return rc;
   }
   if (N == 0) return SMPLB_OK;
   global_rigid_kernel<<<(N + 3) / 4, 128, 0, (cudaStream_t)stream>>>(N, Rs, Js, t, rotate_base, new_J, A44);

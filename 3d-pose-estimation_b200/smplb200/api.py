@@ -169,11 +169,14 @@ class Model:
         io = BackwardIO(B, _ptr(beta), _ptr(theta), _ptr(g_verts), _ptr(g_joints), _ptr(g_kp),
                         _ptr(g_px), _ptr(cam_pos), _ptr(cam_rot), _ptr(focal), CamCfg(**cfg),
                         _ptr(g_beta), _ptr(g_theta))
-        flags |= _lib.F_KEEP_VPOSED
-        ws, need = self.workspace(B, flags)
+        if g_verts is not None or g_kp is not None:   # vertex path: needs the forward's workspace
+            flags |= _lib.F_KEEP_VPOSED
+            ws, need = self.workspace(B, flags)
+            wsp, wsn = _ptr(ws), ws.numel()
+        else:
+            wsp, wsn = None, 0
         with torch.cuda.device(dev):
-            check(_lib.lib().smplb_backward(self._h, C.byref(io), _ptr(ws), ws.numel(), flags,
-                                            _stream(dev)))
+            check(_lib.lib().smplb_backward(self._h, C.byref(io), wsp, wsn, flags, _stream(dev)))
         return g_beta, g_theta
 
 
