@@ -21,7 +21,8 @@ struct JointBwdParams {
   const float* cam_rot;
   const float* focal;
   const float* g_A;        // [B,24,12] nullable (skinning adjoint)
-  const float* g_X;        // [B,KPAD] nullable (blend adjoint: 10 shape + 207 pose-feature columns)
+  const float* g_X;        // [n_slices][B,KPAD] nullable (blend adjoint: 10 shape + 207 pose-feature columns)
+  int n_slices;            // partial sums of the transposed blend GEMM, added here in slice order
   float* g_beta;
   float* g_theta;
   smplb_camcfg cfg;
@@ -181,9 +182,11 @@ __global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwd
 
   // ---- pose feature adjoint (batch_smpl.py:109-110): phi = vec(R_1..23 - I) ----
   if (act && j >= 1 && p.g_X) {
-    const float* g = p.g_X + (size_t)b * KPAD + NB + (j - 1) * 9;
+    for (int sl = 0; sl < p.n_slices; ++sl) {
+      const float* g = p.g_X + ((size_t)sl * p.B + b) * KPAD + NB + (j - 1) * 9;
 #pragma unroll
-    for (int e = 0; e < 9; ++e) gR[e] += __ldg(g + e);
+      for (int e = 0; e < 9; ++e) gR[e] += __ldg(g + e);
+    }
   }
 
   // ---- Rodrigues adjoint -> g_theta ----
@@ -212,7 +215,8 @@ __global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwd
 #pragma unroll
     for (int k = 0; k < NB; ++k)
       if (k == lane) v = gb[k];
-    if (p.g_X) v += __ldg(p.g_X + (size_t)b * KPAD + lane);
+    if (p.g_X)
+      for (int sl = 0; sl < p.n_slices; ++sl) v += __ldg(p.g_X + ((size_t)sl * p.B + b) * KPAD + lane);
     p.g_beta[(size_t)b * NB + lane] = v;
   }
 }
@@ -259,22 +263,32 @@ __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, 
   }
 }
 
-size_t backward_scratch_bytes(int B) {
+struct BwdScratch {
+  float* g_A;     // [B,24,12]
+  float* g_X;     // [n_slices][B,KPAD]
+  float* g_img;   // TF32 hi/lo operand image of g_vposed: [ceil(B/128)][BB_NKB][BB_GSTAGE]
+  float* g_vtot;  // [B,NV3] g_verts + regressor^T g_kp (only touched when g_kp is given)
+  size_t total;
+};
+
+static BwdScratch carve_bwd(void* base, int B) {
+  BwdScratch w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    char* p = base ? (char*)base + off : nullptr;
+    off += (bytes + 255) / 256 * 256;
+    return (float*)p;
+  };
   const size_t b = (size_t)(B > 0 ? B : 0);
-  auto al = [](size_t x) { return (x + 255) / 256 * 256; };
-  // g_A [B,24,12] + g_X [B,KPAD] + g_vposed [B,VPP] + g_verts_total [B,NV3] (only touched when needed)
-  return al(b * NJ * 12 * 4) + al(b * KPAD * 4) + al(b * VPP * 4) + al(b * NV3 * 4);
+  w.g_A = take(b * NJ * 12 * 4);
+  w.g_X = take((size_t)blend_bwd_slices(B, 148) * b * KPAD * 4);
+  w.g_img = take(((b + BL_BM - 1) / BL_BM) * (size_t)BB_NKB * BB_GSTAGE * 4);
+  w.g_vtot = take(b * NV3 * 4);
+  w.total = off;
+  return w;
 }
 
-int32_t launch_vertex_backward(const smplb_model* m, int B, const float* vposed, const float* A, const float* Aimg,
-                               const float* g_verts, const float* g_kp, float* g_A, float* g_X, float* g_vposed,
-                               float* g_vtot, cudaStream_t st);
-#ifndef SMPLB_HAVE_VERTEX_BWD
-int32_t launch_vertex_backward(const smplb_model*, int, const float*, const float*, const float*, const float*,
-                               const float*, float*, float*, float*, float*, cudaStream_t) {
-  return fail(SMPLB_E_UNSUPPORTED, "smplb_backward: vertex / keypoint gradients not built yet");
-}
-#endif
+size_t backward_scratch_bytes(int B) { return carve_bwd(nullptr, B).total; }
 
 }  // namespace smplb
 
@@ -293,24 +307,29 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   cudaStream_t st = (cudaStream_t)stream;
   const int B = io->B;
   float *g_A = nullptr, *g_X = nullptr;
+  int n_slices = 0;
   if (vertex_path) {
     if (!(flags & SMPLB_F_KEEP_VPOSED) || (flags & SMPLB_F_NO_SKIN))
       return fail(SMPLB_E_INVALID_ARG, "smplb_backward: vertex gradients need the workspace of a forward call made with SMPLB_F_KEEP_VPOSED");
     if (!workspace || workspace_bytes < smplb_workspace_bytes(m, B, flags))
       return fail(SMPLB_E_INVALID_ARG, "smplb_backward: workspace too small (see smplb_workspace_bytes)");
     Workspace w = carve(workspace, B, flags);
-    auto al = [](size_t x) { return (x + 255) / 256 * 256; };
-    char* s = (char*)w.bwd;
-    g_A = (float*)s;
-    s += al((size_t)B * NJ * 12 * 4);
-    g_X = (float*)s;
-    s += al((size_t)B * KPAD * 4);
-    float* g_vposed = (float*)s;
-    s += al((size_t)B * VPP * 4);
-    float* g_vtot = (float*)s;
-    int32_t rc = launch_vertex_backward(m, B, w.vposed, w.A, w.Aimg, io->g_verts, io->g_kp, g_A, g_X, g_vposed,
-                                        g_vtot, st);
+    BwdScratch s = carve_bwd(w.bwd, B);
+    const float* gy = io->g_verts;
+    int32_t rc;
+    if (io->g_kp) {   // adjoint of the keypoint regression folded into the vertex gradient
+      rc = launch_gverts_total(m, B, io->g_verts, io->g_kp, s.g_vtot, st);
+      if (rc != SMPLB_OK) return rc;
+      gy = s.g_vtot;
+    }
+    rc = launch_skin_bwd_gA(m, B, gy, w.vposed, s.g_A, st);                 // g_A  = sum_v w (g_y (x) [v_posed;1])
     if (rc != SMPLB_OK) return rc;
+    rc = launch_skin_bwd_vposed(m, B, gy, w.Aimg, s.g_img, st);             // g_vp = T^T g_y  (operand image)
+    if (rc != SMPLB_OK) return rc;
+    rc = launch_blend_bwd(m, B, s.g_img, s.g_X, &n_slices, st);             // g_X  = g_vp . D^T
+    if (rc != SMPLB_OK) return rc;
+    g_A = s.g_A;
+    g_X = s.g_X;
   }
   JointBwdParams p;
   p.B = B;
@@ -325,6 +344,7 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   p.focal = io->focal;
   p.g_A = g_A;
   p.g_X = g_X;
+  p.n_slices = n_slices;
   p.g_beta = io->g_beta;
   p.g_theta = io->g_theta;
   p.cfg = io->cfg;

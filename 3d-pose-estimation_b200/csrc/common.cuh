@@ -72,6 +72,10 @@ struct smplb_model {
   float4* skin_w;         // [NV]
   int has_compressed;
   float* Wimg;            // [SK_NVT][SK_WTILE] TF32 hi/lo operand image of the dense LBS weights
+  // backward tables
+  int* ent_ptr;           // [SK_NVT][NJ+1] (vertex, weight) pairs of every (vertex tile, joint): skin_bwd.cu
+  float2* ent;            // [nnz] {weight, vertex index inside the tile as int bits}
+  float* DTimg;           // [BB_NKB][BB_DSTAGE] TF32 hi/lo image of D^T (blend_bwd.cu B operand)
   // keypoint regressor (joint_regressor, batch_smpl.py:63-69), CSR by keypoint, fixed summation order
   int* kp_ptr;            // [NK+1]
   int* kp_vtx;            // [nnz] vertex id
@@ -144,6 +148,20 @@ __host__ __device__ inline size_t wimg_off(int v, int j, int hl) {
   return (size_t)(v / SK_VT) * SK_WTILE + (size_t)(((hl * SK_KCH + j / 4) * SK_VT + (v % SK_VT)) * 4 + (j & 3));
 }
 
+// ---- operand images of the transposed blend GEMM (blend_bwd.cu): g_X[b,k] = sum_n g_vposed[b,n] D[k,n] ----
+// A operand = g_vposed (rows = samples, K = the 20736 internal columns): [m_tile][k_block][hi|lo][chunk][row][4]
+// B operand = D^T      (rows = k 0..223,  K = columns)                 :         [k_block][hi|lo][chunk][row][4]
+#define BB_NKB (VPP / BL_KB)                          // 648 k-blocks of 32 columns
+#define BB_GSTAGE (2 * (BL_KB / 4) * BL_BM * 4)       // floats per A stage (8192)
+#define BB_DSTAGE (2 * (BL_KB / 4) * KPAD * 4)        // floats per B stage (14336)
+__host__ __device__ inline size_t gimg_off(int b, int n, int hl) {
+  return (size_t)(b / BL_BM) * ((size_t)BB_NKB * BB_GSTAGE) + (size_t)(n / BL_KB) * BB_GSTAGE +
+         (size_t)(((hl * (BL_KB / 4) + (n % BL_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (n & 3));
+}
+__host__ __device__ inline size_t dtimg_off(int k, int n, int hl) {
+  return (size_t)(n / BL_KB) * BB_DSTAGE + (size_t)(((hl * (BL_KB / 4) + (n % BL_KB) / 4) * KPAD + k) * 4 + (n & 3));
+}
+
 // float offset of element (row b, k) of the X operand image; hl = 0 (hi) / 1 (lo)
 __host__ __device__ inline size_t ximg_off(int b, int k, int hl) {
   return (size_t)(b / BL_BM) * BL_XTILE +
@@ -158,9 +176,23 @@ int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const
                          cudaStream_t st);
 int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts,
                        cudaStream_t st);
+int32_t launch_skin_bwd_vposed(const smplb_model* m, int B, const float* g_verts, const float* Aimg, float* g_img,
+                               cudaStream_t st);
+int32_t launch_skin_bwd_gA(const smplb_model* m, int B, const float* g_verts, const float* vposed, float* g_A,
+                           cudaStream_t st);
+int32_t launch_gverts_total(const smplb_model* m, int B, const float* g_verts, const float* g_kp, float* out,
+                            cudaStream_t st);
+// g_X partial sums: [n_slices][B][KPAD]; returns the slice count through *n_slices
+int32_t launch_blend_bwd(const smplb_model* m, int B, const float* g_img, float* g_X, int* n_slices, cudaStream_t st);
+int blend_bwd_slices(int B, int n_sm);
 int32_t launch_keypoints(const smplb_model* m, int B, const float* verts, float* kp, cudaStream_t st);
 
 // TF32 helpers --------------------------------------------------------------------------------
+__device__ __forceinline__ float tf32_rna_dev(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
 __host__ __device__ inline float tf32_rna_host(float x) {
   // round-to-nearest (ties away) to 10 explicit mantissa bits, like cvt.rna.tf32.f32
   union { float f; uint32_t u; } c;

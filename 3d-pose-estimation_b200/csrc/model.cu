@@ -142,6 +142,35 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   for (size_t i = 0; i < Jbar.size(); ++i) Jbar[i] = (float)Jbar64[i];
   for (size_t i = 0; i < JS.size(); ++i) JS[i] = (float)JS64[i];
 
+  // ---- backward tables ----
+  std::vector<int> eptr((size_t)SK_NVT * (NJ + 1), 0);
+  std::vector<float2> ents;
+  for (int t = 0; t < SK_NVT; ++t) {
+    for (int j = 0; j < NJ; ++j) {
+      eptr[(size_t)t * (NJ + 1) + j] = (int)ents.size();
+      for (int l = 0; l < SK_VT; ++l) {
+        const int v = t * SK_VT + l;
+        if (v >= NV) break;
+        const float w = weights[(size_t)v * NJ + j];
+        if (w != 0.0f) {
+          float2 e;
+          e.x = w;
+          memcpy(&e.y, &l, sizeof(int));
+          ents.push_back(e);
+        }
+      }
+    }
+    eptr[(size_t)t * (NJ + 1) + NJ] = (int)ents.size();
+  }
+  std::vector<float> DTimg((size_t)BB_NKB * BB_DSTAGE, 0.f);
+  for (int k = 0; k < KDIM; ++k)
+    for (int n = 0; n < VPP; ++n) {
+      const float x = D32[(size_t)k * VPP + n];
+      const float hi = tf32_rna_host(x);
+      DTimg[dtimg_off(k, n, 0)] = hi;
+      DTimg[dtimg_off(k, n, 1)] = tf32_rna_host(x - hi);
+    }
+
   // ---- keypoint regressor CSR by keypoint (batch_smpl.py:63-69, :134-138) ----
   std::vector<int> kptr(NK + 1, 0), kvtx;
   std::vector<float> kval;
@@ -180,6 +209,9 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->kp_ptr, kptr));
   chk(upload(&m->kp_vtx, kvtx));
   chk(upload(&m->Wimg, Wimg));
+  chk(upload(&m->ent_ptr, eptr));
+  chk(upload(&m->ent, ents));
+  chk(upload(&m->DTimg, DTimg));
   chk(upload(&m->kp_val, kval));
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
@@ -209,6 +241,9 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->kp_ptr);
   cudaFree(m->kp_vtx);
   cudaFree(m->Wimg);
+  cudaFree(m->ent_ptr);
+  cudaFree(m->ent);
+  cudaFree(m->DTimg);
   cudaFree(m->kp_val);
   smplb::free_tmap_cache(m);
   cudaSetDevice(prev);

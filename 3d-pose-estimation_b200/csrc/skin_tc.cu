@@ -38,6 +38,11 @@ struct SktSmem {
   uint32_t tmem_base;
 };
 
+// MODE 0: forward (above).  MODE 1: adjoint wrt v_posed, g_vposed[b,v] = T[b,v][:3,:3]^T g_verts[b,v]: same
+// weight-blend MMA; the epilogue reads g_verts straight from global (stride-3 loads, prefetched for the whole
+// group before the accumulator is awaited) and writes the result as the TF32 hi/lo A-operand image of the
+// transposed blend GEMM (blend_bwd.cu); `vposed` = g_verts [B,6890,3], `verts` = that image.
+template <int MODE>
 __global__ void __launch_bounds__(SKT_THREADS, 1)
 skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vposed,
                const float* __restrict__ Aimg, const float* __restrict__ Wimg, float* __restrict__ verts) {
@@ -82,10 +87,12 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
         for (int g = g0; g < g1; ++g, ++it) {
           const int sv = it % SKT_VSTAGES, sa = it % SKT_ASTAGES;
           const int ns = min(SK_S, B - g * SK_S);
-          mbar_wait(&sm.vempty[sv], ((it / SKT_VSTAGES) & 1) ^ 1);
-          mbar_arrive_expect_tx(&sm.vfull[sv], ns * SKT_VP_ROW_BYTES);
-          const float* src = vposed + (size_t)g * SK_S * VPP + (size_t)vt * (3 * SK_VT);
-          for (int i = 0; i < ns; ++i) bulk_g2s(sm.vp[sv][i], src + (size_t)i * VPP, SKT_VP_ROW_BYTES, &sm.vfull[sv]);
+          if (MODE == 0) {
+            mbar_wait(&sm.vempty[sv], ((it / SKT_VSTAGES) & 1) ^ 1);
+            mbar_arrive_expect_tx(&sm.vfull[sv], ns * SKT_VP_ROW_BYTES);
+            const float* src = vposed + (size_t)g * SK_S * VPP + (size_t)vt * (3 * SK_VT);
+            for (int i = 0; i < ns; ++i) bulk_g2s(sm.vp[sv][i], src + (size_t)i * VPP, SKT_VP_ROW_BYTES, &sm.vfull[sv]);
+          }
           mbar_wait(&sm.aempty[sa], ((it / SKT_ASTAGES) & 1) ^ 1);
           mbar_arrive_expect_tx(&sm.afull[sa], SK_AGRP * 4);
           bulk_g2s(sm.a[sa], Aimg + (size_t)g * SK_AGRP, SK_AGRP * 4, &sm.afull[sa]);
@@ -142,10 +149,60 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
       const int nvalid2 = min(3 * SK_VT, NV3 - vt * 3 * SK_VT) / 2;   // float2 of this tile that exist in verts
       for (int g = g0; g < g1; ++g, ++it) {
         const int sv = it % SKT_VSTAGES, ac = it & 1;
+        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)ac * SK_N + half * (SK_S / 2) * 12;
+        if (MODE == 1) {
+          // ---- adjoint wrt v_posed ----
+          const int v = vt * SK_VT + l4;
+          const bool vok = v < NV;
+          float gy[SK_S / 2][3];
+#pragma unroll
+          for (int k = 0; k < SK_S / 2; ++k) {
+            const int b = g * SK_S + half * (SK_S / 2) + k;
+            const float* src = vposed + (size_t)(b < B ? b : B - 1) * NV3 + 3 * (size_t)(vok ? v : 0);
+#pragma unroll
+            for (int r = 0; r < 3; ++r) gy[k][r] = vok ? __ldg(src + r) : 0.f;
+          }
+          mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int bt = 0; bt < SK_S / 8; ++bt) {
+            uint32_t r0[16], r1[16], r2[16];
+            tmem_ld16(tbase + bt * 48, r0);
+            tmem_ld16(tbase + bt * 48 + 16, r1);
+            tmem_ld16(tbase + bt * 48 + 32, r2);
+            tmem_ld_wait();
+            float T[48];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              T[e] = __uint_as_float(r0[e]);
+              T[16 + e] = __uint_as_float(r1[e]);
+              T[32 + e] = __uint_as_float(r2[e]);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int b = g * SK_S + half * (SK_S / 2) + bt * 4 + k;
+              const float* t = T + 12 * k;
+              const float* gg = gy[bt * 4 + k];
+              if (b < B) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                  const float val = fmaf(t[c], gg[0], fmaf(t[4 + c], gg[1], t[8 + c] * gg[2]));   // (T.R^T gy)[c]
+                  const float hi = tf32_rna_dev(val);
+                  const int n = vt * (3 * SK_VT) + c * SK_VT + l4;
+                  verts[gimg_off(b, n, 0)] = hi;
+                  verts[gimg_off(b, n, 1)] = tf32_rna_dev(val - hi);
+                }
+              }
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.acc_empty[ac]);
+          continue;
+        }
         mbar_wait(&sm.vfull[sv], (it / SKT_VSTAGES) & 1);   // v_posed rows of this group have landed
         mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);         // blended transforms are in TMEM
         tc_fence_after();
-        const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)ac * SK_N + half * (SK_S / 2) * 12;
 #pragma unroll
         for (int bt = 0; bt < SK_S / 8; ++bt) {
           uint32_t r0[16], r1[16], r2[16];
@@ -209,8 +266,9 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
   }
 }
 
-int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts,
-                       cudaStream_t st) {
+template <int MODE>
+static int32_t launch_skin_tc_mode(const smplb_model* m, int B, const float* in, const float* Aimg, float* out,
+                                   cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
   static int n_sm[64] = {};
   const int dev = m->device & 63;
@@ -218,7 +276,7 @@ int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const f
   if (!n_sm[dev]) {
     int v = 0;
     SMPLB_CUDA_CHECK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, m->device));
-    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(skin_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(skin_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     n_sm[dev] = v;
   }
   const int n_groups = (B + SK_S - 1) / SK_S;
@@ -228,9 +286,20 @@ int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const f
   if (n_chunks > n_groups) n_chunks = n_groups;
   const int n_units = SK_NVT * n_chunks;
   const int grid = n_units < n_sm[dev] ? n_units : n_sm[dev];
-  skin_tc_kernel<<<grid, SKT_THREADS, smem, st>>>(B, n_groups, n_chunks, vposed, Aimg, m->Wimg, verts);
+  skin_tc_kernel<MODE><<<grid, SKT_THREADS, smem, st>>>(B, n_groups, n_chunks, in, Aimg, m->Wimg, out);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
+}
+
+int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts,
+                       cudaStream_t st) {
+  return launch_skin_tc_mode<0>(m, B, vposed, Aimg, verts, st);
+}
+
+// g_verts [B,6890,3] -> TF32 hi/lo operand image of g_vposed (see gimg_off)
+int32_t launch_skin_bwd_vposed(const smplb_model* m, int B, const float* g_verts, const float* Aimg, float* g_img,
+                               cudaStream_t st) {
+  return launch_skin_tc_mode<1>(m, B, g_verts, Aimg, g_img, st);
 }
 
 }  // namespace smplb

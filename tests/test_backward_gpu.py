@@ -115,3 +115,51 @@ def test_dropin_project_autograd():
     assert maxrel(pts.grad.cpu().numpy(), tp.grad.numpy()) <= GTOL
     assert maxrel(cp.grad.cpu().numpy(), tcp.grad.numpy()) <= GTOL
     assert maxrel(ca.grad.cpu().numpy(), tca.grad.numpy()) <= GTOL
+
+
+@pytest.mark.parametrize('B,with_kp', [(3, False), (40, True), (130, False)])
+def test_vertex_path_gradients(gpu_model, tmodel64, B, with_kp):
+    """Linear functionals of the vertices (+ keypoints, + posed joints): skinning adjoint (tensor-core T^T g and
+    the per-joint reduction), transposed blend GEMM, then the joint path (mesh loss, pose_model_3d.py:183-192)."""
+    inp = syn.make_inputs(B, seed=900 + B, dtype=np.float32)
+    rng = np.random.default_rng(B)
+    wv = rng.normal(size=(B, 6890, 3)).astype(np.float32) / 6890
+    wj = rng.normal(size=(B, 24, 3)).astype(np.float32) * 0.1
+    wk = rng.normal(size=(B, 19, 3)).astype(np.float32) * 0.1 if with_kp else None
+    beta, theta = _t64(inp['beta'], True), _t64(inp['theta'], True)
+    o = rt.smpl_forward(tmodel64, beta, theta, tile_W=False)
+    loss = (o['verts'] * _t64(wv)).sum() + (o['J_transformed'] * _t64(wj)).sum()
+    if with_kp:
+        loss = loss + (o['joints'] * _t64(wk)).sum()
+    loss.backward()
+    gpu_model.forward(inp['beta'], inp['theta'], flags=_lib.F_KEEP_VPOSED)
+    gb, gt = gpu_model.backward(inp['beta'], inp['theta'], g_verts=wv, g_joints=wj, g_kp=wk)
+    assert maxrel(gt.cpu().numpy(), theta.grad.numpy()) <= GTOL
+    assert maxrel(gb.cpu().numpy(), beta.grad.numpy()) <= GTOL
+
+
+def test_dropin_smpl_autograd(synth_dd, tmodel64, tmp_path):
+    """The drop-in SMPL class is differentiable (torch.autograd.Function over the hand-written backward):
+    mesh + joint MSE as in pose_model_3d.py:183-192."""
+    from tf_smpl.batch_smpl import SMPL
+    path = str(tmp_path / 'm.pkl')
+    syn.write_pkl(path, synth_dd)
+    smpl = SMPL(path)
+    B = 6
+    inp = syn.make_inputs(B, seed=5, dtype=np.float32)
+    tgt = syn.make_inputs(B, seed=6, dtype=np.float32)
+    with torch.no_grad():
+        gt_v, _, _ = smpl(inp['beta'], tgt['theta'], get_skin=True)
+        gt_j = smpl.J_transformed.clone()
+    beta = torch.tensor(inp['beta'], device='cuda', requires_grad=True)
+    theta = torch.tensor(inp['theta'], device='cuda', requires_grad=True)
+    verts, _, _ = smpl(beta, theta, get_skin=True)
+    loss = 1.0 * torch.mean((verts - gt_v) ** 2) + 2.0 * torch.mean((smpl.J_transformed - gt_j) ** 2)
+    loss.backward()
+    b64, t64 = _t64(inp['beta'], True), _t64(inp['theta'], True)
+    o = rt.smpl_forward(tmodel64, b64, t64, tile_W=False)
+    with torch.no_grad():
+        og = rt.smpl_forward(tmodel64, _t64(inp['beta']), _t64(tgt['theta']), tile_W=False)
+    rt.loss3d(og['verts'], o['verts'], og['J_transformed'], o['J_transformed']).backward()
+    assert maxrel(theta.grad.cpu().numpy(), t64.grad.numpy()) <= GTOL
+    assert maxrel(beta.grad.cpu().numpy(), b64.grad.numpy()) <= GTOL
