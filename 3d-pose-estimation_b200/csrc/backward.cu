@@ -290,6 +290,32 @@ static BwdScratch carve_bwd(void* base, int B) {
 
 size_t backward_scratch_bytes(int B) { return carve_bwd(nullptr, B).total; }
 
+int32_t launch_joint_bwd_px(const smplb_model* m, int B, const float* beta, const float* theta, const float* g_px,
+                            const float* cam_pos, const float* cam_rot, const float* focal, const smplb_camcfg& cfg,
+                            float* g_beta, float* g_theta, cudaStream_t st) {
+  JointBwdParams p;
+  p.B = B;
+  p.beta = beta;
+  p.theta = theta;
+  p.Jbar = m->Jbar;
+  p.JS = m->JS;
+  p.g_joints = nullptr;
+  p.g_px = g_px;
+  p.cam_pos = cam_pos;
+  p.cam_rot = cam_rot;
+  p.focal = focal;
+  p.g_A = nullptr;
+  p.g_X = nullptr;
+  p.n_slices = 0;
+  p.g_beta = g_beta;
+  p.g_theta = g_theta;
+  p.cfg = cfg;
+  p.tree = m->tree;
+  joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
 }  // namespace smplb
 
 using namespace smplb;

@@ -47,6 +47,19 @@ class BackwardIO(C.Structure):
                 ('g_beta', C.c_void_p), ('g_theta', C.c_void_p)]
 
 
+class FitIO(C.Structure):
+    _fields_ = [('B', C.c_int32),
+                ('beta', C.c_void_p), ('theta', C.c_void_p),
+                ('cam_pos', C.c_void_p), ('cam_rot', C.c_void_p), ('focal', C.c_void_p),
+                ('gt_px', C.c_void_p), ('px', C.c_void_p), ('g_px', C.c_void_p),
+                ('g_beta', C.c_void_p), ('g_theta', C.c_void_p),
+                ('m_theta', C.c_void_p), ('v_theta', C.c_void_p),
+                ('m_beta', C.c_void_p), ('v_beta', C.c_void_p),
+                ('loss', C.c_void_p), ('scratch', C.c_void_p),
+                ('cfg', LossCfg), ('n_total', C.c_int64), ('step', C.c_int32),
+                ('lr', C.c_float), ('beta1', C.c_float), ('beta2', C.c_float), ('eps', C.c_float)]
+
+
 # name -> (restype, argtypes); every symbol include/smplb200.h declares
 SYMBOLS = {
     'smplb_last_error': (C.c_char_p, []),
@@ -75,6 +88,8 @@ SYMBOLS = {
     'smplb_project_backward': (C.c_int32, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p]),
+    'smplb_fit_scratch_bytes': (C.c_size_t, [C.c_int32]),
+    'smplb_fit_step': (C.c_int32, [C.c_void_p, C.POINTER(FitIO), C.c_void_p]),
     'smplb_timing_begin': (C.c_int32, [C.c_int32]),
     'smplb_timing_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
     'smplb_adam_step': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -192,6 +192,39 @@ int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts, const flo
 int32_t smplb_adam_step(int64_t n, float* x, const float* g, float* m, float* v, int32_t t,
                         float lr, float beta1, float beta2, float eps, void* stream);
 
+/* One Adam step of iterative fitting on the 2D re-projection loss with per-sample pose (and, when m_beta /
+ * v_beta are given, shape) as the variables: the loss block of deps/pose_3d/pose_model_3d.py:194-238 driven by
+ * the optimiser of :393-401, joint-only path (no vertices).  theta / beta / m / v are updated in place.
+ * loss[0] = scale * sum((px - gt_px)^2) / n_total (this shard's share of the global mean; n_total = global
+ * B*24*2 so that the shares of several GPUs add up under an all-reduce), loss[1] = min(cap, loss[0]),
+ * loss[2] = 1 when the cap is inactive else 0 (the gradient gate of tf.minimum, :237).
+ * Stream-ordered, allocation-free: capturable in a CUDA graph. */
+typedef struct {
+  int32_t B;
+  float* beta;            /* [B,10]  updated when m_beta != NULL */
+  float* theta;           /* [B,72]  updated */
+  const float* cam_pos;   /* [B,3] */
+  const float* cam_rot;   /* [B,3] */
+  const float* focal;     /* [B] nullable -> cfg.cam.focal_const */
+  const float* gt_px;     /* [B,24,2] target 2D joints in pixels */
+  float* px;              /* [B,24,2] out: current projection */
+  float* g_px;            /* [B,24,2] scratch */
+  float* g_beta;          /* [B,10]  out */
+  float* g_theta;         /* [B,72]  out */
+  float* m_theta;         /* Adam moments, [B,72] */
+  float* v_theta;
+  float* m_beta;          /* nullable pair */
+  float* v_beta;
+  float* loss;            /* [3] device */
+  void* scratch;          /* smplb_fit_scratch_bytes(B) device bytes */
+  smplb_losscfg cfg;
+  int64_t n_total;
+  int32_t step;           /* 1-based */
+  float lr, beta1, beta2, eps;
+} smplb_fit_io;
+size_t smplb_fit_scratch_bytes(int32_t B);
+int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, void* stream);
+
 /* Measurement aid (no reference counterpart): while enabled, every smplb_forward on this host thread
  * records CUDA events on its stream around pose_prep / blend GEMM / skinning / keypoints.
  * smplb_timing_end synchronises those events and writes ms_out[call][4] = {prep, blend, skin, keypoints}
