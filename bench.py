@@ -141,6 +141,66 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def run_fit(args, rank, local_rank, world, dist):
+    """BASELINE config 3: fitting on the 2D re-projection loss, B samples per GPU, one Adam step per bench step;
+    the loss scalars are all-reduced over NCCL every step (the only collective of the path)."""
+    import smplb200
+    from smplb200 import synthetic as syn, dist as sd
+    from smplb200.fit import Fitter
+    dev = torch.device('cuda', local_rank)
+    B = args.batch if args.batch != 65536 else 4096
+    model = smplb200.Model(syn.make_synthetic_smpl(0), device=local_rank)
+    inp = syn.make_inputs(B, seed=1000 + rank)
+    tgt = syn.make_inputs(B, seed=5000 + rank)
+    gt_px = model.forward(inp['beta'], tgt['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=4)['px'].clone()
+    f = Fitter(model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, focal=inp['focal'], lr=2e-4,
+               n_total=B * world * 48)
+    gl = torch.zeros(1, device=dev)
+
+    def step():
+        l = f.step()
+        gl.copy_(l[:1])
+        sd.allreduce_scalars(gl)
+
+    for _ in range(args.warmup):
+        step()
+    first = float(gl)
+    graph = None
+    if args.graph and world == 1:
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=s):
+                f.step()
+        torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        graph.replay() if graph is not None else step()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        ms = float(t[0])
+        print(json.dumps({
+            'metric': 'smpl_fit_sample_steps_per_s', 'value': world * B * args.steps / (ms * 1e-3), 'unit': 'sample-steps/s',
+            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': 'SMPL fitting, fwd+bwd of the 2D re-projection loss + TF1 Adam on theta, B=%d per GPU '
+                                   '(BASELINE configs[2])' % B, 'cuda_graph': graph is not None,
+                       'collective': 'all-reduce of 1 loss scalar per step' if world > 1 else 'none'},
+            'gpu_launches': 5 * args.steps, 'loss_first': first, 'loss_last': float(f.loss[0]) * (1 if world == 1 else 1)}),
+            flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -154,6 +214,9 @@ def main():
     ap.add_argument('--cpu-seconds', type=float, default=12.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--mode', default='forward', choices=['forward', 'fit'],
+                    help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
+    ap.add_argument('--graph', action='store_true', help='fit mode: replay the step from a CUDA graph')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
 
@@ -174,6 +237,9 @@ def main():
 
     import smplb200
     from smplb200 import synthetic as syn, _lib
+    if args.mode == 'fit':
+        run_fit(args, rank, local_rank, world, dist)
+        return
     dev = torch.device('cuda', local_rank)
     dd = syn.make_synthetic_smpl(0)
     model = smplb200.Model(dd, device=local_rank)
