@@ -69,7 +69,7 @@ blend_bwd_kernel(int B, int n_mtiles, int n_slices, const float* __restrict__ Gi
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc(2, BL_BM, KPAD);
       constexpr uint32_t G_LBO = BL_BM * 16, D_LBO = KPAD * 16, SBO = 128;
-      constexpr uint32_t G_HL = (BL_KB / 4) * G_LBO, D_HL = (BL_KB / 4) * D_LBO;
+      constexpr uint32_t G_HL = (BB_KB / 4) * G_LBO, D_HL = (BB_KB / 4) * D_LBO;
       uint32_t it = 0, ul = 0;
       for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++ul) {
         const int sl = u % n_slices;
@@ -84,7 +84,7 @@ blend_bwd_kernel(int B, int n_mtiles, int n_slices, const float* __restrict__ Gi
           tc_fence_after();
           const uint32_t gb = smem_u32(sm.g[s]), db = smem_u32(sm.d[s]);
 #pragma unroll
-          for (int ks = 0; ks < BL_KB / 8; ++ks) {
+          for (int ks = 0; ks < BB_KB / 8; ++ks) {
             const uint64_t gh = umma_desc_kmajor_noswz(gb + ks * 2 * G_LBO, G_LBO, SBO);
             const uint64_t gl = umma_desc_kmajor_noswz(gb + G_HL + ks * 2 * G_LBO, G_LBO, SBO);
             const uint64_t dh = umma_desc_kmajor_noswz(db + ks * 2 * D_LBO, D_LBO, SBO);

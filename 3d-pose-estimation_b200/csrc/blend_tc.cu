@@ -3,12 +3,20 @@
 // in 3xTF32 so the result stays fp32-faithful: with X = Xhi + Xlo and D = Dhi + Dlo (each part exactly
 // representable in TF32), acc += Xhi.Dhi + Xlo.Dhi + Xhi.Dlo (the dropped Xlo.Dlo term is ~2^-22).
 //
-// v1 organisation (one CTA per SM, persistent over 128 x 256 output tiles, cta_group::1):
-//   warp 0    producer : one 1-D bulk copy (TMA engine) per operand per k-block into a 2-stage smem ring;
-//                        the operands already sit in global memory as ready-made smem images (common.cuh)
-//   warp 1    MMA      : one elected thread issues tcgen05.mma.kind::tf32 (M=128, N=256, K=8) x 3 products
-//                        x 28 k-steps per tile into one of two 256-column TMEM accumulators
-//   warps 2-5 epilogue : tcgen05.ld the accumulator (lane = sample row), add v_template, store v_posed
+// v2 organisation: CTA PAIRS (cluster of 2 = one TPC, tcgen05 cta_group::2), persistent over 256 x 256
+// output tiles.  v1 (one CTA per 128 x 256 tile, 2 x 96 KB stages) pulled 688 KB of operands from L2 per
+// tile = 64 B/clk/SM at the tensor-pipe rate, more than the L2 delivers (~43 B/clk/SM): tensor pipe 50 %
+// busy.  A pair shares the D tile (each CTA stages one 128-column half), so a CTA reads 458 KB per
+// 128 x 256 outputs, and the smaller stages (32 KB) make a 6-deep ring.
+//   warp 0    producer : per k-block one 1-D bulk copy (TMA engine) of its 128 X rows and one of its D half
+//                        into a 6-stage smem ring; the operands sit in global memory as ready-made smem
+//                        images (common.cuh)
+//   warp 1    leader CTA: one thread issues tcgen05.mma.cta_group::2.kind::tf32 (M=256, N=256, K=8) x 3
+//                        products x 28 k-steps per tile into one of two 256-column TMEM accumulators (each
+//                        CTA holds its 128 rows); commits are multicast to both CTAs' barriers.
+//             peer CTA : one thread relays "my stage is full" to the leader's peer_full barrier
+//   warps 2-5 epilogue : tcgen05.ld the accumulator (lane = sample row), transpose 32 x 32 blocks through
+//                        smem so that every store instruction writes four full 128-byte lines, + v_template
 // smem ring <-> MMA and TMEM <-> epilogue are mbarrier pipelines, so the epilogue of tile i overlaps the
 // MMAs of tile i+1.
 #include "tc_common.cuh"
@@ -17,142 +25,190 @@ namespace smplb {
 
 using namespace tc;
 
-constexpr int TC_STAGES = 2;
-constexpr int TC_X_STAGE_FLOATS = 2 * (BL_KB / 4) * BL_BM * 4;   // hi+lo : 8192 floats = 32 KB
-constexpr int TC_D_STAGE_FLOATS = 2 * (BL_KB / 4) * BL_BN * 4;   // hi+lo : 16384 floats = 64 KB
+constexpr int TC_STAGES = 6;
+constexpr int TC_X_STAGE_FLOATS = 2 * (BL_KB / 4) * BL_BM * 4;   // hi+lo : 4096 floats = 16 KB
+constexpr int TC_D_STAGE_FLOATS = 2 * (BL_KB / 4) * BL_BH * 4;   // hi+lo of one half : 4096 floats = 16 KB
 constexpr uint32_t TC_STAGE_BYTES = (TC_X_STAGE_FLOATS + TC_D_STAGE_FLOATS) * 4;
 constexpr int TC_THREADS = 192;
 constexpr int TC_TMEM_COLS = 512;
+constexpr int TC_EP_PITCH = 36;   // floats per staged row (32 + 4: conflict-free 16-byte accesses both ways)
 
 struct TcSmem {
   float x[TC_STAGES][TC_X_STAGE_FLOATS];
   float d[TC_STAGES][TC_D_STAGE_FLOATS];
-  uint64_t full[TC_STAGES];
-  uint64_t empty[TC_STAGES];
-  uint64_t acc_full[2];
-  uint64_t acc_empty[2];
+  float ep[4][32 * TC_EP_PITCH];
+  uint64_t full[TC_STAGES];        // local bulk copies landed
+  uint64_t peer_full[TC_STAGES];   // (leader) the peer's copies landed
+  uint64_t empty[TC_STAGES];       // MMAs that read the stage completed (multicast commit)
+  uint64_t acc_full[2];            // accumulator complete (multicast commit)
+  uint64_t acc_empty[2];           // (leader) both CTAs' epilogue warps drained the accumulator
   uint32_t tmem_base;
 };
 
-__global__ void __launch_bounds__(TC_THREADS, 1)
+// One 32-row x 32-column block of the accumulator: registers (thread = row) -> smem -> coalesced stores.
+__device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* stage, int lane, const float* vrow,
+                                               float* obase, int rows_valid) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    *reinterpret_cast<float4*>(stage + lane * TC_EP_PITCH + j * 4) =
+        make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                    __uint_as_float(r[4 * j + 3]));
+  __syncwarp();
+  const int c4 = (lane & 7) * 4, rsub = lane >> 3;
+  const float4 tv = __ldg(reinterpret_cast<const float4*>(vrow + c4));
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int row = it * 4 + rsub;
+    float4 v = *reinterpret_cast<const float4*>(stage + row * TC_EP_PITCH + c4);
+    v.x += tv.x;
+    v.y += tv.y;
+    v.z += tv.z;
+    v.w += tv.w;
+    if (row < rows_valid) __stcs(reinterpret_cast<float4*>(obase + (size_t)row * VPP + c4), v);
+  }
+  __syncwarp();
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
 blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float* __restrict__ Dimg,
                 const float* __restrict__ vt, float* __restrict__ vposed) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   TcSmem& sm = *reinterpret_cast<TcSmem*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tiles = n_mtiles * BL_NT;
+  const uint32_t rank = cluster_ctarank();
+  const int n_tiles = ((n_mtiles + 1) / 2) * BL_NT;   // 256-row x 256-column pair tiles
+  const int cl = blockIdx.x >> 1, n_cl = gridDim.x >> 1;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < TC_STAGES; ++s) {
       mbar_init(&sm.full[s], 1);
+      mbar_init(&sm.peer_full[s], 1);
       mbar_init(&sm.empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&sm.acc_full[a], 1);
-      mbar_init(&sm.acc_empty[a], 4);   // one arrival per epilogue warp
+      mbar_init(&sm.acc_empty[a], 8);   // one arrival per epilogue warp of both CTAs
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(&sm.tmem_base, TC_TMEM_COLS);
+  if (warp == 1) tmem_alloc_pair(&sm.tmem_base, TC_TMEM_COLS);
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem = sm.tmem_base;
 
   if (warp == 0) {
-    // ================= producer =================
+    // ================= producer (both CTAs) =================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int mt = t / BL_NT, nt = t % BL_NT;
+      for (int t = cl; t < n_tiles; t += n_cl) {
+        const int mt2 = t / BL_NT, nt = t % BL_NT;
+        int mt = mt2 * 2 + (int)rank;
+        if (mt >= n_mtiles) mt = n_mtiles - 1;   // odd tile count: the peer recomputes a valid tile, stores nothing
         const float* xs = Ximg + (size_t)mt * BL_XTILE;
-        const float* ds = Dimg + (size_t)nt * BL_DTILE;
+        const float* ds = Dimg + (size_t)nt * BL_DTILE + (size_t)rank * TC_D_STAGE_FLOATS;
         for (int kb = 0; kb < BL_NKB; ++kb, ++it) {
           const int s = it % TC_STAGES;
           const uint32_t ph = (it / TC_STAGES) & 1;
           mbar_wait(&sm.empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&sm.full[s], TC_STAGE_BYTES);
           bulk_g2s(sm.x[s], xs + (size_t)kb * TC_X_STAGE_FLOATS, TC_X_STAGE_FLOATS * 4, &sm.full[s]);
-          bulk_g2s(sm.d[s], ds + (size_t)kb * TC_D_STAGE_FLOATS, TC_D_STAGE_FLOATS * 4, &sm.full[s]);
+          bulk_g2s(sm.d[s], ds + (size_t)kb * 2 * TC_D_STAGE_FLOATS, TC_D_STAGE_FLOATS * 4, &sm.full[s]);
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(2, BL_BM, BL_BN);
-      constexpr uint32_t X_LBO = BL_BM * 16, D_LBO = BL_BN * 16, SBO = 128;   // bytes
-      constexpr uint32_t X_HL = (BL_KB / 4) * BL_BM * 16, D_HL = (BL_KB / 4) * BL_BN * 16;   // hi -> lo offset
-      uint32_t it = 0, tl = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
-        const int a = tl & 1;
-        mbar_wait(&sm.acc_empty[a], ((tl >> 1) & 1) ^ 1);
+    // Whole warp runs the loops (uniform control flow); one elected lane issues the tcgen05 / arrive ops.
+    const uint32_t issue = elect_one() ? 1u : 0u;
+    const uint32_t full0 = smem_u32(&sm.full[0]), pfull0 = smem_u32(&sm.peer_full[0]);
+    if (rank != 0) {
+      // ================= peer: relay stage-full to the leader =================
+      uint32_t s = 0, ph = 0;
+      for (int t = cl; t < n_tiles; t += n_cl)
+        for (int kb = 0; kb < BL_NKB; ++kb) {
+          mbar_wait_spin(full0 + s * 8, ph);
+          if (issue) mbar_arrive_remote(&sm.peer_full[s], 0);
+          if (++s == TC_STAGES) { s = 0; ph ^= 1; }
+        }
+    } else {
+      // ================= MMA issuer (leader CTA) =================
+      constexpr uint32_t idesc = umma_idesc(2, 2 * BL_BM, BL_BN);
+      constexpr uint32_t LBO = BL_BM * 16, SBO = 128;                 // bytes; X and D halves are both 128 rows
+      constexpr uint32_t HL = (BL_KB / 4) * LBO;                      // hi -> lo offset inside a stage
+      static_assert(BL_BM == BL_BH, "one descriptor template for both operands");
+      const uint64_t dtempl = umma_desc_kmajor_noswz(0, LBO, SBO);
+      const uint32_t empty0 = smem_u32(&sm.empty[0]);
+      const uint32_t xb0 = smem_u32(sm.x[0]) >> 4, db0 = smem_u32(sm.d[0]) >> 4;
+      uint32_t s = 0, ph = 0, tl = 0;
+      for (int t = cl; t < n_tiles; t += n_cl, ++tl) {
+        const uint32_t a = tl & 1;
+        mbar_wait_spin(smem_u32(&sm.acc_empty[a]), ((tl >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t dcol = tmem + (uint32_t)a * BL_BN;
-        for (int kb = 0; kb < BL_NKB; ++kb, ++it) {
-          const int s = it % TC_STAGES;
-          mbar_wait(&sm.full[s], (it / TC_STAGES) & 1);
+        const uint32_t dcol = tmem + a * BL_BN;
+#pragma unroll 1
+        for (int kb = 0; kb < BL_NKB; ++kb) {
+          mbar_wait_spin(full0 + s * 8, ph);
+          mbar_wait_spin(pfull0 + s * 8, ph);
           tc_fence_after();
-          const uint32_t xb = smem_u32(sm.x[s]), db = smem_u32(sm.d[s]);
+          const uint64_t xd = dtempl + (uint64_t)(xb0 + s * (TC_X_STAGE_FLOATS * 4 / 16));
+          const uint64_t dd = dtempl + (uint64_t)(db0 + s * (TC_D_STAGE_FLOATS * 4 / 16));
 #pragma unroll
           for (int ks = 0; ks < BL_KB / 8; ++ks) {
-            const uint64_t xh = umma_desc_kmajor_noswz(xb + ks * 2 * X_LBO, X_LBO, SBO);
-            const uint64_t xl = umma_desc_kmajor_noswz(xb + X_HL + ks * 2 * X_LBO, X_LBO, SBO);
-            const uint64_t dh = umma_desc_kmajor_noswz(db + ks * 2 * D_LBO, D_LBO, SBO);
-            const uint64_t dl = umma_desc_kmajor_noswz(db + D_HL + ks * 2 * D_LBO, D_LBO, SBO);
-            umma_tf32_ss(dcol, xh, dh, idesc, (kb | ks) != 0);
-            umma_tf32_ss(dcol, xl, dh, idesc, 1);
-            umma_tf32_ss(dcol, xh, dl, idesc, 1);
+            const uint64_t xh = xd + (uint64_t)(ks * 2 * LBO / 16), xl = xh + (uint64_t)(HL / 16);
+            const uint64_t dh = dd + (uint64_t)(ks * 2 * LBO / 16), dl = dh + (uint64_t)(HL / 16);
+            umma_tf32_ss_pair(dcol, xh, dh, idesc, (kb | ks) != 0, issue);
+            umma_tf32_ss_pair(dcol, xl, dh, idesc, 1, issue);
+            umma_tf32_ss_pair(dcol, xh, dl, idesc, 1, issue);
           }
-          umma_commit(&sm.empty[s]);                         // stage free once these MMAs have read it
-          if (kb == BL_NKB - 1) umma_commit(&sm.acc_full[a]);  // accumulator complete
+          umma_commit_pair(empty0 + s * 8, 3, issue);                                        // stage free in both CTAs
+          if (kb == BL_NKB - 1) umma_commit_pair(smem_u32(&sm.acc_full[a]), 3, issue);       // accumulator complete
+          if (++s == TC_STAGES) { s = 0; ph ^= 1; }
         }
       }
     }
     __syncwarp();
   } else {
-    // ================= epilogue (warps 2..5) =================
+    // ================= epilogue (warps 2..5, both CTAs) =================
     const int q = warp & 3;   // TMEM lane quarter this warp may access
+    float* stage = sm.ep[warp - 2];
     uint32_t tl = 0;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++tl) {
-      const int mt = t / BL_NT, nt = t % BL_NT;
+    for (int t = cl; t < n_tiles; t += n_cl, ++tl) {
+      const int mt2 = t / BL_NT, nt = t % BL_NT;
       const int a = tl & 1;
       mbar_wait(&sm.acc_full[a], (tl >> 1) & 1);
       tc_fence_after();
-      const int b = mt * BL_BM + q * 32 + lane;
-      float* orow = vposed + (size_t)b * VPP + (size_t)nt * BL_BN;
+      const int row0 = (mt2 * 2 + (int)rank) * BL_BM + q * 32;
+      const int rows_valid = B - row0;   // <= 0: nothing to store (padding tile)
+      float* obase = vposed + (size_t)row0 * VPP + (size_t)nt * BL_BN;
       const float* vrow = vt + (size_t)nt * BL_BN;
       const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)a * BL_BN;
+      uint32_t ra[32], rb[32];
+      tmem_ld32(tbase, ra);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BL_BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(tbase + c0, r);
+      for (int c0 = 0; c0 < BL_BN; c0 += 64) {
         tmem_ld_wait();
-        if (b < B) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 tv = __ldg(reinterpret_cast<const float4*>(vrow + c0 + j));
-            float4 o;
-            o.x = __uint_as_float(r[j]) + tv.x;
-            o.y = __uint_as_float(r[j + 1]) + tv.y;
-            o.z = __uint_as_float(r[j + 2]) + tv.z;
-            o.w = __uint_as_float(r[j + 3]) + tv.w;
-            *reinterpret_cast<float4*>(orow + c0 + j) = o;
-          }
+        tmem_ld32(tbase + c0 + 32, rb);
+        tc_store_block(ra, stage, lane, vrow + c0, obase + c0, rows_valid);
+        tmem_ld_wait();
+        if (c0 + 64 < BL_BN) {
+          tmem_ld32(tbase + c0 + 64, ra);
+        } else {
+          // every TMEM read of this accumulator has completed: hand it back before the last stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(&sm.acc_empty[a], 0);
         }
+        tc_store_block(rb, stage, lane, vrow + c0 + 32, obase + c0 + 32, rows_valid);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&sm.acc_empty[a]);
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem, TC_TMEM_COLS);
+    tmem_dealloc_pair(tmem, TC_TMEM_COLS);
   }
 }
 
@@ -170,8 +226,9 @@ int32_t launch_blend_tc(const smplb_model* m, int B, const float* Ximg, float* v
     n_sm[dev] = v;
   }
   const int n_mtiles = (B + BL_BM - 1) / BL_BM;
-  const int n_tiles = n_mtiles * BL_NT;
-  const int grid = n_tiles < n_sm[dev] ? n_tiles : n_sm[dev];
+  const int n_tiles = ((n_mtiles + 1) / 2) * BL_NT;
+  const int n_cl = n_tiles < n_sm[dev] / 2 ? n_tiles : n_sm[dev] / 2;
+  const int grid = 2 * n_cl;   // CTA pairs
   blend_tc_kernel<<<grid, TC_THREADS, smem, st>>>(B, n_mtiles, Ximg, m->Dimg, m->v_template_pad, vposed);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;

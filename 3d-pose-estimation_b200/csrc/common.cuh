@@ -21,11 +21,13 @@
 // Both operands are kept in global memory in exactly the byte order the tcgen05 MMA reads them from
 // shared memory (K-major, no swizzle: 16-byte K-chunks, rows contiguous inside a chunk), so that one
 // 1-D bulk copy moves one pipeline stage.  X (samples) : [m_tile][k_block][hi|lo][chunk][row 0..127][4]
-//                                          D (columns) : [n_tile][k_block][hi|lo][chunk][row 0..255][4]
+//                                          D (columns) : [n_tile][k_block][half][hi|lo][chunk][row 0..127][4]
+// (the two CTAs of a pair each hold one 128-column half of the 256-column N tile: cta_group::2 MMA)
 #define BL_BM 128               // samples per M tile
 #define BL_BN 256               // v_posed columns per N tile (VPP = 81 * 256)
-#define BL_KB 32                // K elements per pipeline stage (k-block) = 8 chunks of 4
-#define BL_NKB (KPAD / BL_KB)   // 7 k-blocks
+#define BL_BH 128               // columns of the N tile held by each CTA of the pair
+#define BL_KB 16                // K elements per pipeline stage (k-block) = 4 chunks of 4
+#define BL_NKB (KPAD / BL_KB)   // 14 k-blocks
 #define BL_NT (VPP / BL_BN)     // 81 N tiles
 #define BL_XTILE (BL_NKB * 2 * (BL_KB / 4) * BL_BM * 4)   // floats per X m-tile image (57344)
 #define BL_DTILE (BL_NKB * 2 * (BL_KB / 4) * BL_BN * 4)   // floats per D n-tile image (114688)
@@ -151,15 +153,16 @@ __host__ __device__ inline size_t wimg_off(int v, int j, int hl) {
 // ---- operand images of the transposed blend GEMM (blend_bwd.cu): g_X[b,k] = sum_n g_vposed[b,n] D[k,n] ----
 // A operand = g_vposed (rows = samples, K = the 20736 internal columns): [m_tile][k_block][hi|lo][chunk][row][4]
 // B operand = D^T      (rows = k 0..223,  K = columns)                 :         [k_block][hi|lo][chunk][row][4]
-#define BB_NKB (VPP / BL_KB)                          // 648 k-blocks of 32 columns
-#define BB_GSTAGE (2 * (BL_KB / 4) * BL_BM * 4)       // floats per A stage (8192)
-#define BB_DSTAGE (2 * (BL_KB / 4) * KPAD * 4)        // floats per B stage (14336)
+#define BB_KB 32                                      // columns per pipeline stage
+#define BB_NKB (VPP / BB_KB)                          // 648 k-blocks of 32 columns
+#define BB_GSTAGE (2 * (BB_KB / 4) * BL_BM * 4)       // floats per A stage (8192)
+#define BB_DSTAGE (2 * (BB_KB / 4) * KPAD * 4)        // floats per B stage (14336)
 __host__ __device__ inline size_t gimg_off(int b, int n, int hl) {
-  return (size_t)(b / BL_BM) * ((size_t)BB_NKB * BB_GSTAGE) + (size_t)(n / BL_KB) * BB_GSTAGE +
-         (size_t)(((hl * (BL_KB / 4) + (n % BL_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (n & 3));
+  return (size_t)(b / BL_BM) * ((size_t)BB_NKB * BB_GSTAGE) + (size_t)(n / BB_KB) * BB_GSTAGE +
+         (size_t)(((hl * (BB_KB / 4) + (n % BB_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (n & 3));
 }
 __host__ __device__ inline size_t dtimg_off(int k, int n, int hl) {
-  return (size_t)(n / BL_KB) * BB_DSTAGE + (size_t)(((hl * (BL_KB / 4) + (n % BL_KB) / 4) * KPAD + k) * 4 + (n & 3));
+  return (size_t)(n / BB_KB) * BB_DSTAGE + (size_t)(((hl * (BB_KB / 4) + (n % BB_KB) / 4) * KPAD + k) * 4 + (n & 3));
 }
 
 // float offset of element (row b, k) of the X operand image; hl = 0 (hi) / 1 (lo)
@@ -169,8 +172,9 @@ __host__ __device__ inline size_t ximg_off(int b, int k, int hl) {
 }
 // float offset of element (column n, k) of the D operand image
 __host__ __device__ inline size_t dimg_off(int n, int k, int hl) {
+  const int half = (n % BL_BN) / BL_BH;
   return (size_t)(n / BL_BN) * BL_DTILE +
-         (size_t)((((k / BL_KB) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BN + (n % BL_BN)) * 4 + (k & 3);
+         (size_t)(((((k / BL_KB) * 2 + half) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BH + (n % BL_BH)) * 4 + (k & 3);
 }
 int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
                          cudaStream_t st);

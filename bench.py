@@ -201,6 +201,85 @@ def run_fit(args, rank, local_rank, world, dist):
         dist.destroy_process_group()
 
 
+def run_sweep(args, rank, local_rank, world, dist):
+    """BASELINE config 5: batch-size sweep 1..65536 per GPU, forward (+projection) and forward+backward
+    (mesh + joint loss gradients through the vertex path), per-kernel times and roofline fractions.
+    Each rank runs its own shard (weak scaling, no collective); the time is the max over ranks."""
+    import smplb200
+    from smplb200 import synthetic as syn, _lib
+    dev = torch.device('cuda', local_rank)
+    model = smplb200.Model(syn.make_synthetic_smpl(0), device=local_rank)
+    L = _lib.lib()
+    peak, peak_src = peaks()
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            tf32_peak = float(json.load(f)['bf16_tflops']) / 2.0      # TF32 dense = half the bf16 rate
+    except Exception:
+        tf32_peak = 1125.0
+    rows = []
+    Bs = [1 << i for i in range(0, 17)]
+    if args.batch != 65536:
+        Bs = [b for b in Bs if b <= args.batch]
+    for B in Bs:
+        inp = syn.make_inputs(B, seed=1000 + rank)
+        d = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
+        out = {}
+        g_verts = torch.randn((B, 6890, 3), device=dev) * (1.0 / (B * 20670))
+        g_joints = torch.randn((B, 24, 3), device=dev) * (1.0 / (B * 72))
+        steps = max(3, min(args.steps, int(2e6 / max(B, 1)) + 3))
+
+        def fwd(flags=0):
+            model.forward(d['beta'], d['theta'], d['cam_pos'], d['cam_rot'], d['focal'], flags=flags, out=out)
+
+        def fwdbwd():
+            fwd(_lib.F_KEEP_VPOSED)
+            model.backward(d['beta'], d['theta'], g_verts=g_verts, g_joints=g_joints)
+
+        res = {'B_per_gpu': B, 'steps': steps}
+        for name, fn in (('fwd', fwd), ('fwd_bwd', fwdbwd)):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+            kt = None
+            if name == 'fwd':
+                L.smplb_timing_begin(steps)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            if name == 'fwd':
+                kms = (C.c_float * (4 * steps))()
+                nc = C.c_int32(0)
+                L.smplb_timing_end(kms, C.byref(nc))
+                kt = np.array(list(kms), dtype=np.float64).reshape(-1, 4)[:nc.value].mean(axis=0)
+            t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+            if dist is not None:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t[0])
+            res[name + '_ms'] = ms
+            res[name + '_samples_per_s'] = world * B / (ms * 1e-3)
+            if kt is not None:
+                res['kernel_ms'] = {'pose_prep': kt[0], 'blend_gemm': kt[1], 'skinning': kt[2], 'keypoints': kt[3]}
+                res['skin_hbm_frac'] = SKIN_BYTES_PER_SAMPLE * B / (kt[2] * 1e-3) / 1e9 / peak
+                res['blend_tf32_util_fp32eq'] = 8970780.0 * B / (kt[1] * 1e-3) / 1e12 / tf32_peak
+                res['blend_tf32_util_issued'] = 3 * res['blend_tf32_util_fp32eq']
+        rows.append(res)
+        del g_verts, out, d
+    if rank == 0:
+        print(json.dumps({'metric': 'smpl_sweep', 'n_gpus': world, 'scaling': 'weak', 'dtype': 'f32', 'data': 'synthetic',
+                          'peaks': {'hbm_gbs': peak, 'tf32_tflops': tf32_peak, 'source': peak_src},
+                          'config': {'workload': 'BASELINE configs[4]: batch sweep, fwd+projection and fwd+bwd '
+                                                 '(g_verts + g_joints -> g_theta, g_beta), B per GPU'},
+                          'rows': rows}), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -214,7 +293,7 @@ def main():
     ap.add_argument('--cpu-seconds', type=float, default=12.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
-    ap.add_argument('--mode', default='forward', choices=['forward', 'fit'],
+    ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep'],
                     help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
     ap.add_argument('--graph', action='store_true', help='fit mode: replay the step from a CUDA graph')
     args = ap.parse_args()
@@ -239,6 +318,9 @@ def main():
     from smplb200 import synthetic as syn, _lib
     if args.mode == 'fit':
         run_fit(args, rank, local_rank, world, dist)
+        return
+    if args.mode == 'sweep':
+        run_sweep(args, rank, local_rank, world, dist)
         return
     dev = torch.device('cuda', local_rank)
     dd = syn.make_synthetic_smpl(0)
