@@ -7,7 +7,7 @@ namespace smplb {
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
-Workspace carve(void* base, int B, int flags) {
+Workspace carve(void* base, int B, int flags, int kpv_pitch) {
   Workspace w;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -24,6 +24,7 @@ Workspace carve(void* base, int B, int flags) {
   w.vposed = skin ? take(b * VPP * sizeof(float)) : nullptr;
   w.verts = (skin && (flags & SMPLB_F_SCRATCH_VERTS)) ? take(b * NV3 * sizeof(float)) : nullptr;
   w.bwd = (flags & SMPLB_F_KEEP_VPOSED) ? take(backward_scratch_bytes(B)) : nullptr;
+  w.kpv = (skin && kpv_pitch > 0) ? take(((b + SK_S - 1) / SK_S) * SK_S * (size_t)kpv_pitch * sizeof(float)) : nullptr;
   w.total = off;
   return w;
 }
@@ -75,8 +76,7 @@ extern "C" int32_t smplb_timing_end(float* ms_out, int32_t* ncalls_out) {
 }
 
 extern "C" size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags) {
-  (void)m;
-  return carve(nullptr, B, flags).total;
+  return carve(nullptr, B, flags, m ? m->kpv_pitch : 0).total;
 }
 
 static int32_t check_forward(const smplb_model* m, const smplb_forward_io* io, void* ws, size_t ws_bytes,
@@ -89,8 +89,9 @@ static int32_t check_forward(const smplb_model* m, const smplb_forward_io* io, v
   if ((io->uv || io->px) && !io->cam_pos) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: uv/px need a camera");
   if ((flags & SMPLB_F_NO_SKIN) && (io->verts || io->kp))
     return fail(SMPLB_E_INVALID_ARG, "smplb_forward: SMPLB_F_NO_SKIN excludes verts/kp outputs");
-  if (io->kp && !io->verts && !(flags & SMPLB_F_SCRATCH_VERTS))
-    return fail(SMPLB_E_INVALID_ARG, "smplb_forward: keypoints without a verts buffer need SMPLB_F_SCRATCH_VERTS");
+  if (io->kp && !io->verts && (flags & SMPLB_F_SKIN_SIMT) && !(flags & SMPLB_F_SCRATCH_VERTS))
+    return fail(SMPLB_E_INVALID_ARG,
+                "smplb_forward: keypoints without a verts buffer need SMPLB_F_SCRATCH_VERTS on the SIMT skinning path");
   if (!ws) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace is required");
   if (ws_bytes < smplb_workspace_bytes(m, io->B, flags))
     return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace too small (see smplb_workspace_bytes)");
@@ -104,7 +105,7 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   if (rc != SMPLB_OK || io->B == 0) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int B = io->B;
-  Workspace w = carve(workspace, B, flags);
+  Workspace w = carve(workspace, B, flags, m->kpv_pitch);
   const bool skin = !(flags & SMPLB_F_NO_SKIN) && (io->verts || io->kp || (flags & SMPLB_F_KEEP_VPOSED));
 
   PrepParams p;
@@ -142,16 +143,18 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
     rc = launch_blend_tc(m, B, w.Ximg, w.vposed, st);
   if (rc != SMPLB_OK) return rc;
   timing_mark(2, st);
-  float* verts = io->verts ? io->verts : w.verts;
-  if (verts) {
-    if (flags & SMPLB_F_SKIN_SIMT)
-      rc = launch_skin_simt(m, B, w.vposed, p.A, verts, st);
-    else
-      rc = launch_skin_tc(m, B, w.vposed, w.Aimg, verts, st);
-    if (rc != SMPLB_OK) return rc;
+  // tensor-core path: the skinning epilogue also emits the compact keypoint-vertex rows, so keypoints need
+  // neither a second pass over verts nor (when the caller wants no verts) a verts buffer at all
+  const bool compact = io->kp && !(flags & SMPLB_F_SKIN_SIMT);
+  float* verts = io->verts ? io->verts : (compact ? nullptr : w.verts);
+  if (flags & SMPLB_F_SKIN_SIMT) {
+    if (verts) rc = launch_skin_simt(m, B, w.vposed, p.A, verts, st);
+  } else {
+    rc = launch_skin_tc(m, B, w.vposed, w.Aimg, verts, compact ? w.kpv : nullptr, st);
   }
+  if (rc != SMPLB_OK) return rc;
   timing_mark(3, st);
-  if (io->kp) rc = launch_keypoints(m, B, verts, io->kp, st);
+  if (io->kp) rc = compact ? launch_keypoints_compact(m, B, w.kpv, io->kp, st) : launch_keypoints(m, B, verts, io->kp, st);
   timing_mark(4, st);
   return rc;
 }

@@ -83,6 +83,13 @@ struct smplb_model {
   int* kp_vtx;            // [nnz] vertex id
   float* kp_val;          // [nnz]
   int kp_nnz;
+  // compact keypoint-vertex rows (skin_tc.cu -> keypoints): the skinning epilogue copies the vertices the
+  // regressor touches into kpv[b][kpv_pitch] (runs per vertex tile, padded to whole 32-byte sectors), so the
+  // keypoint pass reads ~8 KB/sample of contiguous data instead of gathering 608 sectors from verts
+  int kpv_pitch;          // floats per sample (multiple of 8)
+  int* kpc_tile_ptr;      // [SK_NVT+1] first compact slot of every vertex tile
+  int* kpc_src;           // [kpv_pitch] float index 3*lv+c inside the tile's staged verts row, -1 = pad
+  int* kpc_slot;          // [nnz] compact slot of the vertex of every regressor entry
   // J_regressor CSR by joint (for d(J)/d(beta) in backward: JS is enough) — not needed
   void* tmap_cache;       // host-side cache of TMA descriptors (blend_tc.cu)
 };
@@ -118,9 +125,10 @@ struct Workspace {
   float* verts;    // scratch verts when only keypoints are wanted (SMPLB_F_SCRATCH_VERTS)
   float* joints;   // scratch J_transformed when the caller passes none
   float* bwd;      // backward scratch (backward.cu)
+  float* kpv;      // compact keypoint-vertex rows [B][kpv_pitch] (last: earlier offsets do not depend on it)
   size_t total;
 };
-Workspace carve(void* base, int B, int flags);
+Workspace carve(void* base, int B, int flags, int kpv_pitch = 0);
 size_t backward_scratch_bytes(int B);
 
 int32_t launch_pose_prep(const PrepParams& p, cudaStream_t st);
@@ -178,7 +186,8 @@ __host__ __device__ inline size_t dimg_off(int n, int k, int hl) {
 }
 int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
                          cudaStream_t st);
-int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts,
+// verts and kpv are each nullable (kpv: compact keypoint-vertex rows, see smplb_model)
+int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts, float* kpv,
                        cudaStream_t st);
 int32_t launch_skin_bwd_vposed(const smplb_model* m, int B, const float* g_verts, const float* Aimg, float* g_img,
                                cudaStream_t st);
@@ -190,6 +199,7 @@ int32_t launch_gverts_total(const smplb_model* m, int B, const float* g_verts, c
 int32_t launch_blend_bwd(const smplb_model* m, int B, const float* g_img, float* g_X, int* n_slices, cudaStream_t st);
 int blend_bwd_slices(int B, int n_sm);
 int32_t launch_keypoints(const smplb_model* m, int B, const float* verts, float* kp, cudaStream_t st);
+int32_t launch_keypoints_compact(const smplb_model* m, int B, const float* kpv, float* kp, cudaStream_t st);
 
 // TF32 helpers --------------------------------------------------------------------------------
 __device__ __forceinline__ float tf32_rna_dev(float x) {

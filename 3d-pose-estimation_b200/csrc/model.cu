@@ -185,6 +185,24 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
     kptr[k + 1] = (int)kvtx.size();
   }
 
+  // compact keypoint-vertex rows: per vertex tile the touched vertices in ascending order, 3 floats each,
+  // the run padded to a multiple of 8 floats (whole 32-byte sectors: no partial-sector writes between CTAs)
+  std::vector<char> touched(NV, 0);
+  for (int v : kvtx) touched[v] = 1;
+  std::vector<int> ctile(SK_NVT + 1, 0), csrc, cslot_of_v(NV, -1), cslot(kvtx.size());
+  for (int t = 0; t < SK_NVT; ++t) {
+    for (int lv = 0; lv < SK_VT; ++lv) {
+      const int v = t * SK_VT + lv;
+      if (v >= NV || !touched[v]) continue;
+      cslot_of_v[v] = (int)csrc.size();
+      for (int c = 0; c < 3; ++c) csrc.push_back(3 * lv + c);
+    }
+    while (csrc.size() % 8) csrc.push_back(-1);
+    ctile[t + 1] = (int)csrc.size();
+  }
+  if (csrc.empty()) csrc.assign(8, -1);
+  for (size_t e = 0; e < kvtx.size(); ++e) cslot[e] = cslot_of_v[kvtx[e]];
+
   int prev = 0;
   cudaGetDevice(&prev);
   SMPLB_CUDA_CHECK(cudaSetDevice(device));
@@ -213,6 +231,10 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->ent, ents));
   chk(upload(&m->DTimg, DTimg));
   chk(upload(&m->kp_val, kval));
+  m->kpv_pitch = ctile[SK_NVT];
+  chk(upload(&m->kpc_tile_ptr, ctile));
+  chk(upload(&m->kpc_src, csrc));
+  chk(upload(&m->kpc_slot, cslot));
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
     smplb_model_destroy(m);
@@ -245,6 +267,9 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->ent);
   cudaFree(m->DTimg);
   cudaFree(m->kp_val);
+  cudaFree(m->kpc_tile_ptr);
+  cudaFree(m->kpc_src);
+  cudaFree(m->kpc_slot);
   smplb::free_tmap_cache(m);
   cudaSetDevice(prev);
   delete m;

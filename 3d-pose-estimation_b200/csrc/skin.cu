@@ -48,7 +48,10 @@ int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const
 
 // warp = sample; for each keypoint the lanes stride over its regressor entries, then a fixed-order
 // butterfly reduction.
-__global__ void __launch_bounds__(128) keypoints_kernel(int B, int NK, const float* __restrict__ verts,
+// Source rows: verts [B][NV3] with entry offset 3*vertex (mul = 3), or the compact keypoint-vertex rows
+// [B][kpv_pitch] written by the skinning epilogue with entry offset = compact slot (mul = 1).  Same entry
+// order either way, so both give bit-identical keypoints.
+__global__ void __launch_bounds__(128) keypoints_kernel(int B, int NK, const float* __restrict__ verts, int pitch, int mul,
                                                         const int* __restrict__ kp_ptr,
                                                         const int* __restrict__ kp_vtx,
                                                         const float* __restrict__ kp_val,
@@ -56,16 +59,17 @@ __global__ void __launch_bounds__(128) keypoints_kernel(int B, int NK, const flo
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * 4 + warp;
   if (b >= B) return;
-  const float* vb = verts + (size_t)b * NV3;
+  const float* vb = verts + (size_t)b * pitch;
+
   for (int k = 0; k < NK; ++k) {
     const int e0 = __ldg(kp_ptr + k), e1 = __ldg(kp_ptr + k + 1);
     float sx = 0.f, sy = 0.f, sz = 0.f;
     for (int e = e0 + lane; e < e1; e += 32) {
-      const int v = __ldg(kp_vtx + e);
+      const int v = __ldg(kp_vtx + e) * mul;
       const float r = __ldg(kp_val + e);
-      sx = fmaf(r, vb[3 * v], sx);
-      sy = fmaf(r, vb[3 * v + 1], sy);
-      sz = fmaf(r, vb[3 * v + 2], sz);
+      sx = fmaf(r, vb[v], sx);
+      sy = fmaf(r, vb[v + 1], sy);
+      sz = fmaf(r, vb[v + 2], sz);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -82,7 +86,46 @@ __global__ void __launch_bounds__(128) keypoints_kernel(int B, int NK, const flo
 
 int32_t launch_keypoints(const smplb_model* m, int B, const float* verts, float* kp, cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
-  keypoints_kernel<<<(B + 3) / 4, 128, 0, st>>>(B, m->NK, verts, m->kp_ptr, m->kp_vtx, m->kp_val, kp);
+  keypoints_kernel<<<(B + 3) / 4, 128, 0, st>>>(B, m->NK, verts, NV3, 3, m->kp_ptr, m->kp_vtx, m->kp_val, kp);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+// Keypoints from the compact rows kpv[group of 16 samples][slot][16] (skin_tc.cu): lane = sample (two groups per
+// warp), every lane walks the regressor entries of its keypoints in order -> coalesced 64-byte row reads, uniform
+// (broadcast) index/value loads, no cross-lane reduction; the 4 warps of a block share 32 samples and split the
+// keypoints.  Same entry order as keypoints_kernel, plain sequential sum per keypoint.
+__global__ void __launch_bounds__(128) keypoints_compact_kernel(int B, int NK, const float* __restrict__ kpv, int pitch,
+                                                                const int* __restrict__ kp_ptr,
+                                                                const int* __restrict__ kp_slot,
+                                                                const float* __restrict__ kp_val,
+                                                                float* __restrict__ kp) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 32 + lane;
+  const bool ok = b < B;
+  const int bc = ok ? b : B - 1;
+  const float* row = kpv + (size_t)(bc / SK_S) * pitch * SK_S + (bc % SK_S);
+  for (int k = warp; k < NK; k += 4) {
+    const int e0 = __ldg(kp_ptr + k), e1 = __ldg(kp_ptr + k + 1);
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+#pragma unroll 8
+    for (int e = e0; e < e1; ++e) {
+      const float* p = row + (size_t)__ldg(kp_slot + e) * SK_S;
+      const float r = __ldg(kp_val + e);
+      sx = fmaf(r, __ldcs(p), sx);
+      sy = fmaf(r, __ldcs(p + SK_S), sy);
+      sz = fmaf(r, __ldcs(p + 2 * SK_S), sz);
+    }
+    if (ok) {
+      float* o = kp + ((size_t)b * NK + k) * 3;
+      o[0] = sx; o[1] = sy; o[2] = sz;
+    }
+  }
+}
+
+int32_t launch_keypoints_compact(const smplb_model* m, int B, const float* kpv, float* kp, cudaStream_t st) {
+  if (B <= 0) return SMPLB_OK;
+  keypoints_compact_kernel<<<(B + 31) / 32, 128, 0, st>>>(B, m->NK, kpv, m->kpv_pitch, m->kp_ptr, m->kpc_slot, m->kp_val, kp);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

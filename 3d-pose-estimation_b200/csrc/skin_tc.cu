@@ -27,12 +27,14 @@ constexpr int SKT_TMEM_COLS = 512;
 constexpr int SKT_ASTAGES = 2;   // A-image ring (released by the MMA)
 constexpr int SKT_VSTAGES = 4;   // v_posed ring (released by the epilogue): HBM prefetch depth
 constexpr uint32_t SKT_VP_ROW_BYTES = 3 * SK_VT * 4;   // 1536
+constexpr int SKT_OUT_PITCH = 3 * SK_VT + 2;
 
 struct SktSmem {
   float w[SK_WTILE];                          // 24 576 B  W tile image (hi|lo)
   float a[SKT_ASTAGES][SK_AGRP];              // 36 864 B  per stage: A group image (hi|lo)
   float vp[SKT_VSTAGES][SK_S][3 * SK_VT];     // 24 576 B  per stage: v_posed tile rows of the group
-  float out[SK_S][3 * SK_VT];                 // 24 576 B  verts staging (AoS)
+  float out[SK_S][SKT_OUT_PITCH];             // 24 704 B  verts staging (AoS); pitch 386: the keypoint-vertex
+                                              //           copy reads 16 samples x 2 slots per warp conflict-free
   uint64_t afull[SKT_ASTAGES], aempty[SKT_ASTAGES], vfull[SKT_VSTAGES], vempty[SKT_VSTAGES];
   uint64_t acc_full[2], acc_empty[2], w_full, w_empty;
   uint32_t tmem_base;
@@ -45,7 +47,9 @@ struct SktSmem {
 template <int MODE>
 __global__ void __launch_bounds__(SKT_THREADS, 1)
 skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vposed,
-               const float* __restrict__ Aimg, const float* __restrict__ Wimg, float* __restrict__ verts) {
+               const float* __restrict__ Aimg, const float* __restrict__ Wimg, float* __restrict__ verts,
+               float* __restrict__ kpv, int kpv_pitch, const int* __restrict__ kpc_tile_ptr,
+               const int* __restrict__ kpc_src) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SktSmem& sm = *reinterpret_cast<SktSmem*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -147,6 +151,19 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
       const int vt = u % SK_NVT, ch = u / SK_NVT;
       const int g0 = (int)((long long)ch * n_groups / n_chunks), g1 = (int)((long long)(ch + 1) * n_groups / n_chunks);
       const int nvalid2 = min(3 * SK_VT, NV3 - vt * 3 * SK_VT) / 2;   // float2 of this tile that exist in verts
+      // compact keypoint-vertex slots of this tile: thread -> (sample i = et & 15, slot ks0 + (et >> 4) + 16 p);
+      // the source indices of the first 4 passes (64 slots) are fetched once per unit
+      int ks0 = 0, ks1 = 0, ksrc[4] = {-1, -1, -1, -1};
+      const int et = (int)threadIdx.x - 64;
+      if (MODE == 0 && kpv) {
+        ks0 = __ldg(kpc_tile_ptr + vt);
+        ks1 = __ldg(kpc_tile_ptr + vt + 1);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const int sl = ks0 + (et >> 4) + 16 * p;
+          if (sl < ks1) ksrc[p] = __ldg(kpc_src + sl);
+        }
+      }
       for (int g = g0; g < g1; ++g, ++it) {
         const int sv = it % SKT_VSTAGES, ac = it & 1;
         const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)ac * SK_N + half * (SK_S / 2) * 12;
@@ -240,11 +257,24 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
         }
         named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging complete
         const int ns = min(SK_S, B - g * SK_S);
+        // vertices the keypoint regressor touches -> compact rows kpv[group][slot][16 samples]: one contiguous
+        // (slots x 64 B) run per (tile, group), each warp store = 128 contiguous bytes
+        if (ks1 > ks0) {
+          const int i = et & 15;
+          float* kd = kpv + ((size_t)g * kpv_pitch + ks0 + (et >> 4)) * SK_S + i;
+#pragma unroll
+          for (int p = 0; p < 4; ++p)
+            if (ks0 + (et >> 4) + 16 * p < ks1) kd[p * 16 * SK_S] = ksrc[p] >= 0 ? sm.out[i][ksrc[p]] : 0.f;
+          for (int sl = ks0 + (et >> 4) + 64; sl < ks1; sl += 16) {   // tiles with more than 64 slots (dense regressors)
+            const int src = __ldg(kpc_src + sl);
+            kpv[((size_t)g * kpv_pitch + sl) * SK_S + i] = src >= 0 ? sm.out[i][src] : 0.f;
+          }
+        }
         float* dst = verts + (size_t)g * SK_S * NV3 + (size_t)vt * (3 * SK_VT);
 #pragma unroll
         for (int rr = 0; rr < SK_S / SKT_EPI_WARPS; ++rr) {
           const int i = ew * (SK_S / SKT_EPI_WARPS) + rr;
-          if (i < ns) {
+          if (i < ns && verts) {
             float2 v[6];
 #pragma unroll
             for (int k = 0; k < 6; ++k) v[k] = *reinterpret_cast<const float2*>(&sm.out[i][2 * (lane + 32 * k)]);
@@ -268,7 +298,7 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
 
 template <int MODE>
 static int32_t launch_skin_tc_mode(const smplb_model* m, int B, const float* in, const float* Aimg, float* out,
-                                   cudaStream_t st) {
+                                   float* kpv, cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
   static int n_sm[64] = {};
   const int dev = m->device & 63;
@@ -286,20 +316,22 @@ static int32_t launch_skin_tc_mode(const smplb_model* m, int B, const float* in,
   if (n_chunks > n_groups) n_chunks = n_groups;
   const int n_units = SK_NVT * n_chunks;
   const int grid = n_units < n_sm[dev] ? n_units : n_sm[dev];
-  skin_tc_kernel<MODE><<<grid, SKT_THREADS, smem, st>>>(B, n_groups, n_chunks, in, Aimg, m->Wimg, out);
+  skin_tc_kernel<MODE><<<grid, SKT_THREADS, smem, st>>>(B, n_groups, n_chunks, in, Aimg, m->Wimg, out, kpv, m->kpv_pitch,
+                                                        m->kpc_tile_ptr, m->kpc_src);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
 
-int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts,
+int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const float* Aimg, float* verts, float* kpv,
                        cudaStream_t st) {
-  return launch_skin_tc_mode<0>(m, B, vposed, Aimg, verts, st);
+  if (!verts && !kpv) return SMPLB_OK;
+  return launch_skin_tc_mode<0>(m, B, vposed, Aimg, verts, kpv, st);
 }
 
 // g_verts [B,6890,3] -> TF32 hi/lo operand image of g_vposed (see gimg_off)
 int32_t launch_skin_bwd_vposed(const smplb_model* m, int B, const float* g_verts, const float* Aimg, float* g_img,
                                cudaStream_t st) {
-  return launch_skin_tc_mode<1>(m, B, g_verts, Aimg, g_img, st);
+  return launch_skin_tc_mode<1>(m, B, g_verts, Aimg, g_img, nullptr, st);
 }
 
 }  // namespace smplb

@@ -116,8 +116,8 @@ class Model:
             return t
 
         skin = not (flags & _lib.F_NO_SKIN)
-        if skin and want_kp and not want_verts:
-            flags |= _lib.F_SCRATCH_VERTS
+        if skin and want_kp and not want_verts and (flags & _lib.F_SKIN_SIMT):
+            flags |= _lib.F_SCRATCH_VERTS   # tensor-core path: keypoints come from the compact rows, no verts needed
         verts = buf('verts', (B, NV, 3), want_verts and skin)
         joints = buf('joints', (B, NJ, 3), True)
         kp = buf('kp', (B, self.NK, 3), want_kp and skin)
