@@ -1,0 +1,331 @@
+// Triangle rasteriser + its gradient as CUDA kernels: the consumer of `verts`
+// (pose_model_3d.py:319-332 -> tf_mesh_renderer).  Pure arithmetic, no graphics API.
+//   forward : deps/tf_mesh_renderer/kernels/rasterize_triangles_impl.cc:75-155 (+ clears of
+//             rasterize_triangles_op.cc:121-125): per pixel the barycentrics, triangle id and NDC depth of the
+//             nearest triangle covering the pixel centre (16.16 fixed-point edge tests, both windings).
+//   backward: kernels/rasterize_triangles_grad.cc:144-218: d f / d vertices(x, y) from d f / d barycentrics.
+//
+// The reference walks the triangles in order on one core; a pixel finally holds the triangle with the smallest
+// z, ties going to the highest triangle id (`z > z_buffer` skips, so an equal z overwrites).  That final state is
+// order independent, so the triangles run in parallel and resolve through ONE 64-bit atomicMin per covered pixel
+// on the key (orderable z bits << 32 | ~id); a second pass decodes the winner and recomputes its barycentrics
+// with the same float operations (no FMA contraction, the double-precision viewport transform of the
+// reference, x86 float->int conversion semantics), so ids, barycentrics and depth are bit-identical to the
+// reference's C++.  (Not reproduced: NaN depths of zero-area triangles, which the reference lets through.)
+#include <vector>
+
+#include "common.cuh"
+
+struct smplb_mesh {
+  int device;
+  int T, V;
+  int* tri;        // [T][3]
+  int* vptr;       // [V+1] CSR vertex -> incident (triangle, corner), ascending triangle id
+  int* vent;       // [3T]  triangle * 3 + corner
+};
+
+namespace smplb {
+
+constexpr int RS_BIG = 256;   // bounding boxes with more pixels than this go to the CTA-per-triangle kernel
+
+// static_cast<int>(float) as x86-64 does it (cvttss2si): out of range / NaN -> INT_MIN
+__device__ __forceinline__ int x86_f2i(float f) {
+  return (f >= -2147483648.0f && f < 2147483648.0f) ? (int)f : (int)0x80000000;
+}
+__device__ __forceinline__ int clamped_min3(float a, float b, float c, int lo, int hi) {   // impl.cc:25-29
+  return min(max(x86_f2i(floorf(fminf(fminf(a, b), c))), lo), hi);
+}
+__device__ __forceinline__ int clamped_max3(float a, float b, float c, int lo, int hi) {   // impl.cc:33-37
+  return min(max(x86_f2i(ceilf(fmaxf(fmaxf(a, b), c))), lo), hi);
+}
+__device__ __forceinline__ int fixed_point(float f) { return x86_f2i(__fmul_rn(f, 65536.0f)); }   // impl.cc:41
+__device__ __forceinline__ bool is_ccw(int v0x, int v0y, int v1x, int v1y, int px, int py) {       // impl.cc:45-56
+  const int ex = v1x - v0x, ey = v1y - v0y, x = px - v0x, y = py - v0y;
+  return (long long)ex * (long long)y >= (long long)ey * (long long)x;
+}
+
+struct TriSetup {
+  float v0x, v0y, v1x, v1y, v2x, v2y, z0, z1, z2;
+  int f0x, f0y, f1x, f1y, f2x, f2y;
+  int left, right, bottom, top;
+};
+
+// impl.cc:82-107.  (v + 1.0) * half is evaluated in double and rounded once, as the C++ does.
+__device__ __forceinline__ void tri_setup(const float* __restrict__ ndc, const int* __restrict__ tri, int t, int W, int H,
+                                          TriSetup& s) {
+  const float half_w = (float)(0.5 * (double)W), half_h = (float)(0.5 * (double)H);
+  const int i0 = 3 * __ldg(tri + 3 * t), i1 = 3 * __ldg(tri + 3 * t + 1), i2 = 3 * __ldg(tri + 3 * t + 2);
+  auto vp = [](float v, float half) { return __double2float_rn(__dmul_rn(__dadd_rn((double)v, 1.0), (double)half)); };
+  s.v0x = vp(ndc[i0], half_w); s.v0y = vp(ndc[i0 + 1], half_h); s.z0 = ndc[i0 + 2];
+  s.v1x = vp(ndc[i1], half_w); s.v1y = vp(ndc[i1 + 1], half_h); s.z1 = ndc[i1 + 2];
+  s.v2x = vp(ndc[i2], half_w); s.v2y = vp(ndc[i2 + 1], half_h); s.z2 = ndc[i2 + 2];
+  s.left = clamped_min3(s.v0x, s.v1x, s.v2x, 0, W);
+  s.right = clamped_max3(s.v0x, s.v1x, s.v2x, 0, W);
+  s.bottom = clamped_min3(s.v0y, s.v1y, s.v2y, 0, H);
+  s.top = clamped_max3(s.v0y, s.v1y, s.v2y, 0, H);
+  s.f0x = fixed_point(s.v0x); s.f0y = fixed_point(s.v0y);
+  s.f1x = fixed_point(s.v1x); s.f1y = fixed_point(s.v1y);
+  s.f2x = fixed_point(s.v2x); s.f2y = fixed_point(s.v2y);
+}
+
+// impl.cc:112-143 for one pixel: coverage test, barycentrics, depth, clip test.  No contraction anywhere.
+__device__ __forceinline__ bool tri_eval(const TriSetup& s, int ix, int iy, float& b0, float& b1, float& b2, float& z) {
+  const float px = (float)ix + 0.5f, py = (float)iy + 0.5f;   // exact
+  const int fx = fixed_point(px), fy = fixed_point(py);
+  const bool in = (is_ccw(s.f0x, s.f0y, s.f1x, s.f1y, fx, fy) && is_ccw(s.f1x, s.f1y, s.f2x, s.f2y, fx, fy) &&
+                   is_ccw(s.f2x, s.f2y, s.f0x, s.f0y, fx, fy)) ||
+                  (is_ccw(s.f1x, s.f1y, s.f0x, s.f0y, fx, fy) && is_ccw(s.f2x, s.f2y, s.f1x, s.f1y, fx, fy) &&
+                   is_ccw(s.f0x, s.f0y, s.f2x, s.f2y, fx, fy));
+  if (!in) return false;
+  const float area2 = __fsub_rn(__fmul_rn(__fsub_rn(s.v2x, s.v0x), __fsub_rn(s.v1y, s.v0y)),
+                                __fmul_rn(__fsub_rn(s.v2y, s.v0y), __fsub_rn(s.v1x, s.v0x)));
+  b0 = __fdiv_rn(__fsub_rn(__fmul_rn(__fsub_rn(px, s.v1x), __fsub_rn(s.v2y, s.v1y)),
+                           __fmul_rn(__fsub_rn(py, s.v1y), __fsub_rn(s.v2x, s.v1x))), area2);
+  b1 = __fdiv_rn(__fsub_rn(__fmul_rn(__fsub_rn(px, s.v2x), __fsub_rn(s.v0y, s.v2y)),
+                           __fmul_rn(__fsub_rn(py, s.v2y), __fsub_rn(s.v0x, s.v2x))), area2);
+  b2 = __fsub_rn(__fsub_rn(1.0f, b0), b1);
+  z = __fadd_rn(__fadd_rn(__fmul_rn(b0, s.z0), __fmul_rn(b1, s.z1)), __fmul_rn(b2, s.z2));
+  return z >= -1.0f && z <= 1.0f;   // also rejects NaN (see header)
+}
+
+__device__ __forceinline__ unsigned long long pack_key(float z, int t) {
+  if (z == 0.0f) z = 0.0f;   // -0 and +0 compare equal in the reference
+  const uint32_t b = __float_as_uint(z);
+  const uint32_t o = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  return ((unsigned long long)o << 32) | (uint32_t)(~(uint32_t)t);
+}
+constexpr unsigned long long KEY_EMPTY = ~0ull;
+
+__global__ void raster_clear_kernel(unsigned long long* keys, size_t n, int* big_count) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) keys[i] = KEY_EMPTY;
+  if (i == 0) *big_count = 0;
+}
+
+// thread = (image, triangle): small bounding boxes are walked here, large ones queued
+__global__ void __launch_bounds__(128) raster_tri_kernel(int T, int V, int W, int H, const float* __restrict__ ndc,
+                                                         const int* __restrict__ tri, unsigned long long* __restrict__ keys,
+                                                         int* __restrict__ big_list, int* __restrict__ big_count) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+  if (t >= T) return;
+  TriSetup s;
+  tri_setup(ndc + (size_t)b * V * 3, tri, t, W, H, s);
+  const int bw = s.right - s.left, bh = s.top - s.bottom;
+  if (bw <= 0 || bh <= 0) return;
+  if (bw * bh > RS_BIG) {
+    big_list[atomicAdd(big_count, 1)] = b * T + t;
+    return;
+  }
+  unsigned long long* k = keys + (size_t)b * W * H;
+  for (int iy = s.bottom; iy < s.top; ++iy)
+    for (int ix = s.left; ix < s.right; ++ix) {
+      float b0, b1, b2, z;
+      if (tri_eval(s, ix, iy, b0, b1, b2, z)) atomicMin(k + iy * W + ix, pack_key(z, t));
+    }
+}
+
+// CTA = one queued large triangle, threads stride over its bounding box
+__global__ void __launch_bounds__(256) raster_big_kernel(int T, int V, int W, int H, const float* __restrict__ ndc,
+                                                         const int* __restrict__ tri, unsigned long long* __restrict__ keys,
+                                                         const int* __restrict__ big_list, const int* __restrict__ big_count) {
+  const int n = *big_count;
+  for (int e = blockIdx.x; e < n; e += gridDim.x) {
+    const int b = big_list[e] / T, t = big_list[e] % T;
+    TriSetup s;
+    tri_setup(ndc + (size_t)b * V * 3, tri, t, W, H, s);
+    const int bw = s.right - s.left, np = bw * (s.top - s.bottom);
+    unsigned long long* k = keys + (size_t)b * W * H;
+    for (int i = threadIdx.x; i < np; i += blockDim.x) {
+      const int ix = s.left + i % bw, iy = s.bottom + i / bw;
+      float b0, b1, b2, z;
+      if (tri_eval(s, ix, iy, b0, b1, b2, z)) atomicMin(k + iy * W + ix, pack_key(z, t));
+    }
+  }
+}
+
+// thread = pixel: decode the winner, recompute its barycentrics / depth, write the three outputs
+__global__ void __launch_bounds__(256) raster_resolve_kernel(int B, int T, int V, int W, int H, const float* __restrict__ ndc,
+                                                             const int* __restrict__ tri,
+                                                             const unsigned long long* __restrict__ keys,
+                                                             float* __restrict__ bary, int* __restrict__ ids,
+                                                             float* __restrict__ zbuf) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)B * W * H) return;
+  const int b = (int)(i / ((size_t)W * H)), p = (int)(i % ((size_t)W * H));
+  const unsigned long long key = keys[i];
+  float b0 = 0.f, b1 = 0.f, b2 = 0.f, z = 1.0f;
+  int t = 0;
+  if (key != KEY_EMPTY) {
+    t = (int)(~(uint32_t)key);
+    TriSetup s;
+    tri_setup(ndc + (size_t)b * V * 3, tri, t, W, H, s);
+    tri_eval(s, p % W, p / W, b0, b1, b2, z);
+  }
+  if (bary) {
+    bary[3 * i] = b0;
+    bary[3 * i + 1] = b1;
+    bary[3 * i + 2] = b2;
+  }
+  if (ids) ids[i] = t;
+  if (zbuf) zbuf[i] = z;
+}
+
+// ---- backward (rasterize_triangles_grad.cc:144-218) ------------------------------------------------------------
+// The reference accumulates pixel by pixel into df_dvertices; here every (image, triangle) thread walks the pixels
+// of its own bounding box in the same row-major order and keeps the six sums of its corners, then every
+// (image, vertex) thread adds the partial sums of its incident corners in ascending triangle order: no atomics,
+// run-to-run deterministic; differs from the reference only in float summation order (tolerance 1e-4, tests).
+__global__ void __launch_bounds__(128) raster_bwd_tri_kernel(int T, int V, int W, int H, const float* __restrict__ ndc,
+                                                             const int* __restrict__ tri, const float* __restrict__ bary,
+                                                             const int* __restrict__ ids, const float* __restrict__ g_bary,
+                                                             float* __restrict__ tri_grad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+  if (t >= T) return;
+  const float* nv = ndc + (size_t)b * V * 3;
+  float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  TriSetup s;
+  tri_setup(nv, tri, t, W, H, s);
+  const int i0 = 3 * __ldg(tri + 3 * t), i1 = 3 * __ldg(tri + 3 * t + 1), i2 = 3 * __ldg(tri + 3 * t + 2);
+  const float v0x = nv[i0], v0y = nv[i0 + 1], v1x = nv[i1], v1y = nv[i1 + 1], v2x = nv[i2], v2y = nv[i2 + 1];
+  const float area = (v1x - v0x) * (v2y - v0y) - (v1y - v0y) * (v2x - v0x);   // grad.cc:183-184 (NDC)
+  if (fabsf(area) >= 1e-13f) {                                                // grad.cc:186
+    const float dx0 = v2y - v1y, dx1 = v0y - v2y, dx2 = v1y - v0y;            // grad.cc:198-203
+    const float dy0 = v1x - v2x, dy1 = v2x - v0x, dy2 = v0x - v1x;
+    const size_t base = (size_t)b * W * H;
+    for (int iy = s.bottom; iy < s.top; ++iy)
+      for (int ix = s.left; ix < s.right; ++ix) {
+        const size_t p = base + (size_t)iy * W + ix;
+        if (__ldg(ids + p) != t) continue;
+        const float b0 = __ldg(bary + 3 * p), b1 = __ldg(bary + 3 * p + 1), b2 = __ldg(bary + 3 * p + 2);
+        if (b0 + b1 + b2 < 0.9f) continue;                                     // grad.cc:155 (also: id 0 = background)
+        const float d0 = __ldg(g_bary + 3 * p), d1 = __ldg(g_bary + 3 * p + 1), d2 = __ldg(g_bary + 3 * p + 2);
+        const float gx = d0 * dx0 + d1 * dx1 + d2 * dx2, gy = d0 * dy0 + d1 * dy1 + d2 * dy2;   // grad.cc:207-210
+        const float s0 = b0 / area, s1 = b1 / area, s2 = b2 / area;            // grad.cc:192-194
+        acc[0] += s0 * gx; acc[1] += s0 * gy;                                  // grad.cc:211-216
+        acc[2] += s1 * gx; acc[3] += s1 * gy;
+        acc[4] += s2 * gx; acc[5] += s2 * gy;
+      }
+  }
+  float* o = tri_grad + ((size_t)b * T + t) * 6;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) o[k] = acc[k];
+}
+
+__global__ void __launch_bounds__(128) raster_bwd_vtx_kernel(int T, int V, const int* __restrict__ vptr,
+                                                             const int* __restrict__ vent,
+                                                             const float* __restrict__ tri_grad, float* __restrict__ g_ndc) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+  if (v >= V) return;
+  float gx = 0.f, gy = 0.f;
+  const float* tg = tri_grad + (size_t)b * T * 6;
+  for (int e = __ldg(vptr + v); e < __ldg(vptr + v + 1); ++e) {
+    const int tc = __ldg(vent + e);   // triangle * 3 + corner
+    gx += tg[(size_t)tc * 2];
+    gy += tg[(size_t)tc * 2 + 1];
+  }
+  float* o = g_ndc + ((size_t)b * V + v) * 3;
+  o[0] = gx; o[1] = gy; o[2] = 0.f;   // no gradient through depth (grad.cc writes x, y only)
+}
+
+static size_t ru256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+}  // namespace smplb
+
+using namespace smplb;
+
+extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int32_t* triangles_host, int32_t T,
+                                     int32_t V) {
+  if (!out || (!triangles_host && T > 0)) return fail(SMPLB_E_INVALID_ARG, "smplb_mesh_create: null argument");
+  if (T < 0 || V <= 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_mesh_create: need T >= 0 and V > 0");
+  std::vector<int> vptr(V + 1, 0), vent((size_t)3 * T);
+  for (int i = 0; i < 3 * T; ++i) {
+    if (triangles_host[i] < 0 || triangles_host[i] >= V)
+      return fail(SMPLB_E_INVALID_ARG, "smplb_mesh_create: triangle vertex index out of range");
+    ++vptr[triangles_host[i] + 1];
+  }
+  for (int v = 0; v < V; ++v) vptr[v + 1] += vptr[v];
+  std::vector<int> fill(vptr.begin(), vptr.end() - 1);
+  for (int i = 0; i < 3 * T; ++i) vent[fill[triangles_host[i]]++] = i;   // i = triangle * 3 + corner, ascending
+  int prev = 0;
+  cudaGetDevice(&prev);
+  SMPLB_CUDA_CHECK(cudaSetDevice(device));
+  smplb_mesh* m = new smplb_mesh();
+  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr;
+  cudaError_t e = cudaMalloc((void**)&m->tri, sizeof(int) * (size_t)(3 * T > 0 ? 3 * T : 1));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&m->vptr, sizeof(int) * (size_t)(V + 1));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&m->vent, sizeof(int) * (size_t)(3 * T > 0 ? 3 * T : 1));
+  if (e == cudaSuccess && T > 0) e = cudaMemcpy(m->tri, triangles_host, sizeof(int) * 3 * (size_t)T, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(m->vptr, vptr.data(), sizeof(int) * (size_t)(V + 1), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && T > 0) e = cudaMemcpy(m->vent, vent.data(), sizeof(int) * 3 * (size_t)T, cudaMemcpyHostToDevice);
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent);
+    delete m;
+    return fail(SMPLB_E_CUDA, std::string("smplb_mesh_create: ") + cudaGetErrorString(e));
+  }
+  *out = m;
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_mesh_destroy(smplb_mesh* m) {
+  if (!m) return SMPLB_OK;
+  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent);
+  delete m;
+  return SMPLB_OK;
+}
+
+// keys [B*W*H] u64 | big_count (256 B) | big_list [B*T] int | tri_grad [B*T*6] float
+extern "C" size_t smplb_rasterize_workspace_bytes(const smplb_mesh* m, int32_t B, int32_t W, int32_t H) {
+  if (!m || B <= 0 || W <= 0 || H <= 0) return 0;
+  const size_t bt = (size_t)B * (size_t)(m->T > 0 ? m->T : 1);
+  return ru256((size_t)B * W * H * 8) + 256 + ru256(bt * 4) + ru256(bt * 6 * 4);
+}
+
+static int32_t raster_check(const char* who, const smplb_mesh* m, int32_t B, int32_t W, int32_t H, const void* ws,
+                            size_t ws_bytes) {
+  if (!m) return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": null mesh");
+  if (B < 0) return fail(SMPLB_E_BAD_SHAPE, std::string(who) + ": negative batch");
+  if (W <= 0 || H <= 0) return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": image width and height must be > 0");
+  if ((size_t)W * H > (1u << 30)) return fail(SMPLB_E_UNSUPPORTED, std::string(who) + ": image too large");
+  if (B > 65535) return fail(SMPLB_E_UNSUPPORTED, std::string(who) + ": at most 65535 images per call");
+  if (B > 0 && (!ws || ws_bytes < smplb_rasterize_workspace_bytes(m, B, W, H) || ((uintptr_t)ws & 255)))
+    return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": workspace missing, too small or not 256-byte aligned");
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_rasterize(const smplb_mesh* m, int32_t B, const float* ndc, int32_t W, int32_t H, float* bary,
+                                   int32_t* ids, float* zbuf, void* workspace, size_t workspace_bytes, void* stream) {
+  int32_t rc = raster_check("smplb_rasterize", m, B, W, H, workspace, workspace_bytes);
+  if (rc != SMPLB_OK || B == 0) return rc;
+  if (!ndc) return fail(SMPLB_E_INVALID_ARG, "smplb_rasterize: null vertices");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t npix = (size_t)B * W * H;
+  char* w = (char*)workspace;
+  unsigned long long* keys = (unsigned long long*)w;
+  int* big_count = (int*)(w + ru256(npix * 8));
+  int* big_list = (int*)(w + ru256(npix * 8) + 256);
+  raster_clear_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(keys, npix, big_count);
+  if (m->T > 0) {
+    raster_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
+    raster_big_kernel<<<592, 256, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
+  }
+  raster_resolve_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(B, m->T, m->V, W, H, ndc, m->tri, keys, bary, ids, zbuf);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_rasterize_backward(const smplb_mesh* m, int32_t B, const float* ndc, const float* bary,
+                                            const int32_t* ids, const float* g_bary, int32_t W, int32_t H, float* g_ndc,
+                                            void* workspace, size_t workspace_bytes, void* stream) {
+  int32_t rc = raster_check("smplb_rasterize_backward", m, B, W, H, workspace, workspace_bytes);
+  if (rc != SMPLB_OK || B == 0) return rc;
+  if (!ndc || !bary || !ids || !g_bary || !g_ndc) return fail(SMPLB_E_INVALID_ARG, "smplb_rasterize_backward: null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t npix = (size_t)B * W * H, bt = (size_t)B * (size_t)(m->T > 0 ? m->T : 1);
+  float* tri_grad = (float*)((char*)workspace + ru256(npix * 8) + 256 + ru256(bt * 4));
+  if (m->T > 0)
+    raster_bwd_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, bary, ids, g_bary, tri_grad);
+  raster_bwd_vtx_kernel<<<dim3((m->V + 127) / 128, B), 128, 0, st>>>(m->T, m->V, m->vptr, m->vent, tri_grad, g_ndc);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}

@@ -90,6 +90,14 @@ SYMBOLS = {
                                            C.c_void_p, C.c_void_p]),
     'smplb_fit_scratch_bytes': (C.c_size_t, [C.c_int32]),
     'smplb_fit_step': (C.c_int32, [C.c_void_p, C.POINTER(FitIO), C.c_void_p]),
+    'smplb_mesh_create': (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32, C.c_void_p, C.c_int32, C.c_int32]),
+    'smplb_mesh_destroy': (C.c_int32, [C.c_void_p]),
+    'smplb_rasterize_workspace_bytes': (C.c_size_t, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
+    'smplb_rasterize': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'smplb_rasterize_backward': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                             C.c_size_t, C.c_void_p]),
     'smplb_timing_begin': (C.c_int32, [C.c_int32]),
     'smplb_timing_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
     'smplb_adam_step': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -1,0 +1,99 @@
+"""Rasteriser bindings: smplb_mesh handle + batched rasterise / gradient (include/smplb200.h).
+torch tensors are carriers only; every pixel is computed by the kernels in csrc/raster.cu."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class Mesh:
+    """Triangle list [T,3] (int32, clockwise = front facing) of a mesh with V vertices, resident on `device`."""
+
+    def __init__(self, triangles, vertex_count, device=None):
+        self._h = None
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = torch.device('cuda', device) if isinstance(device, int) else torch.device(device)
+        tri = np.ascontiguousarray(np.asarray(triangles.cpu() if torch.is_tensor(triangles) else triangles),
+                                   dtype=np.int32).reshape(-1, 3)
+        self.T, self.V = int(tri.shape[0]), int(vertex_count)
+        h = C.c_void_p()
+        check(_lib.lib().smplb_mesh_create(C.byref(h), self.device.index or 0, tri.ctypes.data_as(C.c_void_p),
+                                           self.T, self.V))
+        self._h = h
+        self.triangles = torch.from_numpy(tri.astype(np.int64)).to(self.device)
+        self._ws = None
+
+    def close(self):
+        if self._h is not None:
+            _lib.lib().smplb_mesh_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _workspace(self, B, W, H):
+        need = _lib.lib().smplb_rasterize_workspace_bytes(self._h, B, W, H)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(max(need, 256), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def rasterize(self, ndc, W, H):
+        """ndc [B,V,3] -> (bary [B,H,W,3] f32, ids [B,H,W] i32, z [B,H,W] f32)."""
+        ndc = ndc.to(self.device, torch.float32).contiguous()
+        if ndc.dim() != 3 or ndc.shape[1] != self.V or ndc.shape[2] != 3:
+            raise ValueError('ndc must be [B,%d,3]; got %s' % (self.V, tuple(ndc.shape)))
+        B = ndc.shape[0]
+        bary = torch.empty((B, H, W, 3), dtype=torch.float32, device=self.device)
+        ids = torch.empty((B, H, W), dtype=torch.int32, device=self.device)
+        z = torch.empty((B, H, W), dtype=torch.float32, device=self.device)
+        ws = self._workspace(B, W, H)
+        with torch.cuda.device(self.device):
+            st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            check(_lib.lib().smplb_rasterize(self._h, B, _ptr(ndc), W, H, _ptr(bary), _ptr(ids), _ptr(z), _ptr(ws),
+                                             ws.numel(), st))
+        return bary, ids, z
+
+    def rasterize_backward(self, ndc, bary, ids, g_bary, W, H):
+        ndc = ndc.to(self.device, torch.float32).contiguous()
+        B = ndc.shape[0]
+        g = torch.empty_like(ndc)
+        ws = self._workspace(B, W, H)
+        with torch.cuda.device(self.device):
+            st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            check(_lib.lib().smplb_rasterize_backward(self._h, B, _ptr(ndc), _ptr(bary.contiguous()),
+                                                      _ptr(ids.contiguous()), _ptr(g_bary.contiguous().float()), W, H,
+                                                      _ptr(g), _ptr(ws), ws.numel(), st))
+        return g
+
+
+class _Rasterize(torch.autograd.Function):
+    """RasterizeTriangles with the registered gradient (rasterize_triangles.py:181-188): gradients flow through the
+    barycentrics only; ids and z are not differentiable."""
+
+    @staticmethod
+    def forward(ctx, ndc, mesh, W, H):
+        bary, ids, z = mesh.rasterize(ndc, W, H)
+        ctx.mesh, ctx.W, ctx.H = mesh, W, H
+        ctx.save_for_backward(ndc, bary, ids)
+        ctx.mark_non_differentiable(ids, z)
+        return bary, ids, z
+
+    @staticmethod
+    def backward(ctx, g_bary, g_ids, g_z):
+        ndc, bary, ids = ctx.saved_tensors
+        return ctx.mesh.rasterize_backward(ndc, bary, ids, g_bary, ctx.W, ctx.H), None, None, None
+
+
+def rasterize_ndc(ndc, mesh, W, H):
+    return _Rasterize.apply(ndc, mesh, W, H)

@@ -225,6 +225,28 @@ typedef struct {
 size_t smplb_fit_scratch_bytes(int32_t B);
 int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, void* stream);
 
+/* ---- Triangle rasteriser: deps/tf_mesh_renderer ---------------------------------------
+ * Replaces the custom TF ops RasterizeTriangles (kernels/rasterize_triangles_op.cc:26-147, implementation
+ * kernels/rasterize_triangles_impl.cc:75-155) and RasterizeTrianglesGrad (kernels/rasterize_triangles_grad.cc:
+ * 52-224), which the reference loads with tf.load_op_library (rasterize_triangles.py:21-23) and calls once per
+ * image through tf.map_fn (:98-117).  Here one call rasterises a whole batch.
+ * A mesh handle owns the device copy of the triangle list ([T,3] vertex ids, clockwise = front facing) and the
+ * vertex -> corner table of the gradient; it is immutable, so any number of streams may share it. */
+typedef struct smplb_mesh smplb_mesh;
+int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int32_t* triangles_host, int32_t T,
+                          int32_t V);
+int32_t smplb_mesh_destroy(smplb_mesh* m);
+size_t smplb_rasterize_workspace_bytes(const smplb_mesh* m, int32_t B, int32_t W, int32_t H);
+/* ndc [B,V,3] normalised device coordinates (device) -> bary [B,H,W,3], ids [B,H,W] (int32), zbuf [B,H,W];
+ * any output may be NULL.  Uncovered pixels: bary 0, id 0, z 1 (rasterize_triangles_op.cc:121-125).
+ * Bit-identical to the reference's C++ for finite depths. */
+int32_t smplb_rasterize(const smplb_mesh* m, int32_t B, const float* ndc, int32_t W, int32_t H, float* bary,
+                        int32_t* ids, float* zbuf, void* workspace, size_t workspace_bytes, void* stream);
+/* g_bary [B,H,W,3] -> g_ndc [B,V,3] (z component 0), from the forward's bary / ids. */
+int32_t smplb_rasterize_backward(const smplb_mesh* m, int32_t B, const float* ndc, const float* bary,
+                                 const int32_t* ids, const float* g_bary, int32_t W, int32_t H, float* g_ndc,
+                                 void* workspace, size_t workspace_bytes, void* stream);
+
 /* Measurement aid (no reference counterpart): while enabled, every smplb_forward on this host thread
  * records CUDA events on its stream around pose_prep / blend GEMM / skinning / keypoints.
  * smplb_timing_end synchronises those events and writes ms_out[call][4] = {prep, blend, skin, keypoints}
