@@ -280,6 +280,147 @@ def run_sweep(args, rank, local_rank, world, dist):
         dist.destroy_process_group()
 
 
+def uv_sphere_mesh(n_lon=82, n_ring=84):
+    """Closed UV-sphere with exactly SMPL's counts: 82*84 + 2 = 6890 vertices, 82*83*2 + 2*82 = 13776 triangles."""
+    th = np.pi * (np.arange(n_ring) + 1) / (n_ring + 1)
+    ph = 2 * np.pi * np.arange(n_lon) / n_lon
+    ring = np.stack([np.outer(np.sin(th), np.cos(ph)), np.outer(np.cos(th), np.ones(n_lon)),
+                     np.outer(np.sin(th), np.sin(ph))], -1).reshape(-1, 3)
+    v = np.concatenate([ring, [[0, 1, 0]], [[0, -1, 0]]]).astype(np.float32)
+    idx = lambda r, c: r * n_lon + (c % n_lon)
+    tri = []
+    for r in range(n_ring - 1):
+        for c in range(n_lon):
+            tri += [[idx(r, c), idx(r + 1, c), idx(r, c + 1)], [idx(r, c + 1), idx(r + 1, c), idx(r + 1, c + 1)]]
+    top, bot = n_lon * n_ring, n_lon * n_ring + 1
+    for c in range(n_lon):
+        tri += [[top, idx(0, c), idx(0, c + 1)], [bot, idx(n_ring - 1, c + 1), idx(n_ring - 1, c)]]
+    return v, np.asarray(tri, np.int32)
+
+
+def raster_inputs(B, seed):
+    """Body-sized ellipsoids (SMPL vertex/triangle counts) under random rotations, as NDC [B,6890,3]."""
+    v, tri = uv_sphere_mesh()
+    rng = np.random.default_rng(seed)
+    ang = rng.uniform(0, 2 * np.pi, size=B)
+    c, s = np.cos(ang), np.sin(ang)
+    R = np.zeros((B, 3, 3), np.float32)
+    R[:, 0, 0], R[:, 0, 2], R[:, 1, 1], R[:, 2, 0], R[:, 2, 2] = c, s, 1, -s, c
+    body = v * np.array([0.22, 0.75, 0.15], np.float32)
+    ndc = np.einsum('bij,vj->bvi', R, body) + rng.uniform(-0.15, 0.15, size=(B, 1, 3)).astype(np.float32)
+    ndc[:, :, 2] *= 0.5
+    return ndc.astype(np.float32), tri
+
+
+def run_raster(args, rank, local_rank, world, dist):
+    """batched triangle rasterisation of SMPL-sized meshes (6890 vertices, 13776 triangles) at the
+    reference's 320x240 (config.py img dims): images/s, with the reference's own C++ rasteriser (oracle/_ref, one
+    host thread per image as tf.map_fn would give at best) timed beside it."""
+    from smplb200.raster import Mesh
+    dev = torch.device('cuda', local_rank)
+    W, H = 320, 240
+    B = args.batch if args.batch != 65536 else 1024
+    ndc_h, tri = raster_inputs(min(B, 64), 1000 + rank)
+    ndc = torch.from_numpy(ndc_h).to(dev).repeat((B + ndc_h.shape[0] - 1) // ndc_h.shape[0], 1, 1)[:B].contiguous()
+    mesh = Mesh(tri, ndc.shape[1], local_rank)
+    g_bary = torch.randn((B, H, W, 3), device=dev)
+
+    def sync():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        for _ in range(args.warmup):
+            fn()
+        sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        sync()
+        t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    out = {}
+
+    def fwd():
+        out['r'] = mesh.rasterize(ndc, W, H)
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_f = timed(fwd, args.steps)
+    bary, ids, z = out['r']
+    ms_b = timed(lambda: mesh.rasterize_backward(ndc, bary, ids, g_bary, W, H), args.steps)
+    # e2e: host vertices in, host barycentrics/ids out
+    hv = ndc.cpu().pin_memory()
+    hb = torch.empty((B, H, W, 3), dtype=torch.float32).pin_memory()
+    hi = torch.empty((B, H, W), dtype=torch.int32).pin_memory()
+
+    def e2e():
+        d = hv.to(dev, non_blocking=True)
+        b_, i_, _ = mesh.rasterize(d, W, H)
+        hb.copy_(b_, non_blocking=True)
+        hi.copy_(i_, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e()
+    sync()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e()
+    el = (time.perf_counter() - t0) / args.e2e_steps
+    sampler.stop_flag = True
+    sampler.join()
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    out_bytes = B * W * H * 20 + B * 6890 * 12         # bary + ids + z written, vertices read
+    line = {'metric': 'raster_images_per_s', 'value': world * B / (ms_f * 1e-3), 'unit': 'images/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_f, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32 + 16.16 fixed point', 'data': 'synthetic',
+            'config': {'workload': 'rasterise B=%d SMPL-sized meshes (6890 vertices, 13776 triangles, UV-ellipsoids) at '
+                                   '320x240 per GPU per step -> barycentrics, triangle ids, depth' % B},
+            'clocks': sampler.summary(), 'gpu_launches': 4 * args.steps,
+            'backward_ms_per_step': ms_b, 'backward_images_per_s': world * B / (ms_b * 1e-3),
+            'covered_fraction': float((bary.sum(-1) > 0.5).float().mean()),
+            'roofline': {'bound': 'hbm', 'kernel': 'raster_clear + raster_tri + raster_big + raster_resolve (whole step)',
+                         'achieved': out_bytes / (ms_f * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
+                         'frac': out_bytes / (ms_f * 1e-3) / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
+                         'algorithmic_bytes_per_launch': out_bytes},
+            'e2e': {'value': world * B / el, 'unit': 'images/s', 'h2d_bytes_per_step': hv.numel() * 4,
+                    'd2h_bytes_per_step': hb.numel() * 4 + hi.numel() * 4, 'steps': args.e2e_steps}}
+    if not args.no_cpu_baseline:
+        line['cpu_baseline'] = raster_cpu_rate(ndc_h, tri, W, H, args.cpu_seconds)
+    print(json.dumps(line), flush=True)
+
+
+def raster_cpu_rate(ndc_h, tri, W, H, seconds):
+    """The reference's own C++ rasteriser (oracle/_ref) when it was built, else the C restatement; one image per
+    host thread (ctypes releases the GIL)."""
+    import subprocess
+    from concurrent.futures import ThreadPoolExecutor
+    subprocess.check_call(['make', '-s', '-C', os.path.join(ROOT, 'oracle'), 'port'])
+    from oracle import raster as orc            # timed CPU baseline only
+    kind = 'reference' if orc.ref_available() else 'port'
+    fn = orc.forward_ref if kind == 'reference' else orc.forward_port
+    cores = os.cpu_count() or 1
+    n, t0 = 0, time.perf_counter()
+    with ThreadPoolExecutor(cores) as ex:
+        while time.perf_counter() - t0 < seconds:
+            list(ex.map(lambda i: fn(ndc_h[i % len(ndc_h)], tri, W, H), range(4 * cores)))
+            n += 4 * cores
+    el = time.perf_counter() - t0
+    return {'value': n / el, 'unit': 'images/s', 'cores': cores, 'kind': kind,
+            'sample': '%d images of the same workload in %.1f s (%s)' % (
+                n, el, 'rasterize_triangles_impl.cc compiled from the reference' if kind == 'reference'
+                else 'oracle/raster_port.c')}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -293,7 +434,7 @@ def main():
     ap.add_argument('--cpu-seconds', type=float, default=12.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
-    ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep'],
+    ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep', 'raster'],
                     help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
     ap.add_argument('--graph', action='store_true', help='fit mode: replay the step from a CUDA graph')
     args = ap.parse_args()
@@ -321,6 +462,12 @@ def main():
         return
     if args.mode == 'sweep':
         run_sweep(args, rank, local_rank, world, dist)
+        return
+    if args.mode == 'raster':
+        run_raster(args, rank, local_rank, world, dist)
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
         return
     dev = torch.device('cuda', local_rank)
     dd = syn.make_synthetic_smpl(0)
