@@ -1,0 +1,211 @@
+// Per-sample operators either side of the SMPL path:
+//   N2  rotate_global_pose / add_axis_angle_rotations  deps/pose_3d/utils.py:152-199  (GT pose pre-processing,
+//       called at pose_model_3d.py:371-372 right before SMPL)
+//   N3  camera-angle (ray) loss + camera regularisers  deps/pose_3d/pose_model_3d.py:256-292 with
+//       utils.get_2d_points_in_3d (utils.py:75-89): value and gradient wrt camera position / rotation / focal.
+// Latency-class kernels: thread = sample, a few hundred bytes each; the loss sums are reduced in a fixed
+// order (block tree, then one finishing block) so the scalars are run-to-run identical.
+#include "common.cuh"
+#include "geom.cuh"
+
+namespace smplb {
+
+// utils.py:170-199: rotation c*n equivalent to applying rv2 then rv1 (half-angle / quaternion product).
+__device__ __forceinline__ void add_axis_angle(const float r1[3], const float r2[3], float out[3]) {
+  const float a = sqrtf(r1[0] * r1[0] + r1[1] * r1[1] + r1[2] * r1[2]);
+  const float b = sqrtf(r2[0] * r2[0] + r2[1] * r2[1] + r2[2] * r2[2]);
+  if (b == 0.0f) { out[0] = r1[0]; out[1] = r1[1]; out[2] = r1[2]; return; }   // :198 (applied last, wins)
+  if (a == 0.0f) { out[0] = r2[0]; out[1] = r2[1]; out[2] = r2[2]; return; }   // :197
+  const float l[3] = {r1[0] / a, r1[1] / a, r1[2] / a}, m[3] = {r2[0] / b, r2[1] / b, r2[2] / b};
+  float sa, ca, sb, cb;
+  sincosf(a * 0.5f, &sa, &ca);
+  sincosf(b * 0.5f, &sb, &cb);
+  const float ldm = l[0] * m[0] + l[1] * m[1] + l[2] * m[2];
+  const float cos_half_c = ca * cb - sa * sb * ldm;                                       // :186-188
+  const float cr[3] = {l[1] * m[2] - l[2] * m[1], l[2] * m[0] - l[0] * m[2], l[0] * m[1] - l[1] * m[0]};
+  const float half_c = acosf(cos_half_c);                                                 // :193
+  const float sh = sinf(half_c);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float sn = sa * cb * l[k] + (ca * sb * m[k] + sa * sb * cr[k]);                 // :189-191
+    out[k] = sn / sh * half_c * 2.0f;                                                     // :194-195
+  }
+}
+
+__global__ void add_axis_angle_kernel(int N, const float* __restrict__ rv1, const float* __restrict__ rv2,
+                                      float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const float a[3] = {rv1[3 * i], rv1[3 * i + 1], rv1[3 * i + 2]}, b[3] = {rv2[3 * i], rv2[3 * i + 1], rv2[3 * i + 2]};
+  float o[3];
+  add_axis_angle(a, b, o);
+  out[3 * i] = o[0]; out[3 * i + 1] = o[1]; out[3 * i + 2] = o[2];
+}
+
+// utils.py:152-167: global rotation <- (turn_y(zrot + pi/2) o turn_x(-pi/2)) o theta[:3]; the other 69 copied.
+__global__ void rotate_global_pose_kernel(int B, const float* __restrict__ thetas, const float* __restrict__ zrot,
+                                          float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * 24) return;
+  const int b = i / 24, j = i % 24;
+  const float* t = thetas + (size_t)b * 72 + 3 * j;
+  float o[3] = {t[0], t[1], t[2]};
+  if (j == 0) {
+    const float tx[3] = {-1.5707963267948966f, 0.f, 0.f};
+    const float ty[3] = {0.f, zrot[b] + 1.5707963267948966f, 0.f};
+    float both[3];
+    add_axis_angle(ty, tx, both);
+    add_axis_angle(both, t, o);
+  }
+  float* d = out + (size_t)b * 72 + 3 * j;
+  d[0] = o[0]; d[1] = o[1]; d[2] = o[2];
+}
+
+// ---- N3 ---------------------------------------------------------------------------------------------------
+// per sample: sum_j angle^2 (pose_model_3d.py:260-268), the three limit terms (:276-281), the rotation-norm term
+// (:285-289); optional gradients with the global scales already applied (scale / element count).
+__global__ void __launch_bounds__(128) cam_losses_kernel(int B, const float* __restrict__ j3d, const float* __restrict__ p2d,
+                                                         const float* __restrict__ cpos, const float* __restrict__ crot,
+                                                         const float* __restrict__ cf, const float* __restrict__ f_raw,
+                                                         smplb_camcfg cfg, float w_angle, float w_neg, float w_rot,
+                                                         float* __restrict__ partial /*[gridDim][3]*/,
+                                                         float* __restrict__ g_pos, float* __restrict__ g_rot,
+                                                         float* __restrict__ g_f, float* __restrict__ g_fraw) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  float s_ang = 0.f, s_neg = 0.f, s_rot = 0.f;
+  if (b < B) {
+    const float ax = crot[3 * b], ay = crot[3 * b + 1], az = crot[3 * b + 2];
+    const float c[3] = {cpos[3 * b], cpos[3 * b + 1], cpos[3 * b + 2]};
+    const float f = cf[b];
+    float R[9], gR[9], gc[3] = {0.f, 0.f, 0.f}, gf = 0.f;
+    rodrigues_cam(ax, ay, az, R);
+#pragma unroll
+    for (int e = 0; e < 9; ++e) gR[e] = 0.f;
+    for (int j = 0; j < 24; ++j) {
+      const float* p = j3d + ((size_t)b * 24 + j) * 3;
+      const float d[3] = {p[0] - c[0], p[1] - c[1], p[2] - c[2]};                       // :260
+      const float nd = sqrtf(fmaxf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], 1e-12f));   // l2_normalize eps
+      const float u[3] = {d[0] / nd, d[1] / nd, d[2] / nd};
+      const float* q2 = p2d + ((size_t)b * 24 + j) * 2;
+      const float q[3] = {cfg.ss * (q2[0] - 0.5f * cfg.img_w) / cfg.img_h,               // utils.py:77
+                          cfg.ss * (q2[1] - 0.5f * cfg.img_h) / cfg.img_h, f};
+      float rq[3];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) rq[r] = R[3 * r] * q[0] + R[3 * r + 1] * q[1] + R[3 * r + 2] * q[2];   // :84-85
+      const float nq = sqrtf(fmaxf(rq[0] * rq[0] + rq[1] * rq[1] + rq[2] * rq[2], 1e-12f));
+      const float w[3] = {rq[0] / nq, rq[1] / nq, rq[2] / nq};
+      const float dot = u[0] * w[0] + u[1] * w[1] + u[2] * w[2];                         // :265
+      const float lo = -1.0f + 1e-6f, hi = 1.0f - 1e-6f;
+      const float dc = fminf(fmaxf(dot, lo), hi);                                        // :267
+      const float ang = acosf(dc);                                                       // :268
+      s_ang += ang * ang;
+      if (g_pos && dot >= lo && dot <= hi) {
+        const float gd = -2.0f * w_angle * ang * rsqrtf(1.0f - dc * dc);
+        // through u = d / |d|
+        const float ugw = u[0] * w[0] + u[1] * w[1] + u[2] * w[2];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) gc[r] -= gd * (w[r] - u[r] * ugw) / nd;
+        // through w = Rq / |Rq|
+        float grq[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) grq[r] = gd * (u[r] - w[r] * ugw) / nq;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+#pragma unroll
+          for (int k = 0; k < 3; ++k) gR[3 * r + k] += grq[r] * q[k];
+          gf += R[3 * r + 2] * grq[r];
+        }
+      }
+    }
+    // camera regularisers
+    const float lim0 = -c[2] - 0.3f, lim1 = c[2] + 10.0f;                                // :276-278
+    float gz = 0.f, gfr = 0.f;
+    if (lim0 < 0.f) { s_neg += lim0 * lim0; gz -= 2.0f * w_neg * lim0; }
+    if (lim1 < 0.f) { s_neg += lim1 * lim1; gz += 2.0f * w_neg * lim1; }
+    if (f_raw) {
+      const float l2 = f_raw[b];
+      if (l2 < 0.f) { s_neg += l2 * l2; gfr = 2.0f * w_neg * l2; }
+    }
+    const float nr = sqrtf(ax * ax + ay * ay + az * az);                                 // :285-286
+    float grn = 0.f;
+    if (nr > 0.39269908169872414f) { s_rot += nr * nr; grn = 2.0f * w_rot * nr; }        // pi * 0.125, :288
+    if (g_pos) {
+      g_pos[3 * b] = gc[0]; g_pos[3 * b + 1] = gc[1]; g_pos[3 * b + 2] = gc[2] + gz;
+      float gr[3];
+      rodrigues_cam_bwd(ax, ay, az, gR, gr);
+      const float inv = nr > 0.f ? grn / nr : 0.f;
+      g_rot[3 * b] = gr[0] + inv * ax; g_rot[3 * b + 1] = gr[1] + inv * ay; g_rot[3 * b + 2] = gr[2] + inv * az;
+      if (g_f) g_f[b] = gf;
+      if (g_fraw) g_fraw[b] = gfr;
+    }
+  }
+  __shared__ float red[3][128];
+  red[0][threadIdx.x] = s_ang; red[1][threadIdx.x] = s_neg; red[2][threadIdx.x] = s_rot;
+  __syncthreads();
+  for (int o = 64; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o)
+      for (int k = 0; k < 3; ++k) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x < 3) partial[blockIdx.x * 3 + threadIdx.x] = red[threadIdx.x][0];
+}
+
+// loss_out = {cam_angle_loss, cam_neg_loss, cam_rot_loss, sum}
+__global__ void cam_losses_finish_kernel(int nblocks, const float* __restrict__ partial, float w_angle, float w_neg,
+                                         float w_rot, float* __restrict__ loss_out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  float s[3] = {0.f, 0.f, 0.f};
+  for (int i = 0; i < nblocks; ++i)
+    for (int k = 0; k < 3; ++k) s[k] += partial[i * 3 + k];
+  loss_out[0] = w_angle * s[0];
+  loss_out[1] = w_neg * s[1];
+  loss_out[2] = w_rot * s[2];
+  loss_out[3] = loss_out[0] + loss_out[1] + loss_out[2];
+}
+
+}  // namespace smplb
+
+using namespace smplb;
+
+extern "C" int32_t smplb_add_axis_angle(int32_t N, const float* rv1, const float* rv2, float* out, void* stream) {
+  if (N < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_add_axis_angle: negative count");
+  if (N == 0) return SMPLB_OK;
+  if (!rv1 || !rv2 || !out) return fail(SMPLB_E_INVALID_ARG, "smplb_add_axis_angle: null pointer");
+  add_axis_angle_kernel<<<(N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(N, rv1, rv2, out);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+extern "C" int32_t smplb_rotate_global_pose(int32_t B, const float* thetas, const float* zrot, float* out, void* stream) {
+  if (B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_rotate_global_pose: negative batch");
+  if (B == 0) return SMPLB_OK;
+  if (!thetas || !zrot || !out) return fail(SMPLB_E_INVALID_ARG, "smplb_rotate_global_pose: null pointer");
+  rotate_global_pose_kernel<<<(B * 24 + 127) / 128, 128, 0, (cudaStream_t)stream>>>(B, thetas, zrot, out);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+extern "C" size_t smplb_cam_losses_scratch_bytes(int32_t B) { return (size_t)((B > 0 ? B : 0) + 127) / 128 * 3 * sizeof(float) + 16; }
+
+extern "C" int32_t smplb_cam_losses(int32_t B, const float* gt_joints3d, const float* gt_joints2d, const float* cam_pos,
+                                    const float* cam_rot, const float* cam_f, const float* f_raw,
+                                    const smplb_camcfg* cfg, float angle_scale, float* loss_out, float* g_cam_pos,
+                                    float* g_cam_rot, float* g_cam_f, float* g_f_raw, void* scratch, void* stream) {
+  if (B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_cam_losses: negative batch");
+  if (!cfg || !loss_out) return fail(SMPLB_E_INVALID_ARG, "smplb_cam_losses: null cfg or loss_out");
+  if (B == 0) return SMPLB_OK;
+  if (!gt_joints3d || !gt_joints2d || !cam_pos || !cam_rot || !cam_f || !scratch)
+    return fail(SMPLB_E_INVALID_ARG, "smplb_cam_losses: null pointer");
+  if ((g_cam_pos == nullptr) != (g_cam_rot == nullptr))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_cam_losses: g_cam_pos and g_cam_rot go together");
+  const int nb = (B + 127) / 128;
+  // tf.losses.mean_squared_error: weight * mean over all elements (B*24 angles, B*3 limits, B norms)
+  const float w_angle = angle_scale / (float)((long long)B * 24), w_neg = 1.0f / (float)((long long)B * 3),
+              w_rot = 10.0f / (float)B;
+  cudaStream_t st = (cudaStream_t)stream;
+  cam_losses_kernel<<<nb, 128, 0, st>>>(B, gt_joints3d, gt_joints2d, cam_pos, cam_rot, cam_f, f_raw, *cfg, w_angle, w_neg,
+                                       w_rot, (float*)scratch, g_cam_pos, g_cam_rot, g_cam_f, g_f_raw);
+  cam_losses_finish_kernel<<<1, 32, 0, st>>>(nb, (const float*)scratch, w_angle, w_neg, w_rot, loss_out);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}

@@ -98,6 +98,12 @@ SYMBOLS = {
     'smplb_rasterize_backward': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                              C.c_size_t, C.c_void_p]),
+    'smplb_add_axis_angle': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'smplb_rotate_global_pose': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'smplb_cam_losses_scratch_bytes': (C.c_size_t, [C.c_int32]),
+    'smplb_cam_losses': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.POINTER(CamCfg), C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_timing_begin': (C.c_int32, [C.c_int32]),
     'smplb_timing_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
     'smplb_adam_step': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

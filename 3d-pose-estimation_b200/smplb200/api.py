@@ -284,3 +284,51 @@ def adam_step(x, g, m, v, t, lr=2e-4, beta1=0.9, beta2=0.999, eps=1e-8):
         check(_lib.lib().smplb_adam_step(x.numel(), _ptr(x), _ptr(g), _ptr(m), _ptr(v), int(t),
                                          lr, beta1, beta2, eps, _stream(dev)))
     return x
+
+
+# -- pose pre-processing and the camera losses ------------------------------------
+
+def add_axis_angle_rotations(rv1, rv2):
+    """deps/pose_3d/utils.py:170-199: [N,3], [N,3] -> [N,3]."""
+    dev = _cuda_dev(rv1)
+    rv1, rv2 = _dev_f32(rv1, dev), _dev_f32(rv2, dev)
+    out = torch.empty_like(rv1)
+    with torch.cuda.device(dev):
+        check(_lib.lib().smplb_add_axis_angle(rv1.shape[0], _ptr(rv1), _ptr(rv2), _ptr(out), _stream(dev)))
+    return out
+
+
+def rotate_global_pose(thetas, zrot):
+    """deps/pose_3d/utils.py:152-167: thetas [B,72], zrot [B] -> [B,72]."""
+    dev = _cuda_dev(thetas)
+    thetas, zrot = _dev_f32(thetas, dev), _dev_f32(zrot, dev)
+    out = torch.empty_like(thetas)
+    with torch.cuda.device(dev):
+        check(_lib.lib().smplb_rotate_global_pose(thetas.shape[0], _ptr(thetas), _ptr(zrot), _ptr(out), _stream(dev)))
+    return out
+
+
+def cam_losses(gt_joints3d, gt_joints2d, cam_pos, cam_rot, cam_f, f_raw=None, angle_scale=10.0, cam_cfg=None,
+               want_grad=True):
+    """pose_model_3d.py:256-292.  Returns (loss[4] = angle, neg, rot, sum; grads dict or None)."""
+    dev = _cuda_dev(gt_joints3d)
+    B = gt_joints3d.shape[0]
+    j3, j2 = _dev_f32(gt_joints3d, dev, (B, NJ, 3)), _dev_f32(gt_joints2d, dev, (B, NJ, 2))
+    cp, cr, cf = _dev_f32(cam_pos, dev, (B, 3)), _dev_f32(cam_rot, dev, (B, 3)), _dev_f32(cam_f, dev, (B,))
+    fr = None if f_raw is None else _dev_f32(f_raw, dev, (B,))
+    cfg = dict(DEFAULT_CAM)
+    cfg.update(cam_cfg or {})
+    loss = torch.empty(4, dtype=torch.float32, device=dev)
+    g = None
+    if want_grad:
+        g = {'cam_pos': torch.empty_like(cp), 'cam_rot': torch.empty_like(cr), 'cam_f': torch.empty_like(cf),
+             'f_raw': None if fr is None else torch.empty_like(fr)}
+    scratch = torch.empty(max(int(_lib.lib().smplb_cam_losses_scratch_bytes(B)), 16), dtype=torch.uint8, device=dev)
+    cc = CamCfg(**cfg)
+    with torch.cuda.device(dev):
+        check(_lib.lib().smplb_cam_losses(B, _ptr(j3), _ptr(j2), _ptr(cp), _ptr(cr), _ptr(cf), _ptr(fr), C.byref(cc),
+                                          float(angle_scale), _ptr(loss), _ptr(g['cam_pos']) if g else None,
+                                          _ptr(g['cam_rot']) if g else None, _ptr(g['cam_f']) if g else None,
+                                          _ptr(g['f_raw']) if g and fr is not None else None, _ptr(scratch),
+                                          _stream(dev)))
+    return loss, g

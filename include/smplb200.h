@@ -247,6 +247,24 @@ int32_t smplb_rasterize_backward(const smplb_mesh* m, int32_t B, const float* nd
                                  const int32_t* ids, const float* g_bary, int32_t W, int32_t H, float* g_ndc,
                                  void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- Per-sample operators either side of the path ---------------------------------
+ * add_axis_angle_rotations (deps/pose_3d/utils.py:170-199): rv1, rv2 [N,3] -> axis-angle of "rv2 then rv1". */
+int32_t smplb_add_axis_angle(int32_t N, const float* rv1, const float* rv2, float* out, void* stream);
+/* rotate_global_pose (deps/pose_3d/utils.py:152-167): thetas [B,72], zrot [B] -> thetas with the SURREAL global
+ * rotation re-expressed for a y-up body (called on GT poses at pose_model_3d.py:371-372). */
+int32_t smplb_rotate_global_pose(int32_t B, const float* thetas, const float* zrot, float* out, void* stream);
+/* Camera-angle (ray) loss and camera regularisers (deps/pose_3d/pose_model_3d.py:256-292,
+ * utils.get_2d_points_in_3d utils.py:75-89).  gt_joints3d [B,24,3], gt_joints2d [B,24,2] pixels (already
+ * flipped, :196-197), cam_pos/cam_rot [B,3], cam_f [B] (focal used for the rays), f_raw [B] nullable (the raw
+ * focal output the limit term sees, outputs[:,78]).  loss_out (device, 4 floats) = {cam_angle_loss,
+ * cam_neg_loss, cam_rot_loss, their sum}; angle_scale = config.cam_angle_loss_scale (10).  Gradients of the sum
+ * (nullable, pos and rot together): g_cam_pos/g_cam_rot [B,3], g_cam_f/g_f_raw [B]. */
+size_t smplb_cam_losses_scratch_bytes(int32_t B);
+int32_t smplb_cam_losses(int32_t B, const float* gt_joints3d, const float* gt_joints2d, const float* cam_pos,
+                         const float* cam_rot, const float* cam_f, const float* f_raw, const smplb_camcfg* cfg,
+                         float angle_scale, float* loss_out, float* g_cam_pos, float* g_cam_rot, float* g_cam_f,
+                         float* g_f_raw, void* scratch, void* stream);
+
 /* Measurement aid (no reference counterpart): while enabled, every smplb_forward on this host thread
  * records CUDA events on its stream around pose_prep / blend GEMM / skinning / keypoints.
  * smplb_timing_end synchronises those events and writes ms_out[call][4] = {prep, blend, skin, keypoints}

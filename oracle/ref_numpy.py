@@ -27,7 +27,7 @@ import numpy as np
 CFG = SimpleNamespace(
     n_joints_smpl=24, input_img_size=(240, 320), fl=0.05, ss=0.024,
     total_loss_scale=1.0, mesh_loss_scale=1.0, joint_loss_scale=2.0,
-    reproj_loss_scale=1.0 * 0.024, cam_loss_scale=1.0 / (400 * 24))
+    reproj_loss_scale=1.0 * 0.024, cam_loss_scale=1.0 / (400 * 24), cam_angle_loss_scale=10.0)
 
 
 def load_model(pkl, joint_type='cocoplus', dtype=np.float32):
@@ -305,3 +305,46 @@ def rotate_global_pose(thetas, zrot):
     turn_both = add_axis_angle_rotations(turn_y_batch, turn_x_batch)
     g = add_axis_angle_rotations(turn_both, thetas[:, :3])
     return np.concatenate([g, thetas[:, 3:]], axis=1)
+
+
+# ---- N3 "next" row: camera-angle (ray) loss and camera regularisers (deps/pose_3d/pose_model_3d.py:256-294) ----
+
+def l2_normalize(x, axis, eps=1e-12):
+    """tf.nn.l2_normalize: x * rsqrt(max(sum(x^2), eps))."""
+    return x / np.sqrt(np.maximum(np.sum(x * x, axis=axis, keepdims=True), x.dtype.type(eps)))
+
+
+def get_2d_points_in_3d(points_2d, cam_rot, cam_f, img_w=320.0, img_h=240.0, ss=CFG.ss):
+    """deps/pose_3d/utils.py:75-89: pixels -> points on the camera image plane, rotated into world axes."""
+    dt = points_2d.dtype
+    img_dim = np.array([img_w, img_h], dtype=dt)
+    rescaled_2d = dt.type(ss) * (points_2d - img_dim / 2) / img_dim[1]                   # :77
+    fl = np.tile(np.reshape(cam_f, [-1, 1, 1]), [1, points_2d.shape[1], 1])             # :78-79
+    p = np.concatenate([rescaled_2d, fl], axis=2)                                        # :80
+    R = rodrigues_batch(cam_rot)[:, None]                                                # :81-83
+    return np.matmul(R, p[..., None])[..., 0]                                            # :84-86
+
+
+def cam_angle_loss(gt_joints3d, gt_joints2d, cam_pos, cam_rot, cam_f, img_w=320.0, img_h=240.0, ss=CFG.ss,
+                   scale=CFG.cam_angle_loss_scale):
+    """pose_model_3d.py:256-270."""
+    dt = gt_joints3d.dtype
+    v3 = l2_normalize(gt_joints3d - cam_pos[:, None, :], 2)                              # :260-261
+    v2 = l2_normalize(get_2d_points_in_3d(gt_joints2d, cam_rot, cam_f, img_w, img_h, ss), 2)   # :262-264
+    dot = np.sum(v3 * v2, axis=2)                                                        # :265
+    dot = np.clip(dot, dt.type(-1.0 + 1e-6), dt.type(1.0 - 1e-6))                        # :267
+    ang = np.arccos(dot)                                                                 # :268
+    return mse(np.zeros_like(ang), ang, scale)                                           # :269-271
+
+
+def cam_reg_losses(cam_pos, cam_rot, f_raw):
+    """pose_model_3d.py:273-291: (cam_neg_loss, cam_rot_loss); outputs[:,74] = camera z, outputs[:,78] = raw f."""
+    dt = cam_pos.dtype
+    lim = np.stack([cam_pos[:, 2], cam_pos[:, 2], f_raw], axis=1)                        # :276
+    lim = lim * np.array([-1.0, 1.0, 1.0], dtype=dt)[None] + np.array([-0.3, 10.0, 0.0], dtype=dt)   # :277-278
+    neg = np.where(lim < 0, lim, np.zeros_like(lim))                                     # :279-281
+    neg_loss = mse(np.zeros_like(neg), neg)                                              # :282-283
+    nrm = np.linalg.norm(np.reshape(cam_rot, [-1, 3]), axis=1)                           # :285-286
+    big = np.where(nrm > dt.type(np.pi * 0.125), nrm, np.zeros_like(nrm))                # :288-289
+    rot_loss = mse(np.zeros_like(big), big, 10.0)                                        # :290-292
+    return neg_loss, rot_loss

@@ -8,6 +8,7 @@ Independent torch-CPU twin of `oracle/ref_numpy.py` (same reference citations): 
     `batch_smpl.py:120-132`) in `bench.py`.
 PARITY UNPINNED — see `oracle/ref_numpy.py` header.  Never imported by the product path.
 """
+import math
 from types import SimpleNamespace
 
 import numpy as np
@@ -175,3 +176,35 @@ def cam_loss(gt_joints3d, gt_joints2d_flipped, cam_pos, cam_rot, focal, img_w=32
 def loss3d(gt_meshes, out_meshes, gt_joints3d, out_joints):
     """pose_model_3d.py:183-192."""
     return mse(gt_meshes, out_meshes, CFG.mesh_loss_scale) + mse(gt_joints3d, out_joints, CFG.joint_loss_scale)
+
+
+# ---- N3: camera-angle loss and regularisers (pose_model_3d.py:256-294), autograd twin ----
+
+def l2_normalize(x, dim, eps=1e-12):
+    return x / torch.sqrt(torch.clamp((x * x).sum(dim, keepdim=True), min=eps))
+
+
+def get_2d_points_in_3d(points_2d, cam_rot, cam_f, img_w=320.0, img_h=240.0, ss=CFG.ss):
+    img_dim = torch.tensor([img_w, img_h], dtype=points_2d.dtype)
+    rescaled = ss * (points_2d - img_dim / 2) / img_dim[1]
+    fl = cam_f.reshape(-1, 1, 1).expand(-1, points_2d.shape[1], 1)
+    p = torch.cat([rescaled, fl], dim=2)
+    R = rodrigues_batch(cam_rot)[:, None]
+    return torch.matmul(R, p[..., None])[..., 0]
+
+
+def cam_angle_loss(gt_joints3d, gt_joints2d, cam_pos, cam_rot, cam_f, img_w=320.0, img_h=240.0, ss=CFG.ss,
+                   scale=CFG.cam_angle_loss_scale):
+    v3 = l2_normalize(gt_joints3d - cam_pos[:, None, :], 2)
+    v2 = l2_normalize(get_2d_points_in_3d(gt_joints2d, cam_rot, cam_f, img_w, img_h, ss), 2)
+    dot = torch.clamp((v3 * v2).sum(2), -1.0 + 1e-6, 1.0 - 1e-6)
+    ang = torch.acos(dot)
+    return scale * (ang * ang).mean()
+
+
+def cam_reg_losses(cam_pos, cam_rot, f_raw):
+    lim = torch.stack([-cam_pos[:, 2] - 0.3, cam_pos[:, 2] + 10.0, f_raw], dim=1)
+    neg = torch.where(lim < 0, lim, torch.zeros_like(lim))
+    nrm = torch.linalg.norm(cam_rot.reshape(-1, 3), dim=1)
+    big = torch.where(nrm > math.pi * 0.125, nrm, torch.zeros_like(nrm))
+    return (neg * neg).mean(), 10.0 * (big * big).mean()
