@@ -94,6 +94,16 @@ struct smplb_model {
   void* tmap_cache;       // host-side cache of TMA descriptors (blend_tc.cu)
 };
 
+// Triangle mesh handle (raster.cu, normals.cu)
+struct smplb_mesh {
+  int device;
+  int T, V;
+  int max_order;   // largest number of faces around a vertex
+  int* tri;        // [T][3]
+  int* vptr;       // [V+1] CSR vertex -> incident (triangle, corner), ascending triangle id
+  int* vent;       // [3T]  triangle * 3 + corner
+};
+
 namespace smplb {
 
 struct PrepParams {

@@ -1,0 +1,126 @@
+// Vertex normals of the posed meshes (deps/pose_3d/utils.py:92-127 normals_from_mesh), the
+// first consumer of verts[B,6890,3] on the rendering side (utils.py:43).  One pass over HBM: a CTA keeps one
+// sample's vertices (82 KB) and its normals (82 KB) in shared memory, so the kernel reads verts once and writes
+// normals once = 165 360 algorithmic bytes per sample.
+//
+// The reference's graph is reproduced as written, including its two axis quirks:
+//  * face normals are "normalised" over the TRIANGLE axis (`tf.nn.l2_normalize(face_normals, axis=1)` on a
+//    [batch, faces, 3] tensor, utils.py:109-110): one scale per sample and coordinate, 1/sqrt(max(sum_t n_tc^2, eps));
+//  * the outward test sums (v - mean) * n over the VERTEX axis (utils.py:119-121) and then counts positive /
+//    negative entries among the three coordinates (:123-126): sign = +1 iff more coordinates are positive.
+//  * vertex_faces pads the adjacency lists with the index n_vertices (utils.py:145-147), which is a VALID face
+//    index whenever the mesh has more faces than vertices (SMPL: 13776 > 6890), so every vertex of less than
+//    maximal order also receives (max_order - order) copies of face n_vertices' normal; an out-of-range pad
+//    contributes zeros (the GPU tf.gather behaviour the docstring relies on).
+#include "common.cuh"
+
+namespace smplb {
+
+constexpr int NM_THREADS = 512;
+
+__device__ __forceinline__ void face_cross(const float* __restrict__ v, const int* __restrict__ tri, int t, float n[3]) {
+  const int a = 3 * __ldg(tri + 3 * t), b = 3 * __ldg(tri + 3 * t + 1), c = 3 * __ldg(tri + 3 * t + 2);
+  const float e1x = v[b] - v[a], e1y = v[b + 1] - v[a + 1], e1z = v[b + 2] - v[a + 2];   // v2 - v1   (:107)
+  const float e2x = v[c] - v[a], e2y = v[c + 1] - v[a + 1], e2z = v[c + 2] - v[a + 2];   // v3 - v1
+  n[0] = e1y * e2z - e1z * e2y;
+  n[1] = e1z * e2x - e1x * e2z;
+  n[2] = e1x * e2y - e1y * e2x;
+}
+
+// fixed-order block sum of three values per thread; result broadcast to all threads
+__device__ __forceinline__ void block_sum3(float x[3], float (*red)[3]) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x[k] += __shfl_xor_sync(0xffffffffu, x[k], o);
+  __syncthreads();   // red reusable
+  if (lane == 0) { red[warp][0] = x[0]; red[warp][1] = x[1]; red[warp][2] = x[2]; }
+  __syncthreads();
+  float s[3] = {0.f, 0.f, 0.f};
+  for (int w = 0; w < NM_THREADS / 32; ++w) { s[0] += red[w][0]; s[1] += red[w][1]; s[2] += red[w][2]; }
+  x[0] = s[0]; x[1] = s[1]; x[2] = s[2];
+}
+
+__global__ void __launch_bounds__(NM_THREADS, 1)
+normals_kernel(int B, int V, int T, int max_order, const int* __restrict__ tri, const int* __restrict__ vptr,
+               const int* __restrict__ vent, const float* __restrict__ verts, float* __restrict__ normals) {
+  extern __shared__ __align__(16) float nm_smem[];
+  float* sv = nm_smem;              // [3V] vertices of the sample
+  float* sn = nm_smem + 3 * V;      // [3V] its normals (unsigned)
+  __shared__ float red[NM_THREADS / 32][3];
+  const int n3 = 3 * V;
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    const float* src = verts + (size_t)b * n3;
+    float acc[3] = {0.f, 0.f, 0.f};
+    __syncthreads();   // previous sample fully written out
+    for (int i = threadIdx.x; i < n3; i += NM_THREADS) sv[i] = __ldcs(src + i);
+    __syncthreads();
+    for (int v = threadIdx.x; v < V; v += NM_THREADS) { acc[0] += sv[3 * v]; acc[1] += sv[3 * v + 1]; acc[2] += sv[3 * v + 2]; }
+    block_sum3(acc, red);
+    const float mean[3] = {acc[0] / (float)V, acc[1] / (float)V, acc[2] / (float)V};     // :116-117
+    // per-coordinate scale over the triangle axis (:109-110)
+    float sq[3] = {0.f, 0.f, 0.f};
+    for (int t = threadIdx.x; t < T; t += NM_THREADS) {
+      float n[3];
+      face_cross(sv, tri, t, n);
+      sq[0] += n[0] * n[0]; sq[1] += n[1] * n[1]; sq[2] += n[2] * n[2];
+    }
+    block_sum3(sq, red);
+    const float sc[3] = {rsqrtf(fmaxf(sq[0], 1e-12f)), rsqrtf(fmaxf(sq[1], 1e-12f)), rsqrtf(fmaxf(sq[2], 1e-12f))};
+    float pad[3] = {0.f, 0.f, 0.f};
+    if (V < T) face_cross(sv, tri, V, pad);   // the pad index n_vertices is a real face (header)
+    // vertex normals: sum of the incident (scaled) face normals (+ pads), normalised over xyz (:112-114)
+    float sd[3] = {0.f, 0.f, 0.f};
+    for (int v = threadIdx.x; v < V; v += NM_THREADS) {
+      const int e0 = __ldg(vptr + v), e1 = __ldg(vptr + v + 1);
+      float s[3] = {0.f, 0.f, 0.f};
+      for (int e = e0; e < e1; ++e) {
+        float n[3];
+        face_cross(sv, tri, __ldg(vent + e) / 3, n);
+        s[0] += n[0]; s[1] += n[1]; s[2] += n[2];
+      }
+      const float np = (float)(max_order - (e1 - e0));
+      s[0] = (s[0] + np * pad[0]) * sc[0];
+      s[1] = (s[1] + np * pad[1]) * sc[1];
+      s[2] = (s[2] + np * pad[2]) * sc[2];
+      const float inv = rsqrtf(fmaxf(s[0] * s[0] + s[1] * s[1] + s[2] * s[2], 1e-12f));
+      s[0] *= inv; s[1] *= inv; s[2] *= inv;
+      sn[3 * v] = s[0]; sn[3 * v + 1] = s[1]; sn[3 * v + 2] = s[2];
+      sd[0] += (sv[3 * v] - mean[0]) * s[0];                                               // :118-119
+      sd[1] += (sv[3 * v + 1] - mean[1]) * s[1];
+      sd[2] += (sv[3 * v + 2] - mean[2]) * s[2];
+    }
+    block_sum3(sd, red);   // also makes sn visible to every thread
+    const int gt = (sd[0] > 0.f) + (sd[1] > 0.f) + (sd[2] > 0.f), lt = (sd[0] < 0.f) + (sd[1] < 0.f) + (sd[2] < 0.f);
+    const float sign = gt > lt ? 1.0f : -1.0f;                                             // :121-126
+    float* dst = normals + (size_t)b * n3;
+    for (int i = threadIdx.x; i < n3; i += NM_THREADS) __stcs(dst + i, sn[i] * sign);
+  }
+}
+
+}  // namespace smplb
+
+using namespace smplb;
+
+extern "C" int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const float* verts, float* normals, void* stream) {
+  if (!m) return fail(SMPLB_E_INVALID_ARG, "smplb_mesh_normals: null mesh");
+  if (B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_mesh_normals: negative batch");
+  if (B == 0) return SMPLB_OK;
+  if (!verts || !normals) return fail(SMPLB_E_INVALID_ARG, "smplb_mesh_normals: null pointer");
+  const size_t smem = (size_t)6 * m->V * sizeof(float);
+  if (smem > 220 * 1024) return fail(SMPLB_E_UNSUPPORTED, "smplb_mesh_normals: more than 9386 vertices per mesh");
+  static int n_sm[64] = {};
+  const int dev = m->device & 63;
+  if (!n_sm[dev]) {
+    int v = 0;
+    SMPLB_CUDA_CHECK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, m->device));
+    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(normals_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    n_sm[dev] = v;
+  }
+  const int grid = B < n_sm[dev] ? B : n_sm[dev];
+  normals_kernel<<<grid, NM_THREADS, smem, (cudaStream_t)stream>>>(B, m->V, m->T, m->max_order, m->tri, m->vptr, m->vent,
+                                                                   verts, normals);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}

@@ -12,17 +12,10 @@
 // with the same float operations (no FMA contraction, the double-precision viewport transform of the
 // reference, x86 float->int conversion semantics), so ids, barycentrics and depth are bit-identical to the
 // reference's C++.  (Not reproduced: NaN depths of zero-area triangles, which the reference lets through.)
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
-
-struct smplb_mesh {
-  int device;
-  int T, V;
-  int* tri;        // [T][3]
-  int* vptr;       // [V+1] CSR vertex -> incident (triangle, corner), ascending triangle id
-  int* vent;       // [3T]  triangle * 3 + corner
-};
 
 namespace smplb {
 
@@ -251,6 +244,9 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   SMPLB_CUDA_CHECK(cudaSetDevice(device));
   smplb_mesh* m = new smplb_mesh();
   m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr;
+  // vertex_faces_from_face_verts (deps/pose_3d/utils.py:130-149): adjacency lists padded to the maximum vertex order
+  m->max_order = 0;
+  for (int v = 0; v < V; ++v) m->max_order = std::max(m->max_order, vptr[v + 1] - vptr[v]);
   cudaError_t e = cudaMalloc((void**)&m->tri, sizeof(int) * (size_t)(3 * T > 0 ? 3 * T : 1));
   if (e == cudaSuccess) e = cudaMalloc((void**)&m->vptr, sizeof(int) * (size_t)(V + 1));
   if (e == cudaSuccess) e = cudaMalloc((void**)&m->vent, sizeof(int) * (size_t)(3 * T > 0 ? 3 * T : 1));

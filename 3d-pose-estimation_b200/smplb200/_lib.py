@@ -98,6 +98,7 @@ SYMBOLS = {
     'smplb_rasterize_backward': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                              C.c_size_t, C.c_void_p]),
+    'smplb_mesh_normals': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_add_axis_angle': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_rotate_global_pose': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_cam_losses_scratch_bytes': (C.c_size_t, [C.c_int32]),

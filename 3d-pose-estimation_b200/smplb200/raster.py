@@ -64,6 +64,18 @@ class Mesh:
                                              ws.numel(), st))
         return bary, ids, z
 
+    def normals(self, verts, out=None):
+        """normals_from_mesh (deps/pose_3d/utils.py:92-127): verts [B,V,3] -> [B,V,3]."""
+        verts = verts.to(self.device, torch.float32).contiguous()
+        if verts.dim() != 3 or verts.shape[1] != self.V or verts.shape[2] != 3:
+            raise ValueError('verts must be [B,%d,3]; got %s' % (self.V, tuple(verts.shape)))
+        if out is None:
+            out = torch.empty_like(verts)
+        with torch.cuda.device(self.device):
+            st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            check(_lib.lib().smplb_mesh_normals(self._h, verts.shape[0], _ptr(verts), _ptr(out), st))
+        return out
+
     def rasterize_backward(self, ndc, bary, ids, g_bary, W, H):
         ndc = ndc.to(self.device, torch.float32).contiguous()
         B = ndc.shape[0]

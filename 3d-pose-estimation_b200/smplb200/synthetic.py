@@ -98,3 +98,21 @@ def make_inputs(B, seed=1000, dtype=np.float32):
         'cam_pos': cam_pos.astype(dtype), 'cam_rot': cam_rot.astype(dtype),
         'focal': focal.astype(dtype),
     }
+
+
+def uv_sphere_mesh(n_lon=82, n_ring=84):
+    """Closed UV-sphere with exactly SMPL's counts: 82*84 + 2 = 6890 vertices, 82*83*2 + 2*82 = 13776 triangles."""
+    th = np.pi * (np.arange(n_ring) + 1) / (n_ring + 1)
+    ph = 2 * np.pi * np.arange(n_lon) / n_lon
+    ring = np.stack([np.outer(np.sin(th), np.cos(ph)), np.outer(np.cos(th), np.ones(n_lon)),
+                     np.outer(np.sin(th), np.sin(ph))], -1).reshape(-1, 3)
+    v = np.concatenate([ring, [[0, 1, 0]], [[0, -1, 0]]]).astype(np.float32)
+    idx = lambda r, c: r * n_lon + (c % n_lon)
+    tri = []
+    for r in range(n_ring - 1):
+        for c in range(n_lon):
+            tri += [[idx(r, c), idx(r + 1, c), idx(r, c + 1)], [idx(r, c + 1), idx(r + 1, c), idx(r + 1, c + 1)]]
+    top, bot = n_lon * n_ring, n_lon * n_ring + 1
+    for c in range(n_lon):
+        tri += [[top, idx(0, c), idx(0, c + 1)], [bot, idx(n_ring - 1, c + 1), idx(n_ring - 1, c)]]
+    return v, np.asarray(tri, np.int32)

@@ -281,21 +281,8 @@ def run_sweep(args, rank, local_rank, world, dist):
 
 
 def uv_sphere_mesh(n_lon=82, n_ring=84):
-    """Closed UV-sphere with exactly SMPL's counts: 82*84 + 2 = 6890 vertices, 82*83*2 + 2*82 = 13776 triangles."""
-    th = np.pi * (np.arange(n_ring) + 1) / (n_ring + 1)
-    ph = 2 * np.pi * np.arange(n_lon) / n_lon
-    ring = np.stack([np.outer(np.sin(th), np.cos(ph)), np.outer(np.cos(th), np.ones(n_lon)),
-                     np.outer(np.sin(th), np.sin(ph))], -1).reshape(-1, 3)
-    v = np.concatenate([ring, [[0, 1, 0]], [[0, -1, 0]]]).astype(np.float32)
-    idx = lambda r, c: r * n_lon + (c % n_lon)
-    tri = []
-    for r in range(n_ring - 1):
-        for c in range(n_lon):
-            tri += [[idx(r, c), idx(r + 1, c), idx(r, c + 1)], [idx(r, c + 1), idx(r + 1, c), idx(r + 1, c + 1)]]
-    top, bot = n_lon * n_ring, n_lon * n_ring + 1
-    for c in range(n_lon):
-        tri += [[top, idx(0, c), idx(0, c + 1)], [bot, idx(n_ring - 1, c + 1), idx(n_ring - 1, c)]]
-    return v, np.asarray(tri, np.int32)
+    from smplb200 import synthetic as syn
+    return syn.uv_sphere_mesh(n_lon, n_ring)
 
 
 def raster_inputs(B, seed):
@@ -421,6 +408,70 @@ def raster_cpu_rate(ndc_h, tri, W, H, seconds):
                 else 'oracle/raster_port.c')}
 
 
+def run_normals(args, rank, local_rank, world, dist):
+    """SURVEY 8f N1 (shading input): normals_from_mesh over verts[B,6890,3] (deps/pose_3d/utils.py:92-127), one HBM
+    pass; B = 65536 meshes per GPU (the forward's output batch)."""
+    from smplb200 import synthetic as syn
+    from smplb200.raster import Mesh
+    dev = torch.device('cuda', local_rank)
+    B = args.batch
+    v, tri = syn.uv_sphere_mesh()
+    mesh = Mesh(tri, v.shape[0], local_rank)
+    g = torch.Generator(device=dev).manual_seed(1000 + rank)
+    verts = torch.from_numpy(v).to(dev)[None] * (0.2 + 0.8 * torch.rand((B, 1, 3), device=dev, generator=g)) \
+        + 0.002 * torch.randn((B, v.shape[0], 3), device=dev, generator=g)
+    out = torch.empty_like(verts)
+
+    def step():
+        mesh.normals(verts, out=out)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    sampler.stop_flag = True
+    sampler.join()
+    t = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    byt = 2 * 82680 * B
+    line = {'metric': 'mesh_normals_samples_per_s', 'value': world * B / (ms * 1e-3), 'unit': 'samples/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': 'normals_from_mesh of B=%d meshes (6890 vertices, 13776 triangles) per GPU per step; '
+                                   'working set %.1f GB exceeds L2' % (B, byt / 1e9)},
+            'clocks': sampler.summary(), 'gpu_launches': args.steps,
+            'roofline': {'bound': 'hbm', 'kernel': 'normals_kernel', 'achieved': byt / (ms * 1e-3) / 1e9, 'peak': peak,
+                         'unit': 'GB/s', 'frac': byt / (ms * 1e-3) / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
+                         'algorithmic_bytes_per_launch': byt}}
+    if not args.no_cpu_baseline:
+        from oracle import ref_numpy as rn          # timed CPU baseline only
+        vf = rn.vertex_faces_from_face_verts(tri)
+        hv = verts[:64].cpu().numpy()
+        rn.normals_from_mesh(hv, tri, vf)
+        n, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < args.cpu_seconds:
+            rn.normals_from_mesh(hv, tri, vf)
+            n += 64
+        el = time.perf_counter() - t0
+        line['cpu_baseline'] = {'value': n / el, 'unit': 'samples/s', 'cores': 1, 'kind': 'port',
+                                'sample': '%d meshes in %.1f s, numpy restatement of the TF graph (64 per call)' % (n, el)}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -434,7 +485,7 @@ def main():
     ap.add_argument('--cpu-seconds', type=float, default=12.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
-    ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep', 'raster'],
+    ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep', 'raster', 'normals'],
                     help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
     ap.add_argument('--graph', action='store_true', help='fit mode: replay the step from a CUDA graph')
     args = ap.parse_args()
@@ -463,8 +514,8 @@ def main():
     if args.mode == 'sweep':
         run_sweep(args, rank, local_rank, world, dist)
         return
-    if args.mode == 'raster':
-        run_raster(args, rank, local_rank, world, dist)
+    if args.mode in ('raster', 'normals'):
+        (run_raster if args.mode == 'raster' else run_normals)(args, rank, local_rank, world, dist)
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()

@@ -247,6 +247,11 @@ int32_t smplb_rasterize_backward(const smplb_mesh* m, int32_t B, const float* nd
                                  const int32_t* ids, const float* g_bary, int32_t W, int32_t H, float* g_ndc,
                                  void* workspace, size_t workspace_bytes, void* stream);
 
+/* normals_from_mesh (deps/pose_3d/utils.py:92-127, with vertex_faces_from_face_verts :130-149 built into the mesh
+ * handle): verts [B,V,3] -> unit vertex normals [B,V,3], oriented by the reference's outward test.  One HBM pass
+ * (a CTA holds one sample's vertices and normals in shared memory); V <= 9386. */
+int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const float* verts, float* normals, void* stream);
+
 /* ---- Per-sample operators either side of the path ---------------------------------
  * add_axis_angle_rotations (deps/pose_3d/utils.py:170-199): rv1, rv2 [N,3] -> axis-angle of "rv2 then rv1". */
 int32_t smplb_add_axis_angle(int32_t N, const float* rv1, const float* rv2, float* out, void* stream);

@@ -348,3 +348,37 @@ def cam_reg_losses(cam_pos, cam_rot, f_raw):
     big = np.where(nrm > dt.type(np.pi * 0.125), nrm, np.zeros_like(nrm))                # :288-289
     rot_loss = mse(np.zeros_like(big), big, 10.0)                                        # :290-292
     return neg_loss, rot_loss
+
+
+# ---- N1 (shading input): vertex normals, deps/pose_3d/utils.py:92-149 ------------------------------------------
+
+def vertex_faces_from_face_verts(faces):
+    """utils.py:130-149: adjacency lists padded with the index n_vertices."""
+    n_vertices = int(np.amax(faces)) + 1
+    vertex_faces = [[] for _ in range(n_vertices)]
+    for face_idx, face in enumerate(faces):
+        vertex_faces[face[0]].append(face_idx)
+        vertex_faces[face[1]].append(face_idx)
+        vertex_faces[face[2]].append(face_idx)
+    orders = [len(v) for v in vertex_faces]
+    mo = max(orders)
+    return np.array([vf + [n_vertices] * (mo - vo) for vf, vo in zip(vertex_faces, orders)])
+
+
+def normals_from_mesh(vertices, faces, vertex_faces):
+    """utils.py:92-127, as written (face normals normalised over the triangle axis, :109-110; out-of-range gather
+    indices give zeros as on the GPU, in-range pad indices gather that face)."""
+    dt = vertices.dtype
+    v1, v2, v3 = vertices[:, faces[:, 0]], vertices[:, faces[:, 1]], vertices[:, faces[:, 2]]   # :103-105
+    fn = np.cross(v2 - v1, v3 - v1)                                                             # :107
+    fn = l2_normalize(fn, 1)                                                                    # :108 (axis=1!)
+    T = fn.shape[1]
+    fn_pad = np.concatenate([fn, np.zeros((fn.shape[0], 1, 3), dtype=dt)], axis=1)
+    idx = np.where(vertex_faces < T, vertex_faces, T)
+    normals = fn_pad[:, idx].sum(axis=2)                                                        # :110-111
+    normals = l2_normalize(normals, 2)                                                          # :112
+    centered = vertices - vertices.mean(axis=1, keepdims=True)                                  # :115-116
+    s = np.sum(centered * normals, axis=1)                                                      # :117
+    gt, lt = np.count_nonzero(s > 0, axis=1), np.count_nonzero(s < 0, axis=1)                   # :119-120
+    sign = 2 * (gt > lt).astype(dt) - 1                                                         # :122
+    return normals * sign.reshape(-1, 1, 1)

@@ -133,3 +133,21 @@ def test_drop_in_rasterize_triangles_autograd(orc):
     assert np.abs(img[0].detach().cpu().numpy() - bary).max() < 1e-5
     (img * torch.randn_like(img)).sum().backward()
     assert v.grad is not None and float(v.grad.abs().max()) > 0 and float(attr.grad.abs().max()) > 0
+
+
+@pytest.mark.parametrize('B,lon,ring', [(3, 12, 10), (5, 82, 84)])
+def test_vertex_normals_vs_oracle(B, lon, ring):
+    """smplb_mesh_normals vs the float64 restatement of normals_from_mesh (utils.py:92-127), SMPL-sized mesh included."""
+    from oracle import ref_numpy as rn
+    from smplb200 import synthetic as syn
+    from smplb200.raster import Mesh
+    v, tri = syn.uv_sphere_mesh(lon, ring)
+    rng = np.random.default_rng(lon)
+    scale = rng.uniform(0.2, 1.0, size=(B, 1, 3))
+    verts = (v[None] * scale + rng.normal(0, 0.002, size=(B,) + v.shape) + rng.normal(0, 0.3, size=(B, 1, 3))).astype(np.float32)
+    verts[B - 1] *= -1.0          # inside-out sample: the outward test must flip it
+    m = Mesh(tri, v.shape[0], 0)
+    got = m.normals(torch.from_numpy(verts).cuda()).cpu().numpy()
+    want = rn.normals_from_mesh(verts.astype(np.float64), tri, rn.vertex_faces_from_face_verts(tri))
+    assert np.abs(got - want).max() <= 1e-5
+    assert np.allclose(np.linalg.norm(got, axis=2), 1.0, atol=1e-5)

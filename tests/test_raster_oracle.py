@@ -114,3 +114,25 @@ def test_gradient_restatement_vs_finite_differences():
             fd[i, c] = (f(v.astype(np.float64) + d) - f(v.astype(np.float64) - d)) / 2e-5
     assert np.abs(g - fd).max() <= 1e-3 * np.abs(fd).max(), (g, fd)
     assert not g[:, 2].any()
+
+
+def test_normals_restatement_on_sphere_and_pad_quirk():
+    """normals_from_mesh restatement (oracle/ref_numpy.py): unit length, outward on a sphere, and the reference's
+    pad-index behaviour (pad = n_vertices is a valid face id when faces > vertices)."""
+    from oracle import ref_numpy as rn
+    from smplb200 import synthetic as syn
+    v, tri = syn.uv_sphere_mesh(12, 10)
+    vf = rn.vertex_faces_from_face_verts(tri)
+    assert vf.shape[0] == v.shape[0] and (vf == v.shape[0]).any() and tri.shape[0] > v.shape[0]
+    n = rn.normals_from_mesh(v[None].astype(np.float64), tri, vf)[0]
+    assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-9)
+    # vertices of maximal order (the two poles) get no pad contribution and point outward on the unit sphere
+    full = (vf != v.shape[0]).all(1)
+    assert full.sum() == 2 and ((n[full] * v[full]).sum(1) > 0.8).all()
+    # every other vertex also sums (max_order - order) copies of face n_vertices' normal (utils.py:145-147)
+    fn = rn.l2_normalize(np.cross(v[tri[:, 1]] - v[tri[:, 0]], v[tri[:, 2]] - v[tri[:, 0]])[None].astype(np.float64), 1)[0]
+    k = 5
+    own = [t for t in range(tri.shape[0]) if k in tri[t]]
+    raw = fn[own].sum(0) + (vf.shape[1] - len(own)) * fn[v.shape[0]]
+    raw /= np.linalg.norm(raw)
+    assert np.allclose(np.abs(raw), np.abs(n[k]), atol=1e-9)
