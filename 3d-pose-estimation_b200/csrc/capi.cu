@@ -172,11 +172,6 @@ extern "C" int32_t smplb_forward_host(const smplb_model* m, const smplb_forward_
     if (!dst) return cudaErrorInvalidValue;
     return cudaMemcpyAsync((void*)dst, src, n * sizeof(float), cudaMemcpyHostToDevice, st);
   };
-  auto d2h = [&](float* dst, const float* src, size_t n) -> cudaError_t {
-    if (!dst) return cudaSuccess;
-    if (!src) return cudaErrorInvalidValue;
-    return cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToHost, st);
-  };
   SMPLB_CUDA_CHECK(h2d(d->beta, h->beta, B * NB));
   SMPLB_CUDA_CHECK(h2d(d->theta, h->theta, B * NJ * 3));
   SMPLB_CUDA_CHECK(h2d(d->cam_pos, h->cam_pos, B * 3));
@@ -192,15 +187,47 @@ extern "C" int32_t smplb_forward_host(const smplb_model* m, const smplb_forward_
   if (!h->cam_pos) { io.cam_pos = nullptr; io.cam_rot = nullptr; io.focal = nullptr; io.uv = nullptr; io.px = nullptr; }
   if (!h->focal) io.focal = nullptr;
   io.cfg = h->cfg;
-  int32_t rc = smplb_forward(m, &io, workspace, workspace_bytes, flags, stream);
-  if (rc != SMPLB_OK) return rc;
-  SMPLB_CUDA_CHECK(d2h(h->verts, io.verts, B * NV3));
-  SMPLB_CUDA_CHECK(d2h(h->joints, io.joints, B * NJ * 3));
-  SMPLB_CUDA_CHECK(d2h(h->kp, io.kp, B * NK * 3));
-  SMPLB_CUDA_CHECK(d2h(h->Rs, io.Rs, B * NJ * 9));
-  SMPLB_CUDA_CHECK(d2h(h->A, io.A, B * NJ * 12));
-  SMPLB_CUDA_CHECK(d2h(h->uv, io.uv, B * NJ * 2));
-  SMPLB_CUDA_CHECK(d2h(h->px, io.px, B * NJ * 2));
+  // Chunked pipeline: the kernels of chunk k+1 run on `st` while a second stream drains the outputs of chunk k
+  // over PCIe (the D2H of verts is ~20x the kernel time, so everything but the first chunk's kernels is hidden).
+  static thread_local cudaStream_t cs[64] = {};
+  static thread_local cudaEvent_t ev[64] = {}, ev_done[64] = {};
+  const int dv = m ? (m->device & 63) : 0;
+  if (!cs[dv]) {
+    SMPLB_CUDA_CHECK(cudaStreamCreateWithFlags(&cs[dv], cudaStreamNonBlocking));
+    SMPLB_CUDA_CHECK(cudaEventCreateWithFlags(&ev[dv], cudaEventDisableTiming));
+    SMPLB_CUDA_CHECK(cudaEventCreateWithFlags(&ev_done[dv], cudaEventDisableTiming));
+  }
+  auto d2h = [&](float* dst, const float* src, size_t n) -> cudaError_t {
+    if (!dst) return cudaSuccess;
+    if (!src) return cudaErrorInvalidValue;
+    return cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToHost, cs[dv]);
+  };
+  const size_t CH = 8192;
+  auto off = [](const float* p, size_t n) { return p ? p + n : nullptr; };
+  auto offm = [](float* p, size_t n) { return p ? p + n : nullptr; };
+  for (size_t b0 = 0; b0 < B; b0 += CH) {
+    const size_t nb = B - b0 < CH ? B - b0 : CH;
+    smplb_forward_io c = io;
+    c.B = (int32_t)nb;
+    c.beta = off(io.beta, b0 * NB); c.theta = off(io.theta, b0 * NJ * 3);
+    c.cam_pos = off(io.cam_pos, b0 * 3); c.cam_rot = off(io.cam_rot, b0 * 3); c.focal = off(io.focal, b0);
+    c.verts = offm(io.verts, b0 * NV3); c.joints = offm(io.joints, b0 * NJ * 3); c.kp = offm(io.kp, b0 * NK * 3);
+    c.Rs = offm(io.Rs, b0 * NJ * 9); c.A = offm(io.A, b0 * NJ * 12); c.uv = offm(io.uv, b0 * NJ * 2);
+    c.px = offm(io.px, b0 * NJ * 2);
+    int32_t rc = smplb_forward(m, &c, workspace, workspace_bytes, flags, stream);
+    if (rc != SMPLB_OK) return rc;
+    SMPLB_CUDA_CHECK(cudaEventRecord(ev[dv], st));
+    SMPLB_CUDA_CHECK(cudaStreamWaitEvent(cs[dv], ev[dv], 0));
+    SMPLB_CUDA_CHECK(d2h(offm(h->verts, b0 * NV3), c.verts, nb * NV3));
+    SMPLB_CUDA_CHECK(d2h(offm(h->joints, b0 * NJ * 3), c.joints, nb * NJ * 3));
+    SMPLB_CUDA_CHECK(d2h(offm(h->kp, b0 * NK * 3), c.kp, nb * NK * 3));
+    SMPLB_CUDA_CHECK(d2h(offm(h->Rs, b0 * NJ * 9), c.Rs, nb * NJ * 9));
+    SMPLB_CUDA_CHECK(d2h(offm(h->A, b0 * NJ * 12), c.A, nb * NJ * 12));
+    SMPLB_CUDA_CHECK(d2h(offm(h->uv, b0 * NJ * 2), c.uv, nb * NJ * 2));
+    SMPLB_CUDA_CHECK(d2h(offm(h->px, b0 * NJ * 2), c.px, nb * NJ * 2));
+  }
+  SMPLB_CUDA_CHECK(cudaEventRecord(ev_done[dv], cs[dv]));
+  SMPLB_CUDA_CHECK(cudaStreamWaitEvent(st, ev_done[dv], 0));
   SMPLB_CUDA_CHECK(cudaStreamSynchronize(st));
   return SMPLB_OK;
 }

@@ -639,7 +639,7 @@ def main():
             line['e2e'] = {'value': world * B * args.e2e_steps / e2e_max, 'unit': UNIT,
                            'h2d_bytes_per_step': e2e[1], 'd2h_bytes_per_step': e2e[2],
                            'steps': args.e2e_steps, 'note': 'smplb_forward_host, pinned host buffers, PCIe-bound'}
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:     # CPU baseline: rank 0 at N=1 only
             rate, cores, ns, el, _ = cpu_reference_rate(args.ref_chunk, args.cpu_seconds, 1000)
             line['cpu_baseline'] = {
                 'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',

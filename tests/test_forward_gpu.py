@@ -220,3 +220,34 @@ def test_dropin_smpl_class(synth_dd, oracle64, tmp_path):
     uv = project(smpl_model.J_transformed.reshape(-1, 3), cam_p, cam_r, np.full(96, 0.05, np.float32))
     ref = rn.project(o['J_transformed'].reshape(-1, 3), cam_p.astype(np.float64), cam_r.astype(np.float64), np.full(96, 0.05))
     assert maxrel(uv.cpu().numpy(), ref) <= TOL
+
+
+def test_forward_host_chunked_pipeline_matches_device_call(gpu_model):
+    """smplb_forward_host (host buffers, chunked H2D / kernels / D2H pipeline, 8192-sample chunks) returns exactly
+    what the device-resident call computes, across a chunk boundary and with a ragged tail."""
+    import ctypes as C
+    import torch
+    from smplb200 import _lib, synthetic as syn
+    B = 8192 + 8192 + 777
+    inp = syn.make_inputs(B, seed=77)
+    out = gpu_model.forward(inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'])
+    torch.cuda.synchronize()
+    NK = gpu_model.NK
+    hb = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
+    ho = {'verts': torch.empty((B, 6890, 3)).pin_memory(), 'joints': torch.empty((B, 24, 3)).pin_memory(),
+          'kp': torch.empty((B, NK, 3)).pin_memory(), 'px': torch.empty((B, 24, 2)).pin_memory()}
+    dbuf = {k: torch.empty_like(v, device='cuda') for k, v in {**hb, **ho}.items()}
+    cfg = _lib.CamCfg(320.0, 240.0, 0.024, 0.05)
+    FIO = _lib.ForwardIO
+    hio = FIO(B, hb['beta'].data_ptr(), hb['theta'].data_ptr(), ho['verts'].data_ptr(), ho['joints'].data_ptr(),
+              ho['kp'].data_ptr(), None, None, hb['cam_pos'].data_ptr(), hb['cam_rot'].data_ptr(),
+              hb['focal'].data_ptr(), None, ho['px'].data_ptr(), cfg)
+    dio = FIO(B, dbuf['beta'].data_ptr(), dbuf['theta'].data_ptr(), dbuf['verts'].data_ptr(), dbuf['joints'].data_ptr(),
+              dbuf['kp'].data_ptr(), None, None, dbuf['cam_pos'].data_ptr(), dbuf['cam_rot'].data_ptr(),
+              dbuf['focal'].data_ptr(), None, dbuf['px'].data_ptr(), cfg)
+    ws, _ = gpu_model.workspace(B, 0)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(_lib.lib().smplb_forward_host(gpu_model._h, C.byref(hio), C.byref(dio), C.c_void_p(ws.data_ptr()),
+                                             ws.numel(), 0, st))
+    for k in ('verts', 'joints', 'kp', 'px'):
+        assert torch.equal(ho[k], out[k].cpu()), k
