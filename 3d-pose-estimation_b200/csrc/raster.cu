@@ -325,3 +325,143 @@ extern "C" int32_t smplb_rasterize_backward(const smplb_mesh* m, int32_t B, cons
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
+
+// ---- fused interpolation + diffuse Phong shading (the renderer path pose_3d drives: utils.py:20-58) ----------------
+// rasterize_triangles.py:73-86 per vertex (clip transform, guarded perspective divide), then per pixel:
+// winner decode (as raster_resolve_kernel) -> perspective-correct barycentrics (:125-144) -> interpolation of
+// normals | positions | diffuse colours with the -1 background (:147-164, mesh_renderer.py:371-373) ->
+// phong_shader without the specular term (mesh_renderer.py:84-118,158-162), rows reversed (:162).
+// One pass: the per-pixel barycentrics / ids never go to HBM, the only output is RGBA (16 B / pixel).
+namespace smplb {
+
+__global__ void __launch_bounds__(256) clip_transform_kernel(int B, int V, const float* __restrict__ verts,
+                                                             const float* __restrict__ clip_tf, float* __restrict__ ndc,
+                                                             float* __restrict__ clip_w) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)B * V) return;
+  const int b = (int)(i / V);
+  const float* M = clip_tf + (size_t)b * 16;
+  const float x = verts[3 * i], y = verts[3 * i + 1], z = verts[3 * i + 2];
+  float c[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) c[r] = M[4 * r] * x + M[4 * r + 1] * y + M[4 * r + 2] * z + M[4 * r + 3];
+  const float sgn = c[3] > 0.f ? 1.f : (c[3] < 0.f ? -1.f : 0.f);
+  const float w = fmaxf(fabsf(c[3]), 1e-6f) * sgn;                       // :81-84
+  ndc[3 * i] = c[0] / w; ndc[3 * i + 1] = c[1] / w; ndc[3 * i + 2] = c[2] / w;   // :85-86
+  clip_w[i] = w;
+}
+
+__global__ void __launch_bounds__(256) raster_shade_kernel(int B, int T, int V, int W, int H, int L,
+                                                           const float* __restrict__ ndc, const float* __restrict__ clip_w,
+                                                           const int* __restrict__ tri,
+                                                           const unsigned long long* __restrict__ keys,
+                                                           const float* __restrict__ verts, const float* __restrict__ normals,
+                                                           const float* __restrict__ diffuse, const float* __restrict__ light_pos,
+                                                           const float* __restrict__ light_int, const float* __restrict__ ambient,
+                                                           float* __restrict__ rgba) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)B * W * H) return;
+  const int b = (int)(i / ((size_t)W * H)), p = (int)(i % ((size_t)W * H));
+  const int ix = p % W, iy = p / W;
+  const unsigned long long key = keys[i];
+  float bc[3] = {0.f, 0.f, 0.f}, z;
+  int t = 0;
+  if (key != KEY_EMPTY) {
+    t = (int)(~(uint32_t)key);
+    TriSetup s;
+    tri_setup(ndc + (size_t)b * V * 3, tri, t, W, H, s);
+    tri_eval(s, ix, iy, bc[0], bc[1], bc[2], z);
+  }
+  float a9[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, alpha = 0.f;
+  if (T > 0) {
+    int vid[3];
+    float wgt[3], fac = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      vid[k] = __ldg(tri + 3 * t + k);
+      wgt[k] = bc[k] * (1.0f / clip_w[(size_t)b * V + vid[k]]);          // :125-135
+      fac += wgt[k];
+    }
+    const float den = fmaxf(fac, 1e-6f);                                 // :139-144
+    float csum = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float c = wgt[k] / den;
+      csum += c;
+      const size_t o = ((size_t)b * V + vid[k]) * 3;
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        a9[e] += normals[o + e] * c;                                     // attribute order: mesh_renderer.py:361
+        a9[3 + e] += verts[o + e] * c;
+        a9[6 + e] += (diffuse ? diffuse[o + e] : 1.0f) * c;
+      }
+    }
+    alpha = fminf(fmaxf(2.0f * csum, 0.f), 1.f);                         // :157-159
+  }
+#pragma unroll
+  for (int e = 0; e < 9; ++e) a9[e] = alpha * a9[e] + (1.0f - alpha) * -1.0f;   // :161-164, background -1
+  const float nn = rsqrtf(fmaxf(a9[0] * a9[0] + a9[1] * a9[1] + a9[2] * a9[2], 1e-12f));   // mesh_renderer.py:376
+  const float n[3] = {a9[0] * nn, a9[1] * nn, a9[2] * nn};
+  const float mask = (a9[6] >= 0.f || a9[7] >= 0.f || a9[8] >= 0.f) ? 1.f : 0.f;           // :387
+  float col[3] = {0.f, 0.f, 0.f};
+  if (ambient)
+#pragma unroll
+    for (int e = 0; e < 3; ++e) col[e] = ambient[3 * b + e] * a9[6 + e];                    // :92-94
+  for (int l = 0; l < L; ++l) {
+    const float* lp = light_pos + ((size_t)b * L + l) * 3;
+    const float* li = light_int + ((size_t)b * L + l) * 3;
+    const float d[3] = {lp[0] - a9[3], lp[1] - a9[4], lp[2] - a9[5]};
+    const float dn = rsqrtf(fmaxf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], 1e-12f));        // :100-102
+    const float ndl = fminf(fmaxf((n[0] * d[0] + n[1] * d[1] + n[2] * d[2]) * dn, 0.f), 1.f);   // :106-109
+#pragma unroll
+    for (int e = 0; e < 3; ++e) col[e] += a9[6 + e] * ndl * li[e];                          // :112-118
+  }
+  float4 o;
+  o.x = mask > 0.5f ? col[0] : 0.f;                                                        // :158-161
+  o.y = mask > 0.5f ? col[1] : 0.f;
+  o.z = mask > 0.5f ? col[2] : 0.f;
+  o.w = mask;
+  reinterpret_cast<float4*>(rgba)[((size_t)b * H + (H - 1 - iy)) * W + ix] = o;            // :162 tf.reverse(axis=1)
+}
+
+}  // namespace smplb
+
+// raster workspace | ndc [B,V,3] | clip_w [B,V]
+extern "C" size_t smplb_render_workspace_bytes(const smplb_mesh* m, int32_t B, int32_t W, int32_t H) {
+  if (!m || B <= 0) return 0;
+  return smplb_rasterize_workspace_bytes(m, B, W, H) + ru256((size_t)B * m->V * 12) + ru256((size_t)B * m->V * 4);
+}
+
+extern "C" int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const float* verts, const float* normals,
+                                        const float* diffuse, const float* clip_transforms, const float* light_positions,
+                                        const float* light_intensities, int32_t L, const float* ambient, int32_t W,
+                                        int32_t H, float* rgba, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!m) return fail(SMPLB_E_INVALID_ARG, "smplb_render_diffuse: null mesh");
+  if (B < 0 || L < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_render_diffuse: negative batch or light count");
+  if (W <= 0 || H <= 0) return fail(SMPLB_E_INVALID_ARG, "smplb_render_diffuse: image width and height must be > 0");
+  if (B == 0) return SMPLB_OK;
+  if (B > 65535) return fail(SMPLB_E_UNSUPPORTED, "smplb_render_diffuse: at most 65535 images per call");
+  if (!verts || !normals || !clip_transforms || !rgba || (L > 0 && (!light_positions || !light_intensities)))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_render_diffuse: null pointer");
+  if (!workspace || workspace_bytes < smplb_render_workspace_bytes(m, B, W, H) || ((uintptr_t)workspace & 255))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_render_diffuse: workspace missing, too small or not 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t rws = smplb_rasterize_workspace_bytes(m, B, W, H), npix = (size_t)B * W * H;
+  char* w = (char*)workspace;
+  float* ndc = (float*)(w + rws);
+  float* clip_w = (float*)(w + rws + ru256((size_t)B * m->V * 12));
+  unsigned long long* keys = (unsigned long long*)w;
+  int* big_count = (int*)(w + ru256(npix * 8));
+  int* big_list = (int*)(w + ru256(npix * 8) + 256);
+  clip_transform_kernel<<<(unsigned)(((size_t)B * m->V + 255) / 256), 256, 0, st>>>(B, m->V, verts, clip_transforms, ndc, clip_w);
+  raster_clear_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(keys, npix, big_count);
+  if (m->T > 0) {
+    raster_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
+    raster_big_kernel<<<592, 256, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
+  }
+  raster_shade_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(B, m->T, m->V, W, H, L, ndc, clip_w, m->tri, keys, verts,
+                                                                     normals, diffuse, light_positions, light_intensities,
+                                                                     ambient, rgba);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}

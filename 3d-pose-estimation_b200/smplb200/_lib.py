@@ -99,6 +99,10 @@ SYMBOLS = {
                                              C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                              C.c_size_t, C.c_void_p]),
     'smplb_mesh_normals': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'smplb_render_workspace_bytes': (C.c_size_t, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]),
+    'smplb_render_diffuse': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
+                                         C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     'smplb_add_axis_angle': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_rotate_global_pose': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_cam_losses_scratch_bytes': (C.c_size_t, [C.c_int32]),

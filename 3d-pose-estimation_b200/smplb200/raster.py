@@ -76,6 +76,35 @@ class Mesh:
             check(_lib.lib().smplb_mesh_normals(self._h, verts.shape[0], _ptr(verts), _ptr(out), st))
         return out
 
+    def render_diffuse(self, verts, normals, clip_transforms, light_positions, light_intensities, W, H,
+                       diffuse=None, ambient=None):
+        """smplb_render_diffuse: one fused pass verts/normals -> shaded RGBA [B,H,W,4] (no specular term)."""
+        dev = self.device
+
+        def f32(x, shape):
+            x = x.to(dev, torch.float32).contiguous()
+            if tuple(x.shape) != tuple(shape):
+                raise ValueError('expected shape %s, got %s' % (tuple(shape), tuple(x.shape)))
+            return x
+
+        B = verts.shape[0]
+        verts, normals = f32(verts, (B, self.V, 3)), f32(normals, (B, self.V, 3))
+        diffuse = None if diffuse is None else f32(diffuse, (B, self.V, 3))
+        clip_transforms = f32(clip_transforms, (B, 4, 4))
+        L = light_positions.shape[1]
+        lp, li = f32(light_positions, (B, L, 3)), f32(light_intensities, (B, L, 3))
+        ambient = None if ambient is None else f32(ambient, (B, 3))
+        rgba = torch.empty((B, H, W, 4), dtype=torch.float32, device=dev)
+        need = _lib.lib().smplb_render_workspace_bytes(self._h, B, W, H)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            check(_lib.lib().smplb_render_diffuse(self._h, B, _ptr(verts), _ptr(normals), _ptr(diffuse),
+                                                  _ptr(clip_transforms), _ptr(lp), _ptr(li), L, _ptr(ambient), W, H,
+                                                  _ptr(rgba), _ptr(self._ws), self._ws.numel(), st))
+        return rgba
+
     def rasterize_backward(self, ndc, bary, ids, g_bary, W, H):
         ndc = ndc.to(self.device, torch.float32).contiguous()
         B = ndc.shape[0]

@@ -343,6 +343,22 @@ def run_raster(args, rank, local_rank, world, dist):
     ms_f = timed(fwd, args.steps)
     bary, ids, z = out['r']
     ms_b = timed(lambda: mesh.rasterize_backward(ndc, bary, ids, g_bary, W, H), args.steps)
+    # fused renderer (normals -> clip transform -> rasterise -> interpolate -> diffuse Phong), pose_3d's view_f camera
+    from tf_mesh_renderer import camera_utils as cu
+    wv = ndc * torch.tensor([1.0, 1.0, 2.0], device=dev)                      # world-space bodies around the origin
+    eye = torch.tensor([[0.0, -0.35, -4.0]], device=dev).expand(B, 3)
+    clip_tf = torch.matmul(cu.perspective(W / H, torch.full((B,), 30.0, device=dev), torch.full((B,), 0.05, device=dev),
+                                          torch.full((B,), 100.0, device=dev)),
+                           cu.look_at(eye, torch.zeros((B, 3), device=dev), torch.tensor([[0.0, 1.0, 0.0]], device=dev).expand(B, 3)))
+    lights = torch.tensor([[[0.0, 1.0, -4.0]]], device=dev).expand(B, 1, 3).contiguous()
+    li = torch.ones((B, 1, 3), device=dev)
+    nrm = torch.empty_like(wv)
+
+    def render():
+        mesh.normals(wv, out=nrm)
+        out['img'] = mesh.render_diffuse(wv, nrm, clip_tf, lights, li, W, H)
+
+    ms_r = timed(render, args.steps)
     # e2e: host vertices in, host barycentrics/ids out
     hv = ndc.cpu().pin_memory()
     hb = torch.empty((B, H, W, 3), dtype=torch.float32).pin_memory()
@@ -374,6 +390,8 @@ def run_raster(args, rank, local_rank, world, dist):
                                    '320x240 per GPU per step -> barycentrics, triangle ids, depth' % B},
             'clocks': sampler.summary(), 'gpu_launches': 4 * args.steps,
             'backward_ms_per_step': ms_b, 'backward_images_per_s': world * B / (ms_b * 1e-3),
+            'render_ms_per_step': ms_r, 'render_images_per_s': world * B / (ms_r * 1e-3),
+            'render_covered_fraction': float((out['img'][..., 3] > 0.5).float().mean()),
             'covered_fraction': float((bary.sum(-1) > 0.5).float().mean()),
             'roofline': {'bound': 'hbm', 'kernel': 'raster_clear + raster_tri + raster_big + raster_resolve (whole step)',
                          'achieved': out_bytes / (ms_f * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',

@@ -252,6 +252,19 @@ int32_t smplb_rasterize_backward(const smplb_mesh* m, int32_t B, const float* nd
  * (a CTA holds one sample's vertices and normals in shared memory); V <= 9386. */
 int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const float* verts, float* normals, void* stream);
 
+/* Fused renderer for the path pose_3d drives (deps/pose_3d/utils.py:20-58 -> mesh_renderer.mesh_renderer without
+ * specular terms, deps/tf_mesh_renderer/mesh_renderer.py:197-401): clip transform + perspective divide
+ * (rasterize_triangles.py:73-86), rasterisation, perspective-correct interpolation of normals / positions /
+ * diffuse colours (:119-164) and diffuse Phong shading (mesh_renderer.py:84-118,158-162) in one pass; only the
+ * RGBA image [B,H,W,4] (rows reversed as tf.reverse does, :162) is written.  verts/normals [B,V,3], diffuse
+ * [B,V,3] or NULL (= ones), clip_transforms [B,4,4] row-major (perspective x look_at), lights [B,L,3] x2,
+ * ambient [B,3] or NULL. */
+size_t smplb_render_workspace_bytes(const smplb_mesh* m, int32_t B, int32_t W, int32_t H);
+int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const float* verts, const float* normals,
+                             const float* diffuse, const float* clip_transforms, const float* light_positions,
+                             const float* light_intensities, int32_t L, const float* ambient, int32_t W, int32_t H,
+                             float* rgba, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- Per-sample operators either side of the path ---------------------------------
  * add_axis_angle_rotations (deps/pose_3d/utils.py:170-199): rv1, rv2 [N,3] -> axis-angle of "rv2 then rv1". */
 int32_t smplb_add_axis_angle(int32_t N, const float* rv1, const float* rv2, float* out, void* stream);
