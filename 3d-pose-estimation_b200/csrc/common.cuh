@@ -102,6 +102,8 @@ struct smplb_mesh {
   int* tri;        // [T][3]
   int* vptr;       // [V+1] CSR vertex -> incident (triangle, corner), ascending triangle id
   int* vent;       // [3T]  triangle * 3 + corner
+  uint32_t* vpair; // [3T]  per CSR entry: the two other vertices of the face, in winding order after this corner
+                   //       (lo 16 bits = next, hi 16 bits = next-next); only when V <= 65536, else NULL
 };
 
 namespace smplb {

@@ -16,7 +16,7 @@
 
 namespace smplb {
 
-constexpr int NM_THREADS = 512;
+constexpr int NM_THREADS = 1024;
 
 __device__ __forceinline__ void face_cross(const float* __restrict__ v, const int* __restrict__ tri, int t, float n[3]) {
   const int a = 3 * __ldg(tri + 3 * t), b = 3 * __ldg(tri + 3 * t + 1), c = 3 * __ldg(tri + 3 * t + 2);
@@ -38,53 +38,63 @@ __device__ __forceinline__ void block_sum3(float x[3], float (*red)[3]) {
   if (lane == 0) { red[warp][0] = x[0]; red[warp][1] = x[1]; red[warp][2] = x[2]; }
   __syncthreads();
   float s[3] = {0.f, 0.f, 0.f};
+#pragma unroll 8
   for (int w = 0; w < NM_THREADS / 32; ++w) { s[0] += red[w][0]; s[1] += red[w][1]; s[2] += red[w][2]; }
   x[0] = s[0]; x[1] = s[1]; x[2] = s[2];
 }
 
+// v2: one pass over the face CORNERS instead of a face pass plus a corner pass.  (b-a)x(c-a) is the same vector from
+// any corner of the face, so the vertex thread takes its own position from registers and the two other vertices
+// from one packed 4-byte table entry (mesh->vpair); the per-coordinate sum of squares over faces (:109-110) is one
+// third of the sum over corners.  The unscaled vertex sums wait in shared memory for that scale.
 __global__ void __launch_bounds__(NM_THREADS, 1)
 normals_kernel(int B, int V, int T, int max_order, const int* __restrict__ tri, const int* __restrict__ vptr,
-               const int* __restrict__ vent, const float* __restrict__ verts, float* __restrict__ normals) {
+               const uint32_t* __restrict__ vpair, const float* __restrict__ verts, float* __restrict__ normals) {
   extern __shared__ __align__(16) float nm_smem[];
   float* sv = nm_smem;              // [3V] vertices of the sample
-  float* sn = nm_smem + 3 * V;      // [3V] its normals (unsigned)
+  float* sn = nm_smem + 3 * V;      // [3V] vertex sums, then the (unsigned) normals
   __shared__ float red[NM_THREADS / 32][3];
   const int n3 = 3 * V;
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
     const float* src = verts + (size_t)b * n3;
-    float acc[3] = {0.f, 0.f, 0.f};
     __syncthreads();   // previous sample fully written out
     for (int i = threadIdx.x; i < n3; i += NM_THREADS) sv[i] = __ldcs(src + i);
     __syncthreads();
-    for (int v = threadIdx.x; v < V; v += NM_THREADS) { acc[0] += sv[3 * v]; acc[1] += sv[3 * v + 1]; acc[2] += sv[3 * v + 2]; }
+    float acc[3] = {0.f, 0.f, 0.f}, sq[3] = {0.f, 0.f, 0.f};
+    for (int v = threadIdx.x; v < V; v += NM_THREADS) {
+      const float ax = sv[3 * v], ay = sv[3 * v + 1], az = sv[3 * v + 2];
+      acc[0] += ax; acc[1] += ay; acc[2] += az;
+      const int e0 = __ldg(vptr + v), e1 = __ldg(vptr + v + 1);
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll 4
+      for (int e = e0; e < e1; ++e) {
+        const uint32_t pr = __ldg(vpair + e);
+        const int p = 3 * (int)(pr & 0xffffu), q = 3 * (int)(pr >> 16);
+        const float e1x = sv[p] - ax, e1y = sv[p + 1] - ay, e1z = sv[p + 2] - az;
+        const float e2x = sv[q] - ax, e2y = sv[q + 1] - ay, e2z = sv[q + 2] - az;
+        const float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;   // :107
+        s0 += nx; s1 += ny; s2 += nz;
+        sq[0] += nx * nx; sq[1] += ny * ny; sq[2] += nz * nz;
+      }
+      sn[3 * v] = s0; sn[3 * v + 1] = s1; sn[3 * v + 2] = s2;
+    }
     block_sum3(acc, red);
     const float mean[3] = {acc[0] / (float)V, acc[1] / (float)V, acc[2] / (float)V};     // :116-117
-    // per-coordinate scale over the triangle axis (:109-110)
-    float sq[3] = {0.f, 0.f, 0.f};
-    for (int t = threadIdx.x; t < T; t += NM_THREADS) {
-      float n[3];
-      face_cross(sv, tri, t, n);
-      sq[0] += n[0] * n[0]; sq[1] += n[1] * n[1]; sq[2] += n[2] * n[2];
-    }
     block_sum3(sq, red);
-    const float sc[3] = {rsqrtf(fmaxf(sq[0], 1e-12f)), rsqrtf(fmaxf(sq[1], 1e-12f)), rsqrtf(fmaxf(sq[2], 1e-12f))};
+    // per-coordinate scale over the triangle axis (:109-110); every face was visited from its three corners
+    const float third = 1.0f / 3.0f;
+    const float sc[3] = {rsqrtf(fmaxf(sq[0] * third, 1e-12f)), rsqrtf(fmaxf(sq[1] * third, 1e-12f)),
+                         rsqrtf(fmaxf(sq[2] * third, 1e-12f))};
     float pad[3] = {0.f, 0.f, 0.f};
     if (V < T) face_cross(sv, tri, V, pad);   // the pad index n_vertices is a real face (header)
-    // vertex normals: sum of the incident (scaled) face normals (+ pads), normalised over xyz (:112-114)
     float sd[3] = {0.f, 0.f, 0.f};
     for (int v = threadIdx.x; v < V; v += NM_THREADS) {
-      const int e0 = __ldg(vptr + v), e1 = __ldg(vptr + v + 1);
-      float s[3] = {0.f, 0.f, 0.f};
-      for (int e = e0; e < e1; ++e) {
-        float n[3];
-        face_cross(sv, tri, __ldg(vent + e) / 3, n);
-        s[0] += n[0]; s[1] += n[1]; s[2] += n[2];
-      }
-      const float np = (float)(max_order - (e1 - e0));
-      s[0] = (s[0] + np * pad[0]) * sc[0];
-      s[1] = (s[1] + np * pad[1]) * sc[1];
-      s[2] = (s[2] + np * pad[2]) * sc[2];
-      const float inv = rsqrtf(fmaxf(s[0] * s[0] + s[1] * s[1] + s[2] * s[2], 1e-12f));
+      const float np = (float)(max_order - (__ldg(vptr + v + 1) - __ldg(vptr + v)));
+      float s[3];
+      s[0] = (sn[3 * v] + np * pad[0]) * sc[0];
+      s[1] = (sn[3 * v + 1] + np * pad[1]) * sc[1];
+      s[2] = (sn[3 * v + 2] + np * pad[2]) * sc[2];
+      const float inv = rsqrtf(fmaxf(s[0] * s[0] + s[1] * s[1] + s[2] * s[2], 1e-12f));     // :112-114
       s[0] *= inv; s[1] *= inv; s[2] *= inv;
       sn[3 * v] = s[0]; sn[3 * v + 1] = s[1]; sn[3 * v + 2] = s[2];
       sd[0] += (sv[3 * v] - mean[0]) * s[0];                                               // :118-119
@@ -108,6 +118,7 @@ extern "C" int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const floa
   if (B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_mesh_normals: negative batch");
   if (B == 0) return SMPLB_OK;
   if (!verts || !normals) return fail(SMPLB_E_INVALID_ARG, "smplb_mesh_normals: null pointer");
+  if (m->T <= 0 || !m->vpair) return fail(SMPLB_E_UNSUPPORTED, "smplb_mesh_normals: mesh without triangles");
   const size_t smem = (size_t)6 * m->V * sizeof(float);
   if (smem > 220 * 1024) return fail(SMPLB_E_UNSUPPORTED, "smplb_mesh_normals: more than 9386 vertices per mesh");
   static int n_sm[64] = {};
@@ -119,7 +130,7 @@ extern "C" int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const floa
     n_sm[dev] = v;
   }
   const int grid = B < n_sm[dev] ? B : n_sm[dev];
-  normals_kernel<<<grid, NM_THREADS, smem, (cudaStream_t)stream>>>(B, m->V, m->T, m->max_order, m->tri, m->vptr, m->vent,
+  normals_kernel<<<grid, NM_THREADS, smem, (cudaStream_t)stream>>>(B, m->V, m->T, m->max_order, m->tri, m->vptr, m->vpair,
                                                                    verts, normals);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;

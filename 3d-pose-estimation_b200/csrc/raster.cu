@@ -243,7 +243,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   cudaGetDevice(&prev);
   SMPLB_CUDA_CHECK(cudaSetDevice(device));
   smplb_mesh* m = new smplb_mesh();
-  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr;
+  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr; m->vpair = nullptr;
   // vertex_faces_from_face_verts (deps/pose_3d/utils.py:130-149): adjacency lists padded to the maximum vertex order
   m->max_order = 0;
   for (int v = 0; v < V; ++v) m->max_order = std::max(m->max_order, vptr[v + 1] - vptr[v]);
@@ -253,9 +253,20 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   if (e == cudaSuccess && T > 0) e = cudaMemcpy(m->tri, triangles_host, sizeof(int) * 3 * (size_t)T, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(m->vptr, vptr.data(), sizeof(int) * (size_t)(V + 1), cudaMemcpyHostToDevice);
   if (e == cudaSuccess && T > 0) e = cudaMemcpy(m->vent, vent.data(), sizeof(int) * 3 * (size_t)T, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && T > 0 && V <= 65536) {
+    // (b - a) x (c - a) is the same vector from whichever corner it is taken: store, per CSR entry, the next two
+    // vertices after this corner so that the normals kernel needs one 4-byte load per incident face
+    std::vector<uint32_t> vpair((size_t)3 * T);
+    for (size_t i = 0; i < vent.size(); ++i) {
+      const int t = vent[i] / 3, k = vent[i] % 3;
+      vpair[i] = (uint32_t)triangles_host[3 * t + (k + 1) % 3] | ((uint32_t)triangles_host[3 * t + (k + 2) % 3] << 16);
+    }
+    e = cudaMalloc((void**)&m->vpair, sizeof(uint32_t) * 3 * (size_t)T);
+    if (e == cudaSuccess) e = cudaMemcpy(m->vpair, vpair.data(), sizeof(uint32_t) * 3 * (size_t)T, cudaMemcpyHostToDevice);
+  }
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
-    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent);
+    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair);
     delete m;
     return fail(SMPLB_E_CUDA, std::string("smplb_mesh_create: ") + cudaGetErrorString(e));
   }
@@ -265,7 +276,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
 
 extern "C" int32_t smplb_mesh_destroy(smplb_mesh* m) {
   if (!m) return SMPLB_OK;
-  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent);
+  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair);
   delete m;
   return SMPLB_OK;
 }
