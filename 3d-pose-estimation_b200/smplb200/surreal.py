@@ -1,0 +1,44 @@
+"""SURREAL `*_info.mat` -> device batches for the SMPL path.
+
+Host-side I/O (scipy.io), mirroring the annotation half of read_maps_poses_images_surreal
+(deps/pose_3d/data_helpers.py:43-89): `pose [72,T]`, `shape [10,T]`, `joints2D [2,24,T]`, `zrot [T,1]` -> arrays with
+time first, the horizontal flip of the 2D ground truth (:66-67), the validity mask and the every-2nd-frame
+subsampling (:80-87).  The heat-map / JPEG half of that function feeds the CNN encoder and is out of scope.
+`gt_batch` then runs what the reference's graph does with these annotations before the losses
+(pose_model_3d.py:371-372 rotate_global_pose, :177-181 SMPL) on the kernels."""
+import numpy as np
+import torch
+
+from . import api
+
+
+def read_info_surreal(info_file, img_size_x=320, mask=None, skip=2):
+    """Returns dict(poses [N,72], shapes [N,10], joints2d [N,24,2], zrot [N]) float32 (data_helpers.py:58-88)."""
+    import scipy.io
+    info = scipy.io.loadmat(info_file)
+    poses = np.transpose(info['pose'], (1, 0))                                   # :62
+    shapes = np.transpose(info['shape'], (1, 0))                                 # :63
+    joints2d = np.transpose(info['joints2D'], (2, 1, 0)).astype(np.float32)      # :65
+    joints2d[:, :, 0] = img_size_x - joints2d[:, :, 0]                           # :67 (SURREAL images are mirrored)
+    zrot = np.squeeze(np.array(info['zrot']), axis=1) if np.ndim(info['zrot']) == 2 else np.array(info['zrot'])   # :68
+    if mask is not None:                                                         # :80-82
+        mask = np.asarray(mask, dtype=bool)
+        poses, shapes, joints2d, zrot = poses[mask], shapes[mask], joints2d[mask], zrot[mask]
+    poses, shapes, joints2d, zrot = poses[::skip], shapes[::skip], joints2d[::skip], zrot[::skip]   # :84-87
+    return dict(poses=np.ascontiguousarray(poses, dtype=np.float32), shapes=np.ascontiguousarray(shapes, dtype=np.float32),
+                joints2d=np.ascontiguousarray(joints2d, dtype=np.float32),
+                zrot=np.ascontiguousarray(zrot, dtype=np.float32).reshape(-1))
+
+
+def gt_batch(model, ann, device=None, want_verts=True):
+    """Annotations -> ground-truth tensors on the GPU: pose with the y-up global rotation (utils.py:152-167 on the
+    kernel), SMPL meshes / posed joints (batch_smpl.py), 2D joints flipped to the renderer's y-up convention
+    (pose_model_3d.py:196-197)."""
+    dev = model.device if device is None else device
+    theta = api.rotate_global_pose(torch.from_numpy(ann['poses']).to(dev), torch.from_numpy(ann['zrot']).to(dev))
+    beta = torch.from_numpy(ann['shapes']).to(dev)
+    out = model.forward(beta, theta, want_verts=want_verts, want_kp=False, want_Rs=False)
+    j2d = torch.from_numpy(ann['joints2d']).to(dev)
+    j2d_flipped = j2d * torch.tensor([1.0, -1.0], device=dev) + torch.tensor([0.0, 240.0], device=dev)
+    return dict(theta=theta, beta=beta, joints3d=out['joints'], verts=out.get('verts'), joints2d=j2d,
+                joints2d_flipped=j2d_flipped)
