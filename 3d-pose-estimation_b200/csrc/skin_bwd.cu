@@ -17,10 +17,19 @@ constexpr int GA_WARPS = 8;                 // 3 joints each
 constexpr int GA_PITCH = 3 * SK_VT + 1;     // 385 floats
 constexpr int GA_TILE = 3 * SK_VT;          // 384 floats of a row per vertex tile
 
+constexpr int GA_MAXENT = 1024;             // (vertex, weight) pairs of one vertex tile staged in smem (128 x <= 8 nnz)
+
 struct GaSmem {
   float gy[2][GA_SAMPLES][GA_PITCH];
   float vp[2][GA_SAMPLES][GA_PITCH];
+  float2 ent[2][GA_MAXENT];                 // the tile's table entries: no dependent global load in the inner loop
+  int ptr[SK_NVT * (NJ + 1)];               // the whole ent_ptr table (54 x 25), loaded once
 };
+
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
 
 __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
   const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -36,15 +45,27 @@ skin_bwd_gA_kernel(int B, const float* __restrict__ g_verts, const float* __rest
   const int b0 = blockIdx.x * GA_SAMPLES;
   const int nrow = min(GA_SAMPLES, B - b0);
 
+  // warp w stages rows w, w+8, ...; lanes stride over the 384 floats of the row (no index division); the tile's
+  // (vertex, weight) table goes along (ent_ptr rows are contiguous: [t][0..24])
   auto prefetch = [&](int t, int buf) {
     const int nvalid = min(GA_TILE, NV3 - t * GA_TILE);
-    for (int idx = tid; idx < nrow * GA_TILE; idx += GA_WARPS * 32) {
-      const int s = idx / GA_TILE, o = idx - s * GA_TILE;
-      if (o < nvalid) cp_async4(&sm.gy[buf][s][o], g_verts + (size_t)(b0 + s) * NV3 + (size_t)t * GA_TILE + o);
-      cp_async4(&sm.vp[buf][s][o], vposed + (size_t)(b0 + s) * VPP + (size_t)t * GA_TILE + o);
+    for (int s = warp; s < nrow; s += GA_WARPS) {
+      const float* gsrc = g_verts + (size_t)(b0 + s) * NV3 + (size_t)t * GA_TILE;
+      const float* vsrc = vposed + (size_t)(b0 + s) * VPP + (size_t)t * GA_TILE;
+#pragma unroll 4
+      for (int o = lane; o < GA_TILE; o += 32) {
+        if (o < nvalid) cp_async4(&sm.gy[buf][s][o], gsrc + o);
+        cp_async4(&sm.vp[buf][s][o], vsrc + o);
+      }
     }
+    const int e0 = sm.ptr[t * (NJ + 1)], e1 = sm.ptr[t * (NJ + 1) + NJ];
+    if (e1 - e0 <= GA_MAXENT)
+      for (int e = tid; e < e1 - e0; e += GA_WARPS * 32) cp_async8(&sm.ent[buf][e], ent + e0 + e);
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
+
+  for (int i = tid; i < SK_NVT * (NJ + 1); i += GA_WARPS * 32) sm.ptr[i] = __ldg(ent_ptr + i);
+  __syncthreads();
 
   float acc[3][12];
 #pragma unroll
@@ -64,12 +85,15 @@ skin_bwd_gA_kernel(int B, const float* __restrict__ g_verts, const float* __rest
     __syncthreads();
     const float* gy = sm.gy[buf][lane];
     const float* vp = sm.vp[buf][lane];
-    const int* ptr = ent_ptr + t * (NJ + 1) + 3 * warp;
+    const int tb = sm.ptr[t * (NJ + 1)];
+    const bool staged = sm.ptr[t * (NJ + 1) + NJ] - tb <= GA_MAXENT;   // dense models read the table from global
 #pragma unroll
     for (int jj = 0; jj < 3; ++jj) {
-      const int e0 = __ldg(ptr + jj), e1 = __ldg(ptr + jj + 1);
+      const int e0 = sm.ptr[t * (NJ + 1) + 3 * warp + jj] - (staged ? tb : 0);
+      const int e1 = sm.ptr[t * (NJ + 1) + 3 * warp + jj + 1] - (staged ? tb : 0);
+#pragma unroll 2
       for (int e = e0; e < e1; ++e) {
-        const float2 en = __ldg(ent + e);          // uniform across the warp
+        const float2 en = staged ? sm.ent[buf][e] : __ldg(ent + e);          // uniform across the warp
         const int v = __float_as_int(en.y);
         const float w = en.x;
         const float x = vp[v], y = vp[SK_VT + v], z = vp[2 * SK_VT + v];

@@ -164,6 +164,7 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           if (sl < ks1) ksrc[p] = __ldg(kpc_src + sl);
         }
       }
+      float gyn[SK_S / 2][3];   // MODE 1: next group's g_verts (prefetch)
       for (int g = g0; g < g1; ++g, ++it) {
         const int sv = it % SKT_VSTAGES, ac = it & 1;
         const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)ac * SK_N + half * (SK_S / 2) * 12;
@@ -171,14 +172,24 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           // ---- adjoint wrt v_posed ----
           const int v = vt * SK_VT + l4;
           const bool vok = v < NV;
+          // g_verts of this thread's vertex for its 8 samples: fetched one group ahead (gyn), so the DRAM latency
+          // hides behind the previous group's work instead of stalling the first use
+          auto load_gy = [&](int gg, float (&dst)[SK_S / 2][3]) {
+#pragma unroll
+            for (int k = 0; k < SK_S / 2; ++k) {
+              const int b = gg * SK_S + half * (SK_S / 2) + k;
+              const float* src = vposed + (size_t)(b < B ? b : B - 1) * NV3 + 3 * (size_t)(vok ? v : 0);
+#pragma unroll
+              for (int r = 0; r < 3; ++r) dst[k][r] = vok ? __ldg(src + r) : 0.f;
+            }
+          };
           float gy[SK_S / 2][3];
+          if (g == g0) load_gy(g, gyn);
 #pragma unroll
-          for (int k = 0; k < SK_S / 2; ++k) {
-            const int b = g * SK_S + half * (SK_S / 2) + k;
-            const float* src = vposed + (size_t)(b < B ? b : B - 1) * NV3 + 3 * (size_t)(vok ? v : 0);
+          for (int k = 0; k < SK_S / 2; ++k)
 #pragma unroll
-            for (int r = 0; r < 3; ++r) gy[k][r] = vok ? __ldg(src + r) : 0.f;
-          }
+            for (int r = 0; r < 3; ++r) gy[k][r] = gyn[k][r];
+          if (g + 1 < g1) load_gy(g + 1, gyn);
           mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);
           tc_fence_after();
 #pragma unroll
@@ -197,24 +208,46 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
             }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const int b = g * SK_S + half * (SK_S / 2) + bt * 4 + k;
               const float* t = T + 12 * k;
               const float* gg = gy[bt * 4 + k];
-              if (b < B) {
+              float* orow = sm.out[half * (SK_S / 2) + bt * 4 + k] + l4;     // internal column order: c * 128 + vertex
 #pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                  const float val = fmaf(t[c], gg[0], fmaf(t[4 + c], gg[1], t[8 + c] * gg[2]));   // (T.R^T gy)[c]
-                  const float hi = tf32_rna_dev(val);
-                  const int n = vt * (3 * SK_VT) + c * SK_VT + l4;
-                  verts[gimg_off(b, n, 0)] = hi;
-                  verts[gimg_off(b, n, 1)] = tf32_rna_dev(val - hi);
-                }
-              }
+              for (int c = 0; c < 3; ++c)
+                orow[c * SK_VT] = fmaf(t[c], gg[0], fmaf(t[4 + c], gg[1], t[8 + c] * gg[2]));   // (T.R^T gy)[c]
             }
           }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&sm.acc_empty[ac]);
+          named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging complete
+          // copy-out as the TF32 hi/lo operand image of the transposed blend GEMM (gimg_off): for every k-block of
+          // 32 columns and 16-byte K-chunk the group's 16 samples are 256 contiguous bytes, so a warp stores two
+          // full 256-byte runs per instruction (v1 scattered 4-byte stores: 5.7 ms, now bound by the 16 GB it moves)
+          {
+            const int et = (int)threadIdx.x - 64;
+            const int i = et & 15;                                   // sample row of the group
+            const int b = g * SK_S + i;
+            float* gbase = verts + (size_t)(b / BL_BM) * ((size_t)BB_NKB * BB_GSTAGE) + (size_t)(b % BL_BM) * 4;
+            if (b < B) {
+#pragma unroll
+              for (int p = 0; p < (3 * SK_VT / 4) / 16; ++p) {       // 96 four-column chunks / 16 per pass
+                const int ch = (et >> 4) + 16 * p;                   // chunk index inside the tile: 0..95
+                const int nl = ch * 4;                               // local column
+                const float2 v01 = *reinterpret_cast<const float2*>(&sm.out[i][nl]);
+                const float2 v23 = *reinterpret_cast<const float2*>(&sm.out[i][nl + 2]);
+                float4 hi, lo;
+                hi.x = tf32_rna_dev(v01.x); lo.x = tf32_rna_dev(v01.x - hi.x);
+                hi.y = tf32_rna_dev(v01.y); lo.y = tf32_rna_dev(v01.y - hi.y);
+                hi.z = tf32_rna_dev(v23.x); lo.z = tf32_rna_dev(v23.x - hi.z);
+                hi.w = tf32_rna_dev(v23.y); lo.w = tf32_rna_dev(v23.y - hi.w);
+                const int n = vt * (3 * SK_VT) + nl;                 // global internal column
+                float* dst = gbase + (size_t)(n / BB_KB) * BB_GSTAGE + (size_t)((n % BB_KB) / 4) * (BL_BM * 4);
+                __stcs(reinterpret_cast<float4*>(dst), hi);
+                __stcs(reinterpret_cast<float4*>(dst + (BB_KB / 4) * BL_BM * 4), lo);
+              }
+            }
+          }
+          named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging reusable
           continue;
         }
         mbar_wait(&sm.vfull[sv], (it / SKT_VSTAGES) & 1);   // v_posed rows of this group have landed
