@@ -13,7 +13,8 @@
 namespace smplb {
 
 constexpr int GA_SAMPLES = 32;
-constexpr int GA_WARPS = 8;                 // 3 joints each
+constexpr int GA_JW = 8;                    // joint triples
+constexpr int GA_WARPS = 16;                // two warps per joint triple: even / odd table entries
 constexpr int GA_PITCH = 3 * SK_VT + 1;     // 385 floats
 constexpr int GA_TILE = 3 * SK_VT;          // 384 floats of a row per vertex tile
 
@@ -42,6 +43,7 @@ skin_bwd_gA_kernel(int B, const float* __restrict__ g_verts, const float* __rest
   extern __shared__ __align__(16) unsigned char smem_raw[];
   GaSmem& sm = *reinterpret_cast<GaSmem*>(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int jw = warp & (GA_JW - 1), hf = warp >> 3;   // joint triple, entry parity
   const int b0 = blockIdx.x * GA_SAMPLES;
   const int nrow = min(GA_SAMPLES, B - b0);
 
@@ -89,10 +91,10 @@ skin_bwd_gA_kernel(int B, const float* __restrict__ g_verts, const float* __rest
     const bool staged = sm.ptr[t * (NJ + 1) + NJ] - tb <= GA_MAXENT;   // dense models read the table from global
 #pragma unroll
     for (int jj = 0; jj < 3; ++jj) {
-      const int e0 = sm.ptr[t * (NJ + 1) + 3 * warp + jj] - (staged ? tb : 0);
-      const int e1 = sm.ptr[t * (NJ + 1) + 3 * warp + jj + 1] - (staged ? tb : 0);
+      const int e0 = sm.ptr[t * (NJ + 1) + 3 * jw + jj] - (staged ? tb : 0);
+      const int e1 = sm.ptr[t * (NJ + 1) + 3 * jw + jj + 1] - (staged ? tb : 0);
 #pragma unroll 2
-      for (int e = e0; e < e1; ++e) {
+      for (int e = e0 + hf; e < e1; e += 2) {
         const float2 en = staged ? sm.ent[buf][e] : __ldg(ent + e);          // uniform across the warp
         const int v = __float_as_int(en.y);
         const float w = en.x;
@@ -109,13 +111,26 @@ skin_bwd_gA_kernel(int B, const float* __restrict__ g_verts, const float* __rest
     }
     __syncthreads();
   }
-  if (lane < nrow) {
-    float4* o = reinterpret_cast<float4*>(g_A + ((size_t)(b0 + lane) * NJ + 3 * warp) * 12);
+  // combine the two entry-parity halves in a fixed order (even + odd): the odd warps hand their sums over through
+  // the (now idle) staging buffer
+  float* xch = &sm.gy[0][0][0];   // [8 triples][36][32 lanes]
+  if (hf == 1) {
 #pragma unroll
     for (int jj = 0; jj < 3; ++jj)
 #pragma unroll
-      for (int r = 0; r < 3; ++r)
-        o[jj * 3 + r] = make_float4(acc[jj][4 * r], acc[jj][4 * r + 1], acc[jj][4 * r + 2], acc[jj][4 * r + 3]);
+      for (int e = 0; e < 12; ++e) xch[(jw * 36 + jj * 12 + e) * 32 + lane] = acc[jj][e];
+  }
+  __syncthreads();
+  if (hf == 0 && lane < nrow) {
+    float4* o = reinterpret_cast<float4*>(g_A + ((size_t)(b0 + lane) * NJ + 3 * jw) * 12);
+#pragma unroll
+    for (int jj = 0; jj < 3; ++jj)
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float* x = xch + (jw * 36 + jj * 12 + 4 * r) * 32 + lane;
+        o[jj * 3 + r] = make_float4(acc[jj][4 * r] + x[0], acc[jj][4 * r + 1] + x[32], acc[jj][4 * r + 2] + x[64],
+                                    acc[jj][4 * r + 3] + x[96]);
+      }
   }
 }
 
