@@ -30,3 +30,45 @@ def allreduce_scalars(t, group=None):
 def global_loss(fitter_loss, group=None):
     """[uncapped share, capped, gate] of one rank -> global uncapped loss (device tensor, 1 element)."""
     return allreduce_scalars(fitter_loss[:1].clone(), group)
+
+
+class SideStreamAllReduce:
+    """Loss-scalar all-reduce off the critical path: the sum of step k runs on a side stream while
+    the kernels of step k+1 run on the main stream; the value is only consumed for logging / stop criteria.  Two
+    slots alternate, so the main stream waits for the reduction of step k-2 (long finished) before it overwrites
+    that slot."""
+
+    def __init__(self, n, device, group=None):
+        self.buf = torch.zeros((2, n), dtype=torch.float32, device=device)
+        self.group = group
+        self.k = 0
+        self.cuda = torch.device(device).type == 'cuda'
+        self.side = torch.cuda.Stream(device=device) if self.cuda else None
+        self.done = [None, None]
+
+    def push(self, scalars):
+        """Queue the all-reduce of `scalars` (n floats on the device); returns the slot tensor it will land in."""
+        slot = self.k & 1
+        self.k += 1
+        if not self.cuda:
+            self.buf[slot].copy_(scalars)
+            allreduce_scalars(self.buf[slot], self.group)
+            return self.buf[slot]
+        main = torch.cuda.current_stream(self.buf.device)
+        if self.done[slot] is not None:
+            main.wait_event(self.done[slot])
+        self.buf[slot].copy_(scalars)
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            allreduce_scalars(self.buf[slot], self.group)
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+        self.done[slot] = ev
+        return self.buf[slot]
+
+    def latest(self):
+        """Synchronise with the most recent reduction and return its value (host sync only here)."""
+        slot = (self.k - 1) & 1
+        if self.cuda and self.done[slot] is not None:
+            self.done[slot].synchronize()
+        return self.buf[slot]

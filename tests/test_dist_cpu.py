@@ -30,6 +30,11 @@ def _worker(rank, world, port, n, out):
     a, b = sd.shard_range(n, rank, world)
     share = torch.tensor([0.024 * float((err[a:b] ** 2).sum()) / (n * 48), 0.0, 1.0], dtype=torch.float64)
     g = sd.global_loss(share)
+    # the side-stream helper (CPU path: synchronous) gives the same sum, slot after slot
+    red = sd.SideStreamAllReduce(1, 'cpu')
+    for k in range(3):
+        red.push(share[:1].float() * (k + 1))
+    assert abs(float(red.latest()[0]) - 3 * float(g[0])) <= 1e-5 * abs(float(g[0]))
     if rank == 0:
         np.save(out, np.array([float(g[0]), 0.024 * float((err ** 2).mean())]))
     dist.barrier()
