@@ -3,9 +3,11 @@
 // reduces 6890 vertices to 288 numbers per sample.  (The other half, g_vposed = T^T g_verts, is the MODE 1
 // instantiation of skin_tc_kernel.)
 //
-// Mapping: lane = sample (32 samples per CTA), warp w owns joints 3w..3w+2 and keeps their 36 accumulators in
-// registers for the whole sweep over the 54 vertex tiles; the (vertex, weight) pairs of every (tile, joint)
-// come from a table built at model creation, so the summation order is fixed (deterministic, no atomics).
+// Mapping: lane = sample (32 samples per CTA); 16 warps = 8 joint triples x entry parity: a warp keeps the 36
+// accumulators of its three joints in registers for the whole sweep over the 54 vertex tiles and takes every
+// second (vertex, weight) pair of each (tile, joint) list; the two parities are combined in a fixed order at the
+// end.  The lists come from a table built at model creation (staged in smem per tile), so the summation order is
+// fixed (deterministic, no atomics).
 // Tiles of g_verts / v_posed rows are staged through shared memory with cp.async (double buffered); the row
 // pitch is odd so that lane = sample reads are bank-conflict free.
 #include "common.cuh"

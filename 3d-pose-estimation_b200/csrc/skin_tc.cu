@@ -41,9 +41,10 @@ struct SktSmem {
 };
 
 // MODE 0: forward (above).  MODE 1: adjoint wrt v_posed, g_vposed[b,v] = T[b,v][:3,:3]^T g_verts[b,v]: same
-// weight-blend MMA; the epilogue reads g_verts straight from global (stride-3 loads, prefetched for the whole
-// group before the accumulator is awaited) and writes the result as the TF32 hi/lo A-operand image of the
-// transposed blend GEMM (blend_bwd.cu); `vposed` = g_verts [B,6890,3], `verts` = that image.
+// weight-blend MMA; the epilogue reads g_verts straight from global (stride-3 loads, fetched ONE GROUP AHEAD so
+// the DRAM latency hides behind the previous group), stages the result in smem and writes it as the TF32 hi/lo
+// A-operand image of the transposed blend GEMM (blend_bwd.cu) in 256-byte runs; `vposed` = g_verts [B,6890,3],
+// `verts` = that image.
 template <int MODE>
 __global__ void __launch_bounds__(SKT_THREADS, 1)
 skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vposed,
