@@ -94,6 +94,7 @@ struct smplb_model {
   void* tmap_cache;       // host-side cache of TMA descriptors (blend_tc.cu)
 };
 
+#define NM_BIG_ORDER 16
 // Triangle mesh handle (raster.cu, normals.cu)
 struct smplb_mesh {
   int device;
@@ -102,6 +103,8 @@ struct smplb_mesh {
   int* tri;        // [T][3]
   int* vptr;       // [V+1] CSR vertex -> incident (triangle, corner), ascending triangle id
   int* vent;       // [3T]  triangle * 3 + corner
+  int* big_v;      // [n_big] vertices with more than NM_BIG_ORDER incident faces (handled by a whole warp in normals.cu)
+  int n_big;
   uint32_t* vpair; // [3T]  per CSR entry: the two other vertices of the face, in winding order after this corner
                    //       (lo 16 bits = next, hi 16 bits = next-next); only when V <= 65536, else NULL
 };

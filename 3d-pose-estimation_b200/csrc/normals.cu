@@ -49,7 +49,8 @@ __device__ __forceinline__ void block_sum3(float x[3], float (*red)[3]) {
 // third of the sum over corners.  The unscaled vertex sums wait in shared memory for that scale.
 __global__ void __launch_bounds__(NM_THREADS, 1)
 normals_kernel(int B, int V, int T, int max_order, const int* __restrict__ tri, const int* __restrict__ vptr,
-               const uint32_t* __restrict__ vpair, const float* __restrict__ verts, float* __restrict__ normals) {
+               const uint32_t* __restrict__ vpair, const int* __restrict__ big_v, int n_big,
+               const float* __restrict__ verts, float* __restrict__ normals) {
   extern __shared__ __align__(16) float nm_smem[];
   float* sv = nm_smem;              // [3V] vertices of the sample
   float* sn = nm_smem + 3 * V;      // [3V] vertex sums, then the (unsigned) normals
@@ -63,8 +64,9 @@ normals_kernel(int B, int V, int T, int max_order, const int* __restrict__ tri, 
     float acc[3] = {0.f, 0.f, 0.f}, sq[3] = {0.f, 0.f, 0.f};
     for (int v = threadIdx.x; v < V; v += NM_THREADS) {
       const float ax = sv[3 * v], ay = sv[3 * v + 1], az = sv[3 * v + 2];
-      acc[0] += ax; acc[1] += ay; acc[2] += az;
       const int e0 = __ldg(vptr + v), e1 = __ldg(vptr + v + 1);
+      if (e1 - e0 > NM_BIG_ORDER) continue;   // high-order vertex (e.g. a pole): a whole warp takes it below
+      acc[0] += ax; acc[1] += ay; acc[2] += az;
       float s0 = 0.f, s1 = 0.f, s2 = 0.f;
 #pragma unroll 4
       for (int e = e0; e < e1; ++e) {
@@ -77,6 +79,33 @@ normals_kernel(int B, int V, int T, int max_order, const int* __restrict__ tri, 
         sq[0] += nx * nx; sq[1] += ny * ny; sq[2] += nz * nz;
       }
       sn[3 * v] = s0; sn[3 * v + 1] = s1; sn[3 * v + 2] = s2;
+    }
+    // vertices with many incident faces: one warp each, lanes stride over the corners, fixed-order shuffle tree --
+    // a single thread walking an 82-face pole would keep the other 1023 waiting at the barrier
+    for (int i = threadIdx.x >> 5; i < n_big; i += NM_THREADS / 32) {
+      const int v = __ldg(big_v + i), lane = threadIdx.x & 31;
+      const float ax = sv[3 * v], ay = sv[3 * v + 1], az = sv[3 * v + 2];
+      const int e0 = __ldg(vptr + v), e1 = __ldg(vptr + v + 1);
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+      for (int e = e0 + lane; e < e1; e += 32) {
+        const uint32_t pr = __ldg(vpair + e);
+        const int p = 3 * (int)(pr & 0xffffu), q = 3 * (int)(pr >> 16);
+        const float e1x = sv[p] - ax, e1y = sv[p + 1] - ay, e1z = sv[p + 2] - az;
+        const float e2x = sv[q] - ax, e2y = sv[q + 1] - ay, e2z = sv[q + 2] - az;
+        const float nx = e1y * e2z - e1z * e2y, ny = e1z * e2x - e1x * e2z, nz = e1x * e2y - e1y * e2x;
+        s0 += nx; s1 += ny; s2 += nz;
+        sq[0] += nx * nx; sq[1] += ny * ny; sq[2] += nz * nz;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+      }
+      if (lane == 0) {
+        sn[3 * v] = s0; sn[3 * v + 1] = s1; sn[3 * v + 2] = s2;
+        acc[0] += ax; acc[1] += ay; acc[2] += az;
+      }
     }
     block_sum3(acc, red);
     const float mean[3] = {acc[0] / (float)V, acc[1] / (float)V, acc[2] / (float)V};     // :116-117
@@ -131,7 +160,7 @@ extern "C" int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const floa
   }
   const int grid = B < n_sm[dev] ? B : n_sm[dev];
   normals_kernel<<<grid, NM_THREADS, smem, (cudaStream_t)stream>>>(B, m->V, m->T, m->max_order, m->tri, m->vptr, m->vpair,
-                                                                   verts, normals);
+                                                                   m->big_v, m->n_big, verts, normals);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

@@ -23,13 +23,16 @@ __device__ __forceinline__ void add_axis_angle(const float r1[3], const float r2
   const float ldm = l[0] * m[0] + l[1] * m[1] + l[2] * m[2];
   const float cos_half_c = ca * cb - sa * sb * ldm;                                       // :186-188
   const float cr[3] = {l[1] * m[2] - l[2] * m[1], l[2] * m[0] - l[0] * m[2], l[0] * m[1] - l[1] * m[0]};
-  const float half_c = acosf(cos_half_c);                                                 // :193
-  const float sh = sinf(half_c);
+  // :189-195.  The reference takes half_c = acos(cos_half_c) and divides by sin(half_c); |sin_half_c_n| IS sin(half_c)
+  // (n is a unit vector, half_c in [0, pi]), so half_c = atan2(|s|, cos_half_c) is the same function -- evaluated this
+  // way it keeps full float precision where acos loses half of its digits (composed angles near 0 and 2*pi).
+  float sn[3];
 #pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const float sn = sa * cb * l[k] + (ca * sb * m[k] + sa * sb * cr[k]);                 // :189-191
-    out[k] = sn / sh * half_c * 2.0f;                                                     // :194-195
-  }
+  for (int k = 0; k < 3; ++k) sn[k] = sa * cb * l[k] + (ca * sb * m[k] + sa * sb * cr[k]);
+  const float sh = sqrtf(sn[0] * sn[0] + sn[1] * sn[1] + sn[2] * sn[2]);
+  const float half_c = atan2f(sh, cos_half_c);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) out[k] = sn[k] / sh * half_c * 2.0f;   // 0/0 = NaN for a composed identity, like :194
 }
 
 __global__ void add_axis_angle_kernel(int N, const float* __restrict__ rv1, const float* __restrict__ rv2,
@@ -96,11 +99,16 @@ __global__ void __launch_bounds__(128) cam_losses_kernel(int B, const float* __r
       const float w[3] = {rq[0] / nq, rq[1] / nq, rq[2] / nq};
       const float dot = u[0] * w[0] + u[1] * w[1] + u[2] * w[2];                         // :265
       const float lo = -1.0f + 1e-6f, hi = 1.0f - 1e-6f;
-      const float dc = fminf(fmaxf(dot, lo), hi);                                        // :267
-      const float ang = acosf(dc);                                                       // :268
+      // :267-268 acos(clip(dot)).  Inside the clip range the angle is taken as atan2(|u x w|, u.w) -- the same
+      // function of two unit vectors, without acos' loss of digits at dot -> 1 (where a fitted camera lives);
+      // outside, the clipped constants exactly as the float32 graph has them.
+      const float cx = u[1] * w[2] - u[2] * w[1], cy = u[2] * w[0] - u[0] * w[2], cz = u[0] * w[1] - u[1] * w[0];
+      const float sn = sqrtf(cx * cx + cy * cy + cz * cz);
+      const bool inside = dot >= lo && dot <= hi;
+      const float ang = inside ? atan2f(sn, dot) : acosf(dot > hi ? hi : lo);
       s_ang += ang * ang;
-      if (g_pos && dot >= lo && dot <= hi) {
-        const float gd = -2.0f * w_angle * ang * rsqrtf(1.0f - dc * dc);
+      if (g_pos && inside) {
+        const float gd = -2.0f * w_angle * ang / sn;                                     // d acos(x)/dx = -1/sin
         // through u = d / |d|
         const float ugw = u[0] * w[0] + u[1] * w[1] + u[2] * w[2];
 #pragma unroll

@@ -243,7 +243,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   cudaGetDevice(&prev);
   SMPLB_CUDA_CHECK(cudaSetDevice(device));
   smplb_mesh* m = new smplb_mesh();
-  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr; m->vpair = nullptr;
+  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr; m->vpair = nullptr; m->big_v = nullptr; m->n_big = 0;
   // vertex_faces_from_face_verts (deps/pose_3d/utils.py:130-149): adjacency lists padded to the maximum vertex order
   m->max_order = 0;
   for (int v = 0; v < V; ++v) m->max_order = std::max(m->max_order, vptr[v + 1] - vptr[v]);
@@ -253,6 +253,14 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   if (e == cudaSuccess && T > 0) e = cudaMemcpy(m->tri, triangles_host, sizeof(int) * 3 * (size_t)T, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(m->vptr, vptr.data(), sizeof(int) * (size_t)(V + 1), cudaMemcpyHostToDevice);
   if (e == cudaSuccess && T > 0) e = cudaMemcpy(m->vent, vent.data(), sizeof(int) * 3 * (size_t)T, cudaMemcpyHostToDevice);
+  {
+    std::vector<int> big;
+    for (int v = 0; v < V; ++v)
+      if (vptr[v + 1] - vptr[v] > NM_BIG_ORDER) big.push_back(v);
+    m->n_big = (int)big.size();
+    if (e == cudaSuccess) e = cudaMalloc((void**)&m->big_v, sizeof(int) * (big.size() ? big.size() : 1));
+    if (e == cudaSuccess && !big.empty()) e = cudaMemcpy(m->big_v, big.data(), sizeof(int) * big.size(), cudaMemcpyHostToDevice);
+  }
   if (e == cudaSuccess && T > 0 && V <= 65536) {
     // (b - a) x (c - a) is the same vector from whichever corner it is taken: store, per CSR entry, the next two
     // vertices after this corner so that the normals kernel needs one 4-byte load per incident face
@@ -266,7 +274,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   }
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
-    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair);
+    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair); cudaFree(m->big_v);
     delete m;
     return fail(SMPLB_E_CUDA, std::string("smplb_mesh_create: ") + cudaGetErrorString(e));
   }
@@ -276,7 +284,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
 
 extern "C" int32_t smplb_mesh_destroy(smplb_mesh* m) {
   if (!m) return SMPLB_OK;
-  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair);
+  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair); cudaFree(m->big_v);
   delete m;
   return SMPLB_OK;
 }

@@ -1,4 +1,4 @@
-"""Drop-in for deps/tf_smpl/batch_lbs.py (batch_skew, batch_rodrigues,
+"""Drop-in for deps/tf_smpl/batch_lbs.py (batch_skew, batch_rodrigues, batch_lrotmin,
 batch_global_rigid_transformation) on the sm_100a kernels."""
 import torch
 
@@ -17,6 +17,13 @@ def batch_skew(vec, batch_size=None):
 def batch_rodrigues(theta, name=None):
     """theta N x 3 -> N x 3 x 3 (batch_lbs.py:38-57)."""
     return api.rodrigues(theta, 0)
+
+
+def batch_lrotmin(theta, name=None):
+    """theta N x 72 -> N x 207: rotation matrices of the 23 non-root joints minus identity (batch_lbs.py:60-81)."""
+    theta = torch.as_tensor(theta, dtype=torch.float32)
+    Rs = api.rodrigues(theta[:, 3:].reshape(-1, 3).contiguous(), 0)
+    return (Rs - torch.eye(3, dtype=Rs.dtype, device=Rs.device)).reshape(-1, 207)
 
 
 def batch_global_rigid_transformation(Rs, Js, parent, rotate_base=False):

@@ -5,14 +5,16 @@ projection and 2D re-projection loss.  Only `tests/`, `__graft_entry__.smoke()`
 and `bench.py`'s cpu_baseline / `--impl reference` leg may import this module,
 and only as the checker (or the timed CPU baseline) — never the product path.
 
-PARITY UNPINNED: the reference (blzq/3D-pose-estimation) is TensorFlow-1 graph
-code; TensorFlow is not installable in this image and the reference ships no
-test, golden vector or fixture that pins this path.  The
-restatement therefore follows the reference SOURCE op for op (citations per
-function, relative to /root/reference) and is cross-checked against (i) the
-hand-derived expected values of the one example in `project.py:92-97`,
-(ii) analytic identities, (iii) an independent torch float64 twin with autograd
-(`oracle/ref_torch.py`) and finite differences.
+PARITY PIN: the reference (blzq/3D-pose-estimation) is TensorFlow-1 graph code with no test, golden vector or
+fixture for this path, and TensorFlow is not installable in this image.  The restatement is
+pinned on the REFERENCE'S OWN PYTHON FILES instead: `oracle/run_reference.py` imports them unmodified from
+/root/reference and executes them on `oracle/tfshim` (a torch-CPU stand-in for the `tensorflow` module -- TF's op
+library is substituted, the reference's statement sequence is not); `tests/golden/make_reference_golden.py` stores
+their float64 outputs and tf.gradients, and `tests/test_reference_pin.py` holds every function below to them at
+1e-12 (forward), 1e-11 (N2 helpers), 1e-8 (gradients of the torch twin).  What stays unpinned is TensorFlow's own
+float32 kernel rounding (summation order inside tf.matmul), which the tolerance of the GPU tests absorbs.
+Further anchors: (i) the hand-derived values of the one example in `project.py:92-97`, (ii) analytic identities,
+(iii) the independent torch float64 twin with autograd (`oracle/ref_torch.py`) and finite differences.
 
 All functions are dtype-generic: pass float32 arrays for the "fp32 restatement"
 (the reference runs fp32, `batch_smpl.py:17`) or float64 for the high-precision

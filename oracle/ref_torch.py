@@ -6,7 +6,8 @@ Independent torch-CPU twin of `oracle/ref_numpy.py` (same reference citations): 
 (b) in float32 with all host threads as the timed CPU baseline ("port" of the reference's TF
     CPU op sequence, including tile(W) and the [N,6890,4,4] batched matmul,
     `batch_smpl.py:120-132`) in `bench.py`.
-PARITY UNPINNED — see `oracle/ref_numpy.py` header.  Never imported by the product path.
+Pinned like `oracle/ref_numpy.py` (see its header): values and autograd gradients are held to the reference's own
+Python files run on oracle/tfshim (tests/test_reference_pin.py).  Never imported by the product path.
 """
 import math
 from types import SimpleNamespace

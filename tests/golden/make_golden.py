@@ -1,8 +1,7 @@
 """Generates tests/golden/*.npz with the float64 oracle (oracle/ref_numpy.py).
 
-PARITY UNPINNED: the reference is TF1 code that cannot be imported in this image and ships no
-golden vectors for this path, so these fixtures are outputs of the line-by-line restatement, not
-of the reference itself.  Inputs: (a) the synthetic distribution of SURVEY.md §8d, (b) 16 real
+These fixtures are outputs of the line-by-line restatement (the reference ships no golden vectors for this path);
+the fixtures produced by the reference's own files are tests/golden/reference_*.npz (make_reference_golden.py).  Inputs: (a) the synthetic distribution of SURVEY.md §8d, (b) 16 real
 SURREAL frames (pose/shape only) read from the reference's data fixture
 `data/images/01_11_c0001_info.mat` when /root/reference is present (values are data, not code).
 
