@@ -12,8 +12,31 @@ import torch
 from . import api
 
 
+def read_maps_mask_surreal(maps_file):
+    """The frame mask of a SURREAL heat-map file as data_helpers.py:44-50 forms it: squeeze(mask) AND (diffs < 250),
+    written into the mask array itself, so the dtype is the file's.  (NaN diffs compare False, :48.)  Returns
+    (mask, img_size_x = heat-map width, :57).  The heat maps themselves are the CNN's input and are not loaded."""
+    import scipy.io
+    m = scipy.io.loadmat(maps_file, variable_names=['mask', 'diffs'])
+    mask = np.squeeze(m['mask'])
+    diffs = np.squeeze(m['diffs'])
+    with np.errstate(invalid='ignore'):
+        np.logical_and(mask, diffs < 250, out=mask)
+    w = None
+    for name, shape, _ in scipy.io.whosmat(maps_file):
+        if name == 'heat_mat':
+            w = int(shape[1])
+    return mask, w
+
+
 def read_info_surreal(info_file, img_size_x=320, mask=None, skip=2):
-    """Returns dict(poses [N,72], shapes [N,10], joints2d [N,24,2], zrot [N]) float32 (data_helpers.py:58-88)."""
+    """Returns dict(poses [N,72], shapes [N,10], joints2d [N,24,2], zrot [N]) float32 (data_helpers.py:58-88).
+
+    `mask` indexes the frames exactly as the reference's `x[mask]` does (:80-82), with NumPy's rules: a bool array
+    selects frames; an INTEGER array -- which is what scipy.io.loadmat returns for a MATLAB logical (uint8), hence
+    what read_maps_mask_surreal and the reference get from a SURREAL file -- is fancy indexing, i.e. one row per
+    frame holding frame 0 or frame 1.  That is the reference's behaviour on such files and it is reproduced, not
+    repaired; pass `mask.astype(bool)` for the selection the author intended."""
     import scipy.io
     info = scipy.io.loadmat(info_file)
     poses = np.transpose(info['pose'], (1, 0))                                   # :62
@@ -22,7 +45,7 @@ def read_info_surreal(info_file, img_size_x=320, mask=None, skip=2):
     joints2d[:, :, 0] = img_size_x - joints2d[:, :, 0]                           # :67 (SURREAL images are mirrored)
     zrot = np.squeeze(np.array(info['zrot']), axis=1) if np.ndim(info['zrot']) == 2 else np.array(info['zrot'])   # :68
     if mask is not None:                                                         # :80-82
-        mask = np.asarray(mask, dtype=bool)
+        mask = np.asarray(mask)
         poses, shapes, joints2d, zrot = poses[mask], shapes[mask], joints2d[mask], zrot[mask]
     poses, shapes, joints2d, zrot = poses[::skip], shapes[::skip], joints2d[::skip], zrot[::skip]   # :84-87
     return dict(poses=np.ascontiguousarray(poses, dtype=np.float32), shapes=np.ascontiguousarray(shapes, dtype=np.float32),

@@ -56,8 +56,9 @@ def _raster_op_module(tf):
     return types.SimpleNamespace(rasterize_triangles=rasterize_triangles)
 
 
-def load(float64=False):
-    """Fresh import of the reference modules under the shim.  Returns a namespace of modules."""
+def load(float64=False, cv2=None):
+    """Fresh import of the reference modules under the shim.  Returns a namespace of modules.  `cv2`: a stand-in for
+    OpenCV (not installed here); when given, pose_3d/data_helpers.py is imported too (it needs it at import time)."""
     if not available():
         raise RuntimeError('reference tree not present at %s' % REF)
     for k in [k for k in sys.modules if k.split('.')[0] in _PKGS]:
@@ -86,9 +87,12 @@ def load(float64=False):
         ns.config = importlib.import_module('pose_3d.config')
         ns.utils = importlib.import_module('pose_3d.utils')
         ns.pose_model_3d = importlib.import_module('pose_3d.pose_model_3d')
+        if cv2 is not None:
+            sys.modules['cv2'] = cv2
+            ns.data_helpers = importlib.import_module('pose_3d.data_helpers')
         ns.faces = np.load(os.path.join(DEPS, 'tf_smpl', 'smpl_faces.npy')).astype(np.int32)
         return ns
     finally:
         sys.path[:] = saved
-        for k in [k for k in sys.modules if k.split('.')[0] in ('tensorflow', 'tf_pose')]:
+        for k in [k for k in sys.modules if k.split('.')[0] in ('tensorflow', 'tf_pose', 'cv2')]:
             del sys.modules[k]      # never leave the stand-in importable as `tensorflow` for anyone else

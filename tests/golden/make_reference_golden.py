@@ -13,6 +13,8 @@ installable here).  These fixtures are what pins the oracle restatements for the
                         get_camera_normal_plane, vertex_faces_from_face_verts, normals_from_mesh (real SMPL faces,
                         tf_smpl/smpl_faces.npy), render_mesh_verts_cam (the reference's renderer graph around its C++
                         rasteriser built in oracle/_ref); tf_smpl/projection.py batch_orth_proj_idrot
+  reference_surreal.npz pose_3d/data_helpers.py read_maps_poses_images_surreal (:43-89) on the reference's SURREAL
+                        annotation sample, synthetic heat maps / frames (pure NumPy code, no TF op involved)
 
 The SMPL model is the synthetic seed-0 model of smplb200/synthetic.py (the licensed SMPL pickle is not available);
 it is written to a temporary pickle and loaded by the reference's own SMPL.__init__.
@@ -236,15 +238,49 @@ def make_utils(pkl):
     np.savez_compressed(os.path.join(OUT, 'reference_utils.npz'), **g)
 
 
+def make_surreal(pkl):
+    """pose_3d/data_helpers.py:43-89 read_maps_poses_images_surreal on the reference's own annotation sample
+    (data/images/01_11_c0001_info.mat) with a synthetic heat-map file (random mask / diffs incl. NaN) and synthetic
+    JPEG frames.  OpenCV is not installed: the three cv2 calls of that function are served by PIL / NumPy."""
+    from PIL import Image
+    cv2 = types.ModuleType('cv2')
+    cv2.COLOR_BGR2RGB, cv2.NORM_MINMAX = 4, 32
+    cv2.imread = lambda path: np.array(Image.open(path).convert('RGB'))[:, :, ::-1]
+    cv2.cvtColor = lambda img, code: img[:, :, ::-1]
+    cv2.normalize = lambda f, dst, a, b, mode: (f - f.min()) / max(float(f.max() - f.min()), 1e-12) * (b - a) + a
+    ns = rr.load(float64=False, cv2=cv2)
+    import scipy.io
+    info = os.path.join(rr.REF, 'data', 'images', '01_11_c0001_info.mat')
+    T = scipy.io.loadmat(info)['pose'].shape[1]
+    r = np.random.default_rng(77)
+    H, W = 24, 32
+    mask = (r.uniform(size=(T, 1)) < 0.8).astype(np.uint8)
+    diffs = r.uniform(0, 300, size=(T, 1))
+    diffs[r.integers(0, T, 7)] = np.nan
+    tmp = tempfile.mkdtemp()
+    maps = os.path.join(tmp, 'maps.mat')
+    scipy.io.savemat(maps, dict(heat_mat=r.uniform(size=(H, W, 19, T)).astype(np.float32), mask=mask, diffs=diffs))
+    frames = os.path.join(tmp, 'frames')
+    os.mkdir(frames)
+    for t in range(T):
+        Image.fromarray(r.integers(0, 255, (H, W, 3), dtype=np.uint8)).save(os.path.join(frames, 'f%04d.jpg' % t))
+    with np.errstate(invalid='ignore'):
+        concat, poses, shapes, joints2d, zrot = ns.data_helpers.read_maps_poses_images_surreal(
+            maps, info, frames.encode('utf-8'))
+    print('surreal', concat.shape, poses.shape, joints2d.dtype, zrot.shape)
+    np.savez_compressed(os.path.join(OUT, 'reference_surreal.npz'), mask=mask, diffs=diffs, img_size_x=W,
+                        poses=poses, shapes=shapes, joints2d=joints2d, zrot=zrot)
+
+
 def main():
     if not rr.available():
         raise SystemExit('needs the reference tree at ' + rr.REF)
     pkl = os.path.join(tempfile.mkdtemp(), 'synthetic_smpl_seed0.pkl')
     with open(pkl, 'wb') as f:
         pickle.dump(syn.make_synthetic_smpl(0), f)
-    which = sys.argv[1:] or ['smpl', 'losses', 'utils']
+    which = sys.argv[1:] or ['smpl', 'losses', 'utils', 'surreal']
     for w in which:
-        {'smpl': make_smpl, 'losses': make_losses, 'utils': make_utils}[w](pkl)
+        {'smpl': make_smpl, 'losses': make_losses, 'utils': make_utils, 'surreal': make_surreal}[w](pkl)
 
 
 if __name__ == '__main__':

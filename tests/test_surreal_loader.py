@@ -30,6 +30,29 @@ def test_read_info_matches_reference_processing(tmp_path):
     assert np.array_equal(ann['zrot'], np.squeeze(G['raw_zrot'])[10:30:2])
 
 
+def test_reader_matches_reference_function_run(tmp_path):
+    """tests/golden/reference_surreal.npz is what the reference's read_maps_poses_images_surreal itself returned
+    (data_helpers.py:43-89, run by make_reference_golden.py) for its own annotation sample plus a synthetic heat-map
+    file whose mask loads as uint8 -- so its `x[mask]` is integer indexing (frames 0/1), which the loader reproduces."""
+    import scipy.io
+    from smplb200 import surreal
+    R = np.load(os.path.join(ROOT, 'tests', 'golden', 'reference_surreal.npz'))
+    T, W = R['mask'].shape[0], int(R['img_size_x'])
+    maps = str(tmp_path / 'maps.mat')
+    scipy.io.savemat(maps, dict(heat_mat=np.zeros((2, W, 19, T), np.float32), mask=R['mask'], diffs=R['diffs']))
+    mask, w = surreal.read_maps_mask_surreal(maps)
+    assert w == W and mask.dtype == np.uint8 and mask.shape == (T,)
+    with np.errstate(invalid='ignore'):
+        assert np.array_equal(mask.astype(bool), (np.squeeze(R['mask']) != 0) & (np.squeeze(R['diffs']) < 250))
+    ann = surreal.read_info_surreal(write_mat(tmp_path), img_size_x=w, mask=mask)
+    for k in ('poses', 'shapes', 'joints2d', 'zrot'):
+        assert ann[k].shape == R[k].shape, k
+        assert np.array_equal(ann[k], R[k].astype(np.float32)), k
+    # the selection the author intended needs a bool mask
+    sel = surreal.read_info_surreal(write_mat(tmp_path), img_size_x=w, mask=mask.astype(bool))
+    assert sel['poses'].shape[0] == (int(mask.astype(bool).sum()) + 1) // 2
+
+
 @pytest.mark.gpu
 def test_gt_batch_on_gpu(tmp_path, gpu_model, oracle64):
     from oracle import ref_numpy as rn
