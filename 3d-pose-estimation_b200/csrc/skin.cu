@@ -93,9 +93,11 @@ int32_t launch_keypoints(const smplb_model* m, int B, const float* verts, float*
 
 // Keypoints from the compact rows kpv[group of 16 samples][slot][16] (skin_tc.cu): lane = sample (two groups per
 // warp), every lane walks the regressor entries of its keypoints in order -> coalesced 64-byte row reads, uniform
-// (broadcast) index/value loads, no cross-lane reduction; the 4 warps of a block share 32 samples and split the
-// keypoints.  Same entry order as keypoints_kernel, plain sequential sum per keypoint.
-__global__ void __launch_bounds__(128) keypoints_compact_kernel(int B, int NK, const float* __restrict__ kpv, int pitch,
+// (broadcast) index/value loads, no cross-lane reduction; the warps of a block share 32 samples and split the
+// keypoints -- one warp per keypoint (19 or 14 warps), so a small batch is not a chain of NK/4 regressor walks per
+// warp (28 us at B = 1 with 4 warps; the kernel was a third of the B = 1024 step).  Same entry order as
+// keypoints_kernel, plain sequential sum per keypoint.
+__global__ void __launch_bounds__(640) keypoints_compact_kernel(int B, int NK, const float* __restrict__ kpv, int pitch,
                                                                 const int* __restrict__ kp_ptr,
                                                                 const int* __restrict__ kp_slot,
                                                                 const float* __restrict__ kp_val,
@@ -105,10 +107,11 @@ __global__ void __launch_bounds__(128) keypoints_compact_kernel(int B, int NK, c
   const bool ok = b < B;
   const int bc = ok ? b : B - 1;
   const float* row = kpv + (size_t)(bc / SK_S) * pitch * SK_S + (bc % SK_S);
-  for (int k = warp; k < NK; k += 4) {
+  const int nw = blockDim.x >> 5;
+  for (int k = warp; k < NK; k += nw) {
     const int e0 = __ldg(kp_ptr + k), e1 = __ldg(kp_ptr + k + 1);
     float sx = 0.f, sy = 0.f, sz = 0.f;
-#pragma unroll 8
+#pragma unroll 16
     for (int e = e0; e < e1; ++e) {
       const float* p = row + (size_t)__ldg(kp_slot + e) * SK_S;
       const float r = __ldg(kp_val + e);
@@ -125,7 +128,8 @@ __global__ void __launch_bounds__(128) keypoints_compact_kernel(int B, int NK, c
 
 int32_t launch_keypoints_compact(const smplb_model* m, int B, const float* kpv, float* kp, cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
-  keypoints_compact_kernel<<<(B + 31) / 32, 128, 0, st>>>(B, m->NK, kpv, m->kpv_pitch, m->kp_ptr, m->kpc_slot, m->kp_val, kp);
+  const int nw = m->NK < 20 ? m->NK : 20;
+  keypoints_compact_kernel<<<(B + 31) / 32, 32 * nw, 0, st>>>(B, m->NK, kpv, m->kpv_pitch, m->kp_ptr, m->kpc_slot, m->kp_val, kp);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
