@@ -41,6 +41,7 @@ struct TriSetup {
   float v0x, v0y, v1x, v1y, v2x, v2y, z0, z1, z2;
   int f0x, f0y, f1x, f1y, f2x, f2y;
   int left, right, bottom, top;
+  bool safe;   // every fixed-point coordinate (vertices and pixel centres) below 2^29: no int32 wrap in the edge tests
 };
 
 // impl.cc:82-107.  (v + 1.0) * half is evaluated in double and rounded once, as the C++ does.
@@ -59,17 +60,52 @@ __device__ __forceinline__ void tri_setup(const float* __restrict__ ndc, const i
   s.f0x = fixed_point(s.v0x); s.f0y = fixed_point(s.v0y);
   s.f1x = fixed_point(s.v1x); s.f1y = fixed_point(s.v1y);
   s.f2x = fixed_point(s.v2x); s.f2y = fixed_point(s.v2y);
+  auto small = [](int f) { return (uint32_t)f + (1u << 29) < (1u << 30); };   // -2^29 <= f < 2^29 (INT_MIN fails)
+  s.safe = W <= 8192 && H <= 8192 && small(s.f0x) && small(s.f0y) && small(s.f1x) && small(s.f1y) && small(s.f2x) &&
+           small(s.f2y);
+  // The reference walks the box floor(min) .. ceil(max) of the float coordinates (above).  A pixel whose centre lies
+  // strictly beyond the fixed-point extent of the triangle in x or in y cannot pass the inside test of a triangle
+  // with non-zero fixed-point area (the union of "all edges >= 0" and "all edges <= 0" is then the closed triangle),
+  // so the box is shrunk to the pixel centres inside the fixed-point extent -- for a body mesh at 320x240 most boxes
+  // become empty or a single pixel.  Exactly collinear fixed-point triangles keep the reference box: their test
+  // passes along the whole line.
+  if (s.safe) {
+    const long long area = (long long)(s.f1x - s.f0x) * (s.f2y - s.f0y) - (long long)(s.f1y - s.f0y) * (s.f2x - s.f0x);
+    if (area != 0) {
+      const int fx0 = min(min(s.f0x, s.f1x), s.f2x), fx1 = max(max(s.f0x, s.f1x), s.f2x);
+      const int fy0 = min(min(s.f0y, s.f1y), s.f2y), fy1 = max(max(s.f0y, s.f1y), s.f2y);
+      s.left = max(s.left, (fx0 - 32768 + 65535) >> 16);      // first ix with (ix << 16) + 32768 >= fx0
+      s.right = min(s.right, ((fx1 - 32768) >> 16) + 1);      // one past the last ix with (ix << 16) + 32768 <= fx1
+      s.bottom = max(s.bottom, (fy0 - 32768 + 65535) >> 16);
+      s.top = min(s.top, ((fy1 - 32768) >> 16) + 1);
+    }
+  }
+}
+
+// impl.cc:112-124, the pixel-inside test: (all three edges counter-clockwise) or (all three clockwise), six is_ccw
+// calls in the reference.  is_ccw(a, b, p) is E_ab(p) >= 0 with E_ab(p) = (b - a) x (p - a); the reversed call
+// is_ccw(b, a, p) is E_ab(p) <= 0 -- the same integer, because moving the origin from a to b changes E by
+// (b - a) x (b - a) = 0.  With every coordinate below 2^29 nothing wraps in int32 / int64, so three 64-bit edge
+// functions decide both orientations exactly; otherwise the six calls are evaluated literally (wrap-around and all).
+__device__ __forceinline__ bool tri_covers(const TriSetup& s, int ix, int iy) {
+  if (s.safe) {
+    const int fx = (ix << 16) + 32768, fy = (iy << 16) + 32768;   // == fixed_point(ix + 0.5f), exact
+    const long long e01 = (long long)(s.f1x - s.f0x) * (fy - s.f0y) - (long long)(s.f1y - s.f0y) * (fx - s.f0x);
+    const long long e12 = (long long)(s.f2x - s.f1x) * (fy - s.f1y) - (long long)(s.f2y - s.f1y) * (fx - s.f1x);
+    const long long e20 = (long long)(s.f0x - s.f2x) * (fy - s.f2y) - (long long)(s.f0y - s.f2y) * (fx - s.f2x);
+    return (e01 >= 0 && e12 >= 0 && e20 >= 0) || (e01 <= 0 && e12 <= 0 && e20 <= 0);
+  }
+  const int fx = fixed_point((float)ix + 0.5f), fy = fixed_point((float)iy + 0.5f);
+  return (is_ccw(s.f0x, s.f0y, s.f1x, s.f1y, fx, fy) && is_ccw(s.f1x, s.f1y, s.f2x, s.f2y, fx, fy) &&
+          is_ccw(s.f2x, s.f2y, s.f0x, s.f0y, fx, fy)) ||
+         (is_ccw(s.f1x, s.f1y, s.f0x, s.f0y, fx, fy) && is_ccw(s.f2x, s.f2y, s.f1x, s.f1y, fx, fy) &&
+          is_ccw(s.f0x, s.f0y, s.f2x, s.f2y, fx, fy));
 }
 
 // impl.cc:112-143 for one pixel: coverage test, barycentrics, depth, clip test.  No contraction anywhere.
 __device__ __forceinline__ bool tri_eval(const TriSetup& s, int ix, int iy, float& b0, float& b1, float& b2, float& z) {
+  if (!tri_covers(s, ix, iy)) return false;
   const float px = (float)ix + 0.5f, py = (float)iy + 0.5f;   // exact
-  const int fx = fixed_point(px), fy = fixed_point(py);
-  const bool in = (is_ccw(s.f0x, s.f0y, s.f1x, s.f1y, fx, fy) && is_ccw(s.f1x, s.f1y, s.f2x, s.f2y, fx, fy) &&
-                   is_ccw(s.f2x, s.f2y, s.f0x, s.f0y, fx, fy)) ||
-                  (is_ccw(s.f1x, s.f1y, s.f0x, s.f0y, fx, fy) && is_ccw(s.f2x, s.f2y, s.f1x, s.f1y, fx, fy) &&
-                   is_ccw(s.f0x, s.f0y, s.f2x, s.f2y, fx, fy));
-  if (!in) return false;
   const float area2 = __fsub_rn(__fmul_rn(__fsub_rn(s.v2x, s.v0x), __fsub_rn(s.v1y, s.v0y)),
                                 __fmul_rn(__fsub_rn(s.v2y, s.v0y), __fsub_rn(s.v1x, s.v0x)));
   b0 = __fdiv_rn(__fsub_rn(__fmul_rn(__fsub_rn(px, s.v1x), __fsub_rn(s.v2y, s.v1y)),
@@ -89,9 +125,15 @@ __device__ __forceinline__ unsigned long long pack_key(float z, int t) {
 }
 constexpr unsigned long long KEY_EMPTY = ~0ull;
 
-__global__ void raster_clear_kernel(unsigned long long* keys, size_t n, int* big_count) {
+// thread = 4 keys (two 16-byte stores); n is padded to a multiple of 4 by the workspace layout
+__global__ void __launch_bounds__(256) raster_clear_kernel(unsigned long long* keys, size_t n4, int* big_count) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) keys[i] = KEY_EMPTY;
+  if (i < n4) {
+    const uint4 e = make_uint4(~0u, ~0u, ~0u, ~0u);
+    uint4* k = reinterpret_cast<uint4*>(keys) + 2 * i;
+    k[0] = e;
+    k[1] = e;
+  }
   if (i == 0) *big_count = 0;
 }
 
@@ -110,11 +152,14 @@ __global__ void __launch_bounds__(128) raster_tri_kernel(int T, int V, int W, in
     return;
   }
   unsigned long long* k = keys + (size_t)b * W * H;
-  for (int iy = s.bottom; iy < s.top; ++iy)
-    for (int ix = s.left; ix < s.right; ++ix) {
-      float b0, b1, b2, z;
-      if (tri_eval(s, ix, iy, b0, b1, b2, z)) atomicMin(k + iy * W + ix, pack_key(z, t));
-    }
+  // one flat loop over the box (the lanes of a warp have boxes of different shapes: a single trip count
+  // reconverges better than two nested ones)
+  int ix = s.left, iy = s.bottom;
+  for (int i = bw * bh; i > 0; --i) {
+    float b0, b1, b2, z;
+    if (tri_eval(s, ix, iy, b0, b1, b2, z)) atomicMin(k + iy * W + ix, pack_key(z, t));
+    if (++ix == s.right) { ix = s.left; ++iy; }
+  }
 }
 
 // CTA = one queued large triangle, threads stride over its bounding box
@@ -161,6 +206,43 @@ __global__ void __launch_bounds__(256) raster_resolve_kernel(int B, int T, int V
   }
   if (ids) ids[i] = t;
   if (zbuf) zbuf[i] = z;
+}
+
+// same, thread = 4 consecutive pixels of one image (W*H % 4 == 0, 16-byte aligned buffers): 16-byte key loads and
+// output stores, four independent key -> triangle -> vertex load chains in flight per thread
+__global__ void __launch_bounds__(256) raster_resolve4_kernel(int B, int T, int V, int W, int H, const float* __restrict__ ndc,
+                                                              const int* __restrict__ tri,
+                                                              const unsigned long long* __restrict__ keys,
+                                                              float* __restrict__ bary, int* __restrict__ ids,
+                                                              float* __restrict__ zbuf) {
+  const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x, i0 = 4 * q;
+  if (i0 >= (size_t)B * W * H) return;
+  const int b = (int)(i0 / ((size_t)W * H)), p0 = (int)(i0 % ((size_t)W * H));
+  const uint4 ka = __ldcs(reinterpret_cast<const uint4*>(keys) + 2 * q), kb = __ldcs(reinterpret_cast<const uint4*>(keys) + 2 * q + 1);
+  const uint32_t klo[4] = {ka.x, ka.z, kb.x, kb.z}, khi[4] = {ka.y, ka.w, kb.y, kb.w};
+  float bc[12], z[4];
+  int t[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    bc[3 * k] = bc[3 * k + 1] = bc[3 * k + 2] = 0.f;
+    z[k] = 1.0f;
+    t[k] = 0;
+    if ((klo[k] & khi[k]) != 0xffffffffu) {
+      t[k] = (int)(~klo[k]);
+      TriSetup s;
+      tri_setup(ndc + (size_t)b * V * 3, tri, t[k], W, H, s);
+      const int p = p0 + k;
+      tri_eval(s, p % W, p / W, bc[3 * k], bc[3 * k + 1], bc[3 * k + 2], z[k]);
+    }
+  }
+  if (bary) {
+    float4* o = reinterpret_cast<float4*>(bary) + 3 * q;
+    __stcs(o, make_float4(bc[0], bc[1], bc[2], bc[3]));
+    __stcs(o + 1, make_float4(bc[4], bc[5], bc[6], bc[7]));
+    __stcs(o + 2, make_float4(bc[8], bc[9], bc[10], bc[11]));
+  }
+  if (ids) __stcs(reinterpret_cast<int4*>(ids) + q, make_int4(t[0], t[1], t[2], t[3]));
+  if (zbuf) __stcs(reinterpret_cast<float4*>(zbuf) + q, make_float4(z[0], z[1], z[2], z[3]));
 }
 
 // ---- backward (rasterize_triangles_grad.cc:144-218) ------------------------------------------------------------
@@ -319,12 +401,17 @@ extern "C" int32_t smplb_rasterize(const smplb_mesh* m, int32_t B, const float* 
   unsigned long long* keys = (unsigned long long*)w;
   int* big_count = (int*)(w + ru256(npix * 8));
   int* big_list = (int*)(w + ru256(npix * 8) + 256);
-  raster_clear_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(keys, npix, big_count);
+  const size_t n4 = (npix + 3) / 4;   // the key area is padded to 256 bytes
+  raster_clear_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(keys, n4, big_count);
   if (m->T > 0) {
     raster_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
     raster_big_kernel<<<592, 256, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
   }
-  raster_resolve_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(B, m->T, m->V, W, H, ndc, m->tri, keys, bary, ids, zbuf);
+  const bool vec = ((size_t)W * H) % 4 == 0 && (((uintptr_t)bary | (uintptr_t)ids | (uintptr_t)zbuf) & 15) == 0;
+  if (vec)
+    raster_resolve4_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(B, m->T, m->V, W, H, ndc, m->tri, keys, bary, ids, zbuf);
+  else
+    raster_resolve_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(B, m->T, m->V, W, H, ndc, m->tri, keys, bary, ids, zbuf);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
@@ -473,7 +560,7 @@ extern "C" int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const fl
   int* big_count = (int*)(w + ru256(npix * 8));
   int* big_list = (int*)(w + ru256(npix * 8) + 256);
   clip_transform_kernel<<<(unsigned)(((size_t)B * m->V + 255) / 256), 256, 0, st>>>(B, m->V, verts, clip_transforms, ndc, clip_w);
-  raster_clear_kernel<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(keys, npix, big_count);
+  raster_clear_kernel<<<(unsigned)(((npix + 3) / 4 + 255) / 256), 256, 0, st>>>(keys, (npix + 3) / 4, big_count);
   if (m->T > 0) {
     raster_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
     raster_big_kernel<<<592, 256, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
