@@ -125,18 +125,6 @@ __device__ __forceinline__ unsigned long long pack_key(float z, int t) {
 }
 constexpr unsigned long long KEY_EMPTY = ~0ull;
 
-// thread = 4 keys (two 16-byte stores); n is padded to a multiple of 4 by the workspace layout
-__global__ void __launch_bounds__(256) raster_clear_kernel(unsigned long long* keys, size_t n4, int* big_count) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n4) {
-    const uint4 e = make_uint4(~0u, ~0u, ~0u, ~0u);
-    uint4* k = reinterpret_cast<uint4*>(keys) + 2 * i;
-    k[0] = e;
-    k[1] = e;
-  }
-  if (i == 0) *big_count = 0;
-}
-
 // thread = (image, triangle): small bounding boxes are walked here, large ones queued
 __global__ void __launch_bounds__(128) raster_tri_kernel(int T, int V, int W, int H, const float* __restrict__ ndc,
                                                          const int* __restrict__ tri, unsigned long long* __restrict__ keys,
@@ -401,8 +389,11 @@ extern "C" int32_t smplb_rasterize(const smplb_mesh* m, int32_t B, const float* 
   unsigned long long* keys = (unsigned long long*)w;
   int* big_count = (int*)(w + ru256(npix * 8));
   int* big_list = (int*)(w + ru256(npix * 8) + 256);
-  const size_t n4 = (npix + 3) / 4;   // the key area is padded to 256 bytes
-  raster_clear_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(keys, n4, big_count);
+  const size_t n4 = (npix + 3) / 4;
+  // KEY_EMPTY is all ones: the key area is a byte fill (the copy engine's fill runs at write speed, above a
+  // store kernel's), the big-triangle counter a second one
+  SMPLB_CUDA_CHECK(cudaMemsetAsync(keys, 0xff, npix * 8, st));
+  SMPLB_CUDA_CHECK(cudaMemsetAsync(big_count, 0, sizeof(int), st));
   if (m->T > 0) {
     raster_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
     raster_big_kernel<<<592, 256, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
@@ -469,10 +460,16 @@ __global__ void __launch_bounds__(256) raster_shade_kernel(int B, int T, int V, 
   if (i >= (size_t)B * W * H) return;
   const int b = (int)(i / ((size_t)W * H)), p = (int)(i % ((size_t)W * H));
   const int ix = p % W, iy = p / W;
-  const unsigned long long key = keys[i];
+  const unsigned long long key = __ldcs(keys + i);
   float bc[3] = {0.f, 0.f, 0.f}, z;
   int t = 0;
-  if (key != KEY_EMPTY) {
+  if (key == KEY_EMPTY) {
+    // background: zero barycentrics give alpha = 0, every attribute = the background value -1 (:161-164), hence
+    // mask = 0 (:387) and the pixel is (0, 0, 0, 0) whatever the lights are (finite vertex attributes assumed)
+    __stcs(reinterpret_cast<float4*>(rgba) + ((size_t)b * H + (H - 1 - iy)) * W + ix, make_float4(0.f, 0.f, 0.f, 0.f));
+    return;
+  }
+  {
     t = (int)(~(uint32_t)key);
     TriSetup s;
     tri_setup(ndc + (size_t)b * V * 3, tri, t, W, H, s);
@@ -560,7 +557,8 @@ extern "C" int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const fl
   int* big_count = (int*)(w + ru256(npix * 8));
   int* big_list = (int*)(w + ru256(npix * 8) + 256);
   clip_transform_kernel<<<(unsigned)(((size_t)B * m->V + 255) / 256), 256, 0, st>>>(B, m->V, verts, clip_transforms, ndc, clip_w);
-  raster_clear_kernel<<<(unsigned)(((npix + 3) / 4 + 255) / 256), 256, 0, st>>>(keys, (npix + 3) / 4, big_count);
+  SMPLB_CUDA_CHECK(cudaMemsetAsync(keys, 0xff, npix * 8, st));
+  SMPLB_CUDA_CHECK(cudaMemsetAsync(big_count, 0, sizeof(int), st));
   if (m->T > 0) {
     raster_tri_kernel<<<dim3((m->T + 127) / 128, B), 128, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);
     raster_big_kernel<<<592, 256, 0, st>>>(m->T, m->V, W, H, ndc, m->tri, keys, big_list, big_count);

@@ -395,7 +395,7 @@ def run_raster(args, rank, local_rank, world, dist):
             'render_ms_per_step': ms_r, 'render_images_per_s': world * B / (ms_r * 1e-3),
             'render_covered_fraction': float((out['img'][..., 3] > 0.5).float().mean()),
             'covered_fraction': float((bary.sum(-1) > 0.5).float().mean()),
-            'roofline': {'bound': 'hbm', 'kernel': 'raster_clear + raster_tri + raster_big + raster_resolve (whole step)',
+            'roofline': {'bound': 'hbm', 'kernel': 'key fill + raster_tri + raster_big + raster_resolve4 (whole step)',
                          'achieved': out_bytes / (ms_f * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
                          'frac': out_bytes / (ms_f * 1e-3) / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': out_bytes},
