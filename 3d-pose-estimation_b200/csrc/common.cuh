@@ -105,6 +105,7 @@ struct smplb_mesh {
   int* vent;       // [3T]  triangle * 3 + corner
   int* big_v;      // [n_big] vertices with more than NM_BIG_ORDER incident faces (handled by a whole warp in normals.cu)
   int n_big;
+  uint4* vfan;     // [V] closed fans of order 3..8: the ring of neighbours as 8 x uint16 (0xffff = unused); else all ones
   uint32_t* vpair; // [3T]  per CSR entry: the two other vertices of the face, in winding order after this corner
                    //       (lo 16 bits = next, hi 16 bits = next-next); only when V <= 65536, else NULL
 };

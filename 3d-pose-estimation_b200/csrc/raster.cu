@@ -313,7 +313,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
   cudaGetDevice(&prev);
   SMPLB_CUDA_CHECK(cudaSetDevice(device));
   smplb_mesh* m = new smplb_mesh();
-  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr; m->vpair = nullptr; m->big_v = nullptr; m->n_big = 0;
+  m->device = device; m->T = T; m->V = V; m->tri = m->vptr = m->vent = nullptr; m->vpair = nullptr; m->vfan = nullptr; m->big_v = nullptr; m->n_big = 0;
   // vertex_faces_from_face_verts (deps/pose_3d/utils.py:130-149): adjacency lists padded to the maximum vertex order
   m->max_order = 0;
   for (int v = 0; v < V; ++v) m->max_order = std::max(m->max_order, vptr[v + 1] - vptr[v]);
@@ -331,20 +331,59 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
     if (e == cudaSuccess) e = cudaMalloc((void**)&m->big_v, sizeof(int) * (big.size() ? big.size() : 1));
     if (e == cudaSuccess && !big.empty()) e = cudaMemcpy(m->big_v, big.data(), sizeof(int) * big.size(), cudaMemcpyHostToDevice);
   }
-  if (e == cudaSuccess && T > 0 && V <= 65536) {
-    // (b - a) x (c - a) is the same vector from whichever corner it is taken: store, per CSR entry, the next two
-    // vertices after this corner so that the normals kernel needs one 4-byte load per incident face
+  if (e == cudaSuccess && T > 0 && V <= 32768) {
+    // (b - a) x (c - a) is the same vector from whichever corner it is taken: store, per incident face of a vertex,
+    // the next two vertices (p, q) after this corner, 15 bits each, so that the normals kernel needs one 4-byte load
+    // per face.  The faces of a vertex are put in FAN order (q of one = p of the next, as around any manifold
+    // vertex); bit 31 marks an entry whose p is the previous entry's q, which the kernel then keeps in registers:
+    // 3n + 6 shared-memory loads per vertex of order n instead of 6n + 3.
     std::vector<uint32_t> vpair((size_t)3 * T);
-    for (size_t i = 0; i < vent.size(); ++i) {
-      const int t = vent[i] / 3, k = vent[i] % 3;
-      vpair[i] = (uint32_t)triangles_host[3 * t + (k + 1) % 3] | ((uint32_t)triangles_host[3 * t + (k + 2) % 3] << 16);
+    std::vector<uint16_t> vfan((size_t)8 * V, (uint16_t)0xffff);
+    std::vector<std::pair<int, int>> pq;
+    std::vector<char> used;
+    for (int v = 0; v < V; ++v) {
+      const int e0 = vptr[v], n = vptr[v + 1] - vptr[v];
+      pq.resize(n);
+      used.assign(n, 0);
+      for (int i = 0; i < n; ++i) {
+        const int t = vent[e0 + i] / 3, k = vent[e0 + i] % 3;
+        pq[i] = {triangles_host[3 * t + (k + 1) % 3], triangles_host[3 * t + (k + 2) % 3]};
+      }
+      int out = e0, last_q = -1, n_chains = 0;
+      for (int done = 0; done < n; ++done) {
+        int pick = -1;
+        for (int i = 0; i < n && pick < 0; ++i)
+          if (!used[i] && pq[i].first == last_q) pick = i;
+        const bool chained = pick >= 0;
+        n_chains += chained ? 0 : 1;
+        if (!chained) {
+          // start of a chain: prefer a face whose p is nobody's q (the open end of a boundary fan)
+          for (int i = 0; i < n && pick < 0; ++i) {
+            if (used[i]) continue;
+            bool is_q = false;
+            for (int j = 0; j < n; ++j) is_q |= (!used[j] && j != i && pq[j].second == pq[i].first);
+            if (!is_q) pick = i;
+          }
+          for (int i = 0; i < n && pick < 0; ++i)
+            if (!used[i]) pick = i;
+        }
+        used[pick] = 1;
+        vpair[out++] = (uint32_t)pq[pick].first | ((uint32_t)pq[pick].second << 15) | (chained ? 0x80000000u : 0u);
+        last_q = pq[pick].second;
+      }
+      // one closed fan of 3..8 faces (every interior vertex of a manifold mesh): the kernel walks the ring of
+      // neighbours q_0 .. q_{n-1} from a single 16-byte load, the first face's p being q_{n-1}
+      if (n >= 3 && n <= 8 && n_chains == 1 && (int)(vpair[e0] & 0x7fffu) == last_q)
+        for (int i = 0; i < n; ++i) vfan[(size_t)8 * v + i] = (uint16_t)((vpair[e0 + i] >> 15) & 0x7fffu);
     }
-    e = cudaMalloc((void**)&m->vpair, sizeof(uint32_t) * 3 * (size_t)T);
+    e = cudaMalloc((void**)&m->vfan, sizeof(uint16_t) * 8 * (size_t)V);
+    if (e == cudaSuccess) e = cudaMemcpy(m->vfan, vfan.data(), sizeof(uint16_t) * 8 * (size_t)V, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&m->vpair, sizeof(uint32_t) * 3 * (size_t)T);
     if (e == cudaSuccess) e = cudaMemcpy(m->vpair, vpair.data(), sizeof(uint32_t) * 3 * (size_t)T, cudaMemcpyHostToDevice);
   }
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
-    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair); cudaFree(m->big_v);
+    cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair); cudaFree(m->vfan); cudaFree(m->big_v);
     delete m;
     return fail(SMPLB_E_CUDA, std::string("smplb_mesh_create: ") + cudaGetErrorString(e));
   }
@@ -354,7 +393,7 @@ extern "C" int32_t smplb_mesh_create(smplb_mesh** out, int32_t device, const int
 
 extern "C" int32_t smplb_mesh_destroy(smplb_mesh* m) {
   if (!m) return SMPLB_OK;
-  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair); cudaFree(m->big_v);
+  cudaFree(m->tri); cudaFree(m->vptr); cudaFree(m->vent); cudaFree(m->vpair); cudaFree(m->vfan); cudaFree(m->big_v);
   delete m;
   return SMPLB_OK;
 }
