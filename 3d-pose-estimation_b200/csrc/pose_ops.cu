@@ -171,6 +171,37 @@ __global__ void cam_losses_finish_kernel(int nblocks, const float* __restrict__ 
   loss_out[3] = loss_out[0] + loss_out[1] + loss_out[2];
 }
 
+// ---- 3D losses (pose_model_3d.py:183-192): weight * mean((pred - target)^2), value and gradient ----------------
+// Grid-stride over the elements, per-thread sequential partial -> fixed-order block tree -> one partial per block;
+// the finishing block adds the MSE_BLOCKS partials in index order: run-to-run identical.
+constexpr int MSE_BLOCKS = 1184, MSE_THREADS = 256;
+__global__ void __launch_bounds__(MSE_THREADS) mse_grad_kernel(long long n, const float* __restrict__ pred,
+                                                               const float* __restrict__ target, float gscale,
+                                                               float* __restrict__ g_out, float* __restrict__ partial) {
+  float acc = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float d = __ldcs(pred + i) - __ldcs(target + i);
+    acc = fmaf(d, d, acc);
+    if (g_out) __stcs(g_out + i, gscale * d);
+  }
+  __shared__ float red[MSE_THREADS];
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = MSE_THREADS / 2; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = red[0];
+}
+__global__ void mse_finish_kernel(const float* __restrict__ partial, float lscale, float* __restrict__ loss_out,
+                                  int accumulate) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  float s = 0.f;
+  for (int i = 0; i < MSE_BLOCKS; ++i) s += partial[i];
+  loss_out[0] = (accumulate ? loss_out[0] : 0.f) + lscale * s;
+}
+
 }  // namespace smplb
 
 using namespace smplb;
@@ -214,6 +245,20 @@ extern "C" int32_t smplb_cam_losses(int32_t B, const float* gt_joints3d, const f
   cam_losses_kernel<<<nb, 128, 0, st>>>(B, gt_joints3d, gt_joints2d, cam_pos, cam_rot, cam_f, f_raw, *cfg, w_angle, w_neg,
                                        w_rot, (float*)scratch, g_cam_pos, g_cam_rot, g_cam_f, g_f_raw);
   cam_losses_finish_kernel<<<1, 32, 0, st>>>(nb, (const float*)scratch, w_angle, w_neg, w_rot, loss_out);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+extern "C" size_t smplb_mse_scratch_bytes(void) { return MSE_BLOCKS * sizeof(float); }
+
+extern "C" int32_t smplb_mse_grad(int64_t n, const float* pred, const float* target, float weight, int64_t n_total,
+                                  float* g_out, float* loss_out, int32_t accumulate, void* scratch, void* stream) {
+  if (n < 0 || n_total <= 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_mse_grad: n >= 0 and n_total > 0 required");
+  if (!pred || !target || !loss_out || !scratch) return fail(SMPLB_E_INVALID_ARG, "smplb_mse_grad: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const float inv = weight / (float)n_total;
+  mse_grad_kernel<<<MSE_BLOCKS, MSE_THREADS, 0, st>>>((long long)n, pred, target, 2.0f * inv, g_out, (float*)scratch);
+  mse_finish_kernel<<<1, 32, 0, st>>>((const float*)scratch, inv, loss_out, accumulate);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

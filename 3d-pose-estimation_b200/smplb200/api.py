@@ -276,6 +276,27 @@ def reproj_loss(px_pred, px_gt, ss=0.024, scale=None, cap=1.0 / 24):
     return out
 
 
+def mse_grad(pred, target, weight=1.0, n_total=None, want_grad=True, loss_out=None, accumulate=False, g_out=None,
+             scratch=None):
+    """tf.losses.mean_squared_error with a scalar weight (pose_model_3d.py:183-192): returns (loss[1] CUDA tensor,
+    gradient w.r.t. pred or None).  accumulate adds into loss_out."""
+    dev = _cuda_dev(pred)
+    a = _dev_f32(pred, dev)
+    b = _dev_f32(target, dev, a.shape)
+    n = a.numel()
+    if loss_out is None:
+        loss_out = torch.zeros(1, dtype=torch.float32, device=dev)
+    if want_grad and g_out is None:
+        g_out = torch.empty_like(a)
+    if scratch is None:
+        scratch = torch.empty(int(_lib.lib().smplb_mse_scratch_bytes()), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.lib().smplb_mse_grad(n, _ptr(a), _ptr(b), float(weight), int(n_total if n_total is not None else n),
+                                        _ptr(g_out) if want_grad else None, _ptr(loss_out), int(bool(accumulate)),
+                                        _ptr(scratch), _stream(dev)))
+    return loss_out, (g_out if want_grad else None)
+
+
 def adam_step(x, g, m, v, t, lr=2e-4, beta1=0.9, beta2=0.999, eps=1e-8):
     """In-place TF1 Adam (pose_model_3d.py:393)."""
     dev = x.device

@@ -152,9 +152,17 @@ def run_fit(args, rank, local_rank, world, dist):
     model = smplb200.Model(syn.make_synthetic_smpl(0), device=local_rank)
     inp = syn.make_inputs(B, seed=1000 + rank)
     tgt = syn.make_inputs(B, seed=5000 + rank)
-    gt_px = model.forward(inp['beta'], tgt['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=4)['px'].clone()
-    f = Fitter(model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, focal=inp['focal'], lr=2e-4,
-               n_total=B * world * 48)
+    mesh = args.loss == 'mesh'
+    if mesh:
+        # the 3D-loss variant (pose_model_3d.py:183-192): drives the backward through the vertices
+        from smplb200.fit import MeshFitter
+        o = model.forward(inp['beta'], tgt['theta'], want_kp=False, want_Rs=False)
+        f = MeshFitter(model, inp['beta'], inp['theta'], o['verts'].clone(), o['joints'].clone(), lr=2e-4,
+                       n_total_verts=B * world * 6890 * 3, n_total_joints=B * world * 72)
+    else:
+        gt_px = model.forward(inp['beta'], tgt['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=4)['px'].clone()
+        f = Fitter(model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, focal=inp['focal'], lr=2e-4,
+                   n_total=B * world * 48)
     gl = torch.zeros(1, device=dev)
 
     def step():
@@ -193,10 +201,11 @@ def run_fit(args, rank, local_rank, world, dist):
             'metric': 'smpl_fit_sample_steps_per_s', 'value': world * B * args.steps / (ms * 1e-3), 'unit': 'sample-steps/s',
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms / args.steps,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': 'SMPL fitting, fwd+bwd of the 2D re-projection loss + TF1 Adam on theta, B=%d per GPU '
-                                   '(BASELINE configs[2])' % B, 'cuda_graph': graph is not None,
+            'config': {'workload': ('SMPL fitting, fwd+bwd of the %s + TF1 Adam on theta, B=%d per GPU (BASELINE configs[2])'
+                                    % ('3D mesh + joint loss (backward through the vertices)' if mesh else
+                                       '2D re-projection loss', B)), 'cuda_graph': graph is not None,
                        'collective': 'all-reduce of 1 loss scalar per step' if world > 1 else 'none'},
-            'gpu_launches': 5 * args.steps, 'loss_first': first, 'loss_last': float(f.loss[0]) * (1 if world == 1 else 1)}),
+            'gpu_launches': (15 if mesh else 5) * args.steps, 'loss_first': first, 'loss_last': float(f.loss[0]) * (1 if world == 1 else 1)}),
             flush=True)
     if dist is not None:
         dist.barrier()
@@ -507,6 +516,7 @@ def main():
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep', 'raster', 'normals'],
                     help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
+    ap.add_argument('--loss', choices=['reproj', 'mesh'], default='reproj', help='fit mode: which loss drives the step')
     ap.add_argument('--graph', action='store_true', help='fit mode: replay the step from a CUDA graph')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)

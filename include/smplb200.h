@@ -283,6 +283,16 @@ int32_t smplb_cam_losses(int32_t B, const float* gt_joints3d, const float* gt_jo
                          float angle_scale, float* loss_out, float* g_cam_pos, float* g_cam_rot, float* g_cam_f,
                          float* g_f_raw, void* scratch, void* stream);
 
+/* 3D losses of deps/pose_3d/pose_model_3d.py:183-192 (tf.losses.mean_squared_error with a scalar weight):
+ * loss_out[0] (+)= weight * sum((pred - target)^2) / n_total, and, when g_out is given, its gradient w.r.t. pred,
+ * g_out[i] = 2 * weight / n_total * (pred[i] - target[i]).  n_total = element count of the global mean (n, or the
+ * count over all ranks when the batch is sharded).  mesh_loss: weight 1.0 on verts [B,6890,3]; joint_loss: weight
+ * 2.0 on J_transformed [B,24,3] (config.py:17-18).  accumulate != 0 adds to loss_out[0] (loss3d = mesh + joint).
+ * Fixed-order reduction; scratch: smplb_mse_scratch_bytes() of device memory. */
+size_t smplb_mse_scratch_bytes(void);
+int32_t smplb_mse_grad(int64_t n, const float* pred, const float* target, float weight, int64_t n_total,
+                       float* g_out, float* loss_out, int32_t accumulate, void* scratch, void* stream);
+
 /* Measurement aid (no reference counterpart): while enabled, every smplb_forward on this host thread
  * records CUDA events on its stream around pose_prep / blend GEMM / skinning / keypoints.
  * smplb_timing_end synchronises those events and writes ms_out[call][4] = {prep, blend, skin, keypoints}

@@ -88,3 +88,47 @@ def test_fit_step_in_cuda_graph(gpu_model, synth_dd):
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(fa.theta, fb.theta)
+
+
+def test_mse_grad_value_and_gradient():
+    """smplb_mse_grad = tf.losses.mean_squared_error with a scalar weight (pose_model_3d.py:183-192)."""
+    import smplb200
+    rng = np.random.default_rng(0)
+    for n, w in ((1, 1.0), (1000, 2.0), (3 * 6890 * 5, 1.0)):
+        a, b = rng.normal(size=n).astype(np.float32), rng.normal(size=n).astype(np.float32)
+        loss, g = smplb200.mse_grad(a, b, weight=w)
+        want = w * np.mean((a.astype(np.float64) - b) ** 2)
+        assert abs(float(loss[0]) - want) <= 1e-5 * want
+        assert maxrel(g.cpu().numpy(), 2 * w / n * (a.astype(np.float64) - b)) <= 1e-6
+        loss2, _ = smplb200.mse_grad(a, b, weight=w, loss_out=loss, accumulate=True, want_grad=False)
+        assert abs(float(loss2[0]) - 2 * want) <= 1e-5 * want
+        l3, _ = smplb200.mse_grad(a, b, weight=w, want_grad=False)
+        assert float(l3[0]) == float(smplb200.mse_grad(a, b, weight=w, want_grad=False)[0][0])   # run-to-run identical
+
+
+def test_mesh_fit_first_steps_match_oracle(gpu_model, synth_dd):
+    """3D-loss fitting (mesh + joint MSE, pose_model_3d.py:183-192) through the vertex backward vs the float64
+    autograd + TF1-Adam trajectory."""
+    from smplb200.fit import MeshFitter
+    B, steps, lr = 6, 3, 1e-2
+    m64 = rt.load_model(synth_dd, dtype=torch.float64)
+    inp = syn.make_inputs(B, seed=31, dtype=np.float32)
+    rng = np.random.default_rng(4)
+    theta0 = (inp['theta'] + rng.normal(0, 0.1, size=inp['theta'].shape)).astype(np.float32)
+    with torch.no_grad():
+        tgt = rt.smpl_forward(m64, _t64(inp['beta']), _t64(inp['theta']), tile_W=False)
+    gv, gj = tgt['verts'].numpy(), tgt['J_transformed'].numpy()
+    f = MeshFitter(gpu_model, inp['beta'], theta0, gv.astype(np.float32), gj.astype(np.float32), lr=lr)
+    losses = [float(f.step()[0]) for _ in range(steps)]
+    theta = theta0.astype(np.float64)
+    mt, vt, want = 0 * theta, 0 * theta, []
+    for t in range(1, steps + 1):
+        th = _t64(theta, True)
+        o = rt.smpl_forward(m64, _t64(inp['beta']), th, tile_W=False)
+        loss = rt.loss3d(_t64(gv), o['verts'], _t64(gj), o['J_transformed'])
+        want.append(float(loss.detach()))
+        loss.backward()
+        theta, mt, vt = rn.adam_tf1(theta, th.grad.numpy(), mt, vt, t, lr=lr)
+    assert maxrel(np.array(losses), np.array(want)) <= 1e-4
+    assert maxrel(f.theta.cpu().numpy(), theta) <= 1e-4
+    assert losses[-1] < losses[0]
