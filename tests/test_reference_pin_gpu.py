@@ -98,11 +98,12 @@ def test_losses_vs_get_encoder_losses(gpu_model, case):
     o = {k: v.clone() for k, v in gpu_model.forward(betas, out_pose, cam_pos, cam_rot, focal).items() if k != '_keep'}
     q = {k: v.clone() for k, v in gpu_model.forward(betas, gt_pose, cam_pos, cam_rot, focal).items() if k != '_keep'}
     # 3D loss (:183-192): value, and gradient through the vertex path
-    dv, dj = o['verts'] - q['verts'], o['joints'] - q['joints']
-    l3d = float((dv.double() ** 2).mean() * 1.0 + (dj.double() ** 2).mean() * 2.0)
+    l3, g_v = smplb200.mse_grad(o['verts'], q['verts'], weight=1.0)                           # mesh_loss  (:184-186)
+    l3, g_j = smplb200.mse_grad(o['joints'], q['joints'], weight=2.0, loss_out=l3, accumulate=True)   # joint_loss (:187-189)
+    l3d = float(l3[0])
     assert abs(l3d - float(p('term_3d_loss'))) <= TOL * abs(l3d)
     gpu_model.forward(betas, out_pose, flags=_lib.F_KEEP_VPOSED)
-    _, gt = gpu_model.backward(betas, out_pose, g_verts=(2.0 / dv.numel()) * dv, g_joints=(2.0 * 2.0 / dj.numel()) * dj)
+    _, gt = gpu_model.backward(betas, out_pose, g_verts=g_v, g_joints=g_j)
     want = p('g_3d_loss')[:, :72].copy()
     got = cpu(gt)
     got[:, :3] = 0.0                                    # the global rotation is the ground truth's, no gradient to it
