@@ -280,8 +280,24 @@ def run_sweep(args, rank, local_rank, world, dist):
                 res['blend_tf32_util_issued'] = 3 * res['blend_tf32_util_fp32eq']
         rows.append(res)
         del g_verts, out, d
+    cpu_rows = []
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # the CPU port of the reference op sequence at B in {1, 32, 256, 1024} (BASELINE configs[0] is the
+        # B = 1 case), median over the repetitions that fit in ~3 s each, all host threads
+        import statistics
+        for Bc in (1, 32, 256, 1024):
+            _, cores, _, _, step = cpu_reference_rate(Bc, 0.0, 1)
+            ts, t_end = [], time.perf_counter() + 3.0
+            while len(ts) < 50 and (time.perf_counter() < t_end or len(ts) < 3):
+                t0 = time.perf_counter()
+                step()
+                ts.append(time.perf_counter() - t0)
+            med = statistics.median(ts)
+            cpu_rows.append({'B': Bc, 'ms': 1e3 * med, 'samples_per_s': Bc / med, 'reps': len(ts), 'cores': cores,
+                             'kind': 'port'})
     if rank == 0:
         print(json.dumps({'metric': 'smpl_sweep', 'n_gpus': world, 'scaling': 'weak', 'dtype': 'f32', 'data': 'synthetic',
+                          'cpu_port_rows': cpu_rows,
                           'peaks': {'hbm_gbs': peak, 'tf32_tflops': tf32_peak, 'source': peak_src},
                           'config': {'workload': 'BASELINE configs[4]: batch sweep, fwd+projection and fwd+bwd '
                                                  '(g_verts + g_joints -> g_theta, g_beta), B per GPU'},
