@@ -176,12 +176,17 @@ def run_fit(args, rank, local_rank, world, dist):
         step()
     first = float(gl)
     graph = None
-    if args.graph and world == 1:
+    if args.graph:
+        # the whole step -- kernels and, with several GPUs, the NCCL all-reduce of the loss scalar -- replayed from
+        # one CUDA graph: the 50 us step is host-launch-bound otherwise
         s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
+            step()          # the collective once on the capture stream before capturing it
+            torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=s):
-                f.step()
+                step() if world > 1 else f.step()
         torch.cuda.current_stream().wait_stream(s)
     torch.cuda.synchronize()
     if dist is not None:
@@ -207,6 +212,12 @@ def run_fit(args, rank, local_rank, world, dist):
                        'collective': 'all-reduce of 1 loss scalar per step' if world > 1 else 'none'},
             'gpu_launches': (15 if mesh else 5) * args.steps, 'loss_first': first, 'loss_last': float(f.loss[0]) * (1 if world == 1 else 1)}),
             flush=True)
+    if graph is not None:
+        # a captured NCCL collective keeps the communicator busy: drop the graph before tearing the group down
+        # (destroy_process_group otherwise waits forever)
+        graph.reset()
+        graph = None
+        torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
