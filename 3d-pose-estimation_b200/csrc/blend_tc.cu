@@ -46,7 +46,7 @@ struct TcSmem {
 };
 
 // One 32-row x 32-column block of the accumulator: registers (thread = row) -> smem -> coalesced stores.
-__device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* stage, int lane, const float* vrow,
+__device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* stage, int lane, const float4 tv,
                                                float* obase, int rows_valid) {
 #pragma unroll
   for (int j = 0; j < 8; ++j)
@@ -55,7 +55,6 @@ __device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* s
                     __uint_as_float(r[4 * j + 3]));
   __syncwarp();
   const int c4 = (lane & 7) * 4, rsub = lane >> 3;
-  const float4 tv = __ldg(reinterpret_cast<const float4*>(vrow + c4));
 #pragma unroll
   for (int it = 0; it < 8; ++it) {
     const int row = it * 4 + rsub;
@@ -133,9 +132,10 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
         }
     } else {
       // ================= MMA issuer (leader CTA) =================
-      constexpr uint32_t idesc = umma_idesc(2, 2 * BL_BM, BL_BN);
+      constexpr uint32_t idesc = umma_idesc(2, 2 * BL_BM, BL_BN);     // kind::tf32
+      constexpr uint32_t idesc16 = umma_idesc(1, 2 * BL_BM, BL_BN);   // kind::f16, bf16 operands
       constexpr uint32_t LBO = BL_BM * 16, SBO = 128;                 // bytes; X and D halves are both 128 rows
-      constexpr uint32_t HL = (BL_KB / 4) * LBO;                      // hi -> lo offset inside a stage
+      constexpr uint32_t B16_0 = BL_SLAB * 2, B16_1 = BL_SLAB * 3;    // byte offsets of the bf16 parts in a slab
       static_assert(BL_BM == BL_BH, "one descriptor template for both operands");
       const uint64_t dtempl = umma_desc_kmajor_noswz(0, LBO, SBO);
       const uint32_t empty0 = smem_u32(&sm.empty[0]);
@@ -154,13 +154,12 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
           const uint64_t xd = dtempl + (uint64_t)(xb0 + s * (TC_X_STAGE_FLOATS * 4 / 16));
           const uint64_t dd = dtempl + (uint64_t)(db0 + s * (TC_D_STAGE_FLOATS * 4 / 16));
 #pragma unroll
-          for (int ks = 0; ks < BL_KB / 8; ++ks) {
-            const uint64_t xh = xd + (uint64_t)(ks * 2 * LBO / 16), xl = xh + (uint64_t)(HL / 16);
-            const uint64_t dh = dd + (uint64_t)(ks * 2 * LBO / 16), dl = dh + (uint64_t)(HL / 16);
-            umma_tf32_ss_pair(dcol, xh, dh, idesc, (kb | ks) != 0, issue);
-            umma_tf32_ss_pair(dcol, xl, dh, idesc, 1, issue);
-            umma_tf32_ss_pair(dcol, xh, dl, idesc, 1, issue);
-          }
+          for (int ks = 0; ks < BL_KB / 8; ++ks)   // Xh.Dh in TF32: two K = 8 steps
+            umma_tf32_ss_pair(dcol, xd + (uint64_t)(ks * 2 * LBO / 16), dd + (uint64_t)(ks * 2 * LBO / 16), idesc,
+                              (kb | ks) != 0, issue);
+          // corrections in bf16, one K = 16 step each: bf16(Xl).bf16(Dh) + bf16(X).bf16(Dl)
+          umma_f16_ss_pair(dcol, xd + (uint64_t)(B16_0 / 16), dd + (uint64_t)(B16_0 / 16), idesc16, 1, issue);
+          umma_f16_ss_pair(dcol, xd + (uint64_t)(B16_1 / 16), dd + (uint64_t)(B16_1 / 16), idesc16, 1, issue);
           umma_commit_pair(empty0 + s * 8, 3, issue);                                        // stage free in both CTAs
           if (kb == BL_NKB - 1) umma_commit_pair(smem_u32(&sm.acc_full[a]), 3, issue);       // accumulator complete
           if (++s == TC_STAGES) { s = 0; ph ^= 1; }
@@ -176,20 +175,26 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
     for (int t = cl; t < n_tiles; t += n_cl, ++tl) {
       const int mt2 = t / BL_NT, nt = t % BL_NT;
       const int a = tl & 1;
-      mbar_wait(&sm.acc_full[a], (tl >> 1) & 1);
-      tc_fence_after();
       const int row0 = (mt2 * 2 + (int)rank) * BL_BM + q * 32;
       const int rows_valid = B - row0;   // <= 0: nothing to store (padding tile)
       float* obase = vposed + (size_t)row0 * VPP + (size_t)nt * BL_BN;
-      const float* vrow = vt + (size_t)nt * BL_BN;
+      // v_template of this N tile (thread: 4 columns of each 32-column block), fetched BEFORE the accumulator wait:
+      // a load inside the store loop put an L2 round trip on the critical path of every block (ncu: half of the
+      // epilogue warps' samples), which bounds the kernel once the MMAs of a tile take less time than its epilogue
+      float4 tv[BL_BN / 32];
+#pragma unroll
+      for (int j = 0; j < BL_BN / 32; ++j)
+        tv[j] = __ldg(reinterpret_cast<const float4*>(vt + (size_t)nt * BL_BN + j * 32 + (lane & 7) * 4));
+      mbar_wait(&sm.acc_full[a], (tl >> 1) & 1);
+      tc_fence_after();
       const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)a * BL_BN;
       uint32_t ra[32], rb[32];
       tmem_ld32(tbase, ra);
-#pragma unroll 1
+#pragma unroll
       for (int c0 = 0; c0 < BL_BN; c0 += 64) {
         tmem_ld_wait();
         tmem_ld32(tbase + c0 + 32, rb);
-        tc_store_block(ra, stage, lane, vrow + c0, obase + c0, rows_valid);
+        tc_store_block(ra, stage, lane, tv[c0 / 32], obase + c0, rows_valid);
         tmem_ld_wait();
         if (c0 + 64 < BL_BN) {
           tmem_ld32(tbase + c0 + 64, ra);
@@ -199,7 +204,7 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
           __syncwarp();
           if (lane == 0) mbar_arrive_remote(&sm.acc_empty[a], 0);
         }
-        tc_store_block(rb, stage, lane, vrow + c0 + 32, obase + c0 + 32, rows_valid);
+        tc_store_block(rb, stage, lane, tv[c0 / 32 + 1], obase + c0 + 32, rows_valid);
       }
     }
   }

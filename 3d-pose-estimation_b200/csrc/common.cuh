@@ -64,7 +64,7 @@ struct smplb_model {
   float* v_template_pad;  // [VPP]   v_template flattened (3v+c), zero padded
   // blend-shape basis D = [shapedirs; posedirs] : K=217 rows, padded to KPAD x VPP
   float* D32;             // [KPAD][VPP] fp32 (SIMT verification path, backward)
-  float* Dimg;            // [BL_NT][BL_DTILE] TF32 hi/lo operand image of D (tcgen05 B operand)
+  float* Dimg;            // [BL_NT][BL_DTILE] tf32 + bf16 operand image of D (tcgen05 B operand, dimg_*_off)
   // folded joint regression: J = Jbar + JS * beta  (batch_smpl.py:91-101)
   float* Jbar;            // [24*3]
   float* JS;              // [24*3*10]
@@ -118,7 +118,7 @@ struct PrepParams {
   const float* theta;
   const float* Jbar;
   const float* JS;
-  float* Ximg;    // [ceil(B/128)][BL_XTILE] TF32 hi/lo operand image of [beta | pose feature], nullable
+  float* Ximg;    // [ceil(B/128)][BL_XTILE] tf32 + bf16 operand image of [beta | pose feature] (ximg_*_off), nullable
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
@@ -189,16 +189,47 @@ __host__ __device__ inline size_t dtimg_off(int k, int n, int hl) {
   return (size_t)(n / BB_KB) * BB_DSTAGE + (size_t)(((hl * (BB_KB / 4) + (n % BB_KB) / 4) * KPAD + k) * 4 + (n & 3));
 }
 
-// float offset of element (row b, k) of the X operand image; hl = 0 (hi) / 1 (lo)
-__host__ __device__ inline size_t ximg_off(int b, int k, int hl) {
-  return (size_t)(b / BL_BM) * BL_XTILE +
-         (size_t)((((k / BL_KB) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (k & 3);
+// Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated as
+//     X.D ~= Xh.Dh (kind::tf32)  +  bf16(Xl).bf16(Dh)  +  bf16(X).bf16(Dl)   (kind::f16, bf16 operands)
+// with Xh = tf32(X), Xl = X - Xh (same for D): the two correction products only have to be good to ~2^-9
+// relative, and a bf16 MMA (K = 16) costs what a TF32 MMA (K = 8) costs, so the tensor time is 4/6 of 3xTF32.
+// Per 16-element k-block a 128-row operand slab is 16 KB:
+//     [0, 8 KB)    tf32 hi part, 4 K-chunks x 128 rows x 16 B
+//     [8, 12 KB)   bf16 part 0,  2 K-chunks x 128 rows x 16 B (8 elements)     X: bf16(Xl)   D: bf16(Dh)
+//     [12, 16 KB)  bf16 part 1                                                  X: bf16(X)    D: bf16(Dl)
+#define BL_SLAB 4096   // floats per (k-block, 128 rows) slab
+// float offset of the tf32 hi part of element (row b, k) of the X operand image
+__host__ __device__ inline size_t ximg_hi_off(int b, int k) {
+  return (size_t)(b / BL_BM) * BL_XTILE + (size_t)(k / BL_KB) * BL_SLAB +
+         (size_t)(((k % BL_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (k & 3);
 }
-// float offset of element (column n, k) of the D operand image
-__host__ __device__ inline size_t dimg_off(int n, int k, int hl) {
+// 16-bit-element offset of bf16 part `part` of element (row b, k) of the X operand image
+__host__ __device__ inline size_t ximg_b16_off(int b, int k, int part) {
+  return ((size_t)(b / BL_BM) * BL_XTILE + (size_t)(k / BL_KB) * BL_SLAB) * 2 + (size_t)(BL_SLAB + part * (BL_SLAB / 2)) +
+         (size_t)(((k % BL_KB) / 8) * BL_BM + (b % BL_BM)) * 8 + (k & 7);
+}
+// the same for element (column n, k) of the D operand image: slabs ordered [n-tile][k-block][column half]
+__host__ __device__ inline size_t dimg_hi_off(int n, int k) {
   const int half = (n % BL_BN) / BL_BH;
-  return (size_t)(n / BL_BN) * BL_DTILE +
-         (size_t)(((((k / BL_KB) * 2 + half) * 2 + hl) * (BL_KB / 4) + (k % BL_KB) / 4) * BL_BH + (n % BL_BH)) * 4 + (k & 3);
+  return (size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_SLAB +
+         (size_t)(((k % BL_KB) / 4) * BL_BH + (n % BL_BH)) * 4 + (k & 3);
+}
+__host__ __device__ inline size_t dimg_b16_off(int n, int k, int part) {
+  const int half = (n % BL_BN) / BL_BH;
+  return ((size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_SLAB) * 2 +
+         (size_t)(BL_SLAB + part * (BL_SLAB / 2)) + (size_t)(((k % BL_KB) / 8) * BL_BH + (n % BL_BH)) * 8 + (k & 7);
+}
+// fp32 -> bf16 bits, round to nearest even (finite inputs)
+__host__ __device__ inline unsigned short bf16_rne_bits(float x) {
+  union { float f; uint32_t u; } c;
+  c.f = x;
+  c.u += 0x7FFFu + ((c.u >> 16) & 1u);
+  return (unsigned short)(c.u >> 16);
+}
+__host__ __device__ inline float bf16_bits_to_float(unsigned short h) {
+  union { float f; uint32_t u; } c;
+  c.u = (uint32_t)h << 16;
+  return c.f;
 }
 int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
                          cudaStream_t st);

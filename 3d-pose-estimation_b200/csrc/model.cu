@@ -115,12 +115,14 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
       for (int k = 0; k < NP; ++k) D32[(size_t)(NB + k) * VPP + col] = posedirs[(size_t)k * NV3 + 3 * v + c];
     }
   std::vector<float> Dimg((size_t)BL_NT * BL_DTILE, 0.f);
+  unsigned short* d16 = reinterpret_cast<unsigned short*>(Dimg.data());
   for (int k = 0; k < KDIM; ++k)
     for (int n = 0; n < VPP; ++n) {
       const float x = D32[(size_t)k * VPP + n];
       const float hi = tf32_rna_host(x);
-      Dimg[dimg_off(n, k, 0)] = hi;
-      Dimg[dimg_off(n, k, 1)] = tf32_rna_host(x - hi);
+      Dimg[dimg_hi_off(n, k)] = hi;
+      d16[dimg_b16_off(n, k, 0)] = bf16_rne_bits(hi);
+      d16[dimg_b16_off(n, k, 1)] = bf16_rne_bits(x - hi);
     }
   std::vector<float> vt(VPP, 0.f);
   for (int v = 0; v < NV; ++v)

@@ -56,8 +56,10 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       const int k = lane + 32 * i;
       const float v = x[k];
       const float hi = tf32_rna(v);
-      p.Ximg[ximg_off(b, k, 0)] = hi;
-      p.Ximg[ximg_off(b, k, 1)] = tf32_rna(v - hi);
+      unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg);
+      p.Ximg[ximg_hi_off(b, k)] = hi;
+      x16[ximg_b16_off(b, k, 0)] = bf16_rne_bits(v - hi);
+      x16[ximg_b16_off(b, k, 1)] = bf16_rne_bits(v);
     }
   }
 

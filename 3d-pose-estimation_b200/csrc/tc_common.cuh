@@ -204,6 +204,17 @@ __device__ __forceinline__ void umma_tf32_ss_pair(uint32_t d_tmem, uint64_t ades
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
       : "memory");
 }
+// the same with 16-bit operands (f16 / bf16 per the instruction descriptor): K = 16 per instruction
+__device__ __forceinline__ void umma_f16_ss_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                 uint32_t accumulate, uint32_t issue) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
+      : "memory");
+}
 // completion of all MMAs issued so far -> one arrival on the mbarrier at this offset in every CTA of `mask`
 __device__ __forceinline__ void umma_commit_pair(uint32_t bar_smem_addr, uint16_t mask, uint32_t issue) {
   asm volatile(
