@@ -1,18 +1,25 @@
 // K2 blend-shape GEMM on the 5th-generation tensor cores (batch_smpl.py:91-95, :113-115):
 //     v_posed[B, 20670] = [beta | pose_feature][B, 217] . [shapedirs; posedirs][217, 20670] + v_template
-// in 3xTF32 so the result stays fp32-faithful: with X = Xhi + Xlo and D = Dhi + Dlo (each part exactly
-// representable in TF32), acc += Xhi.Dhi + Xlo.Dhi + Xhi.Dlo (the dropped Xlo.Dlo term is ~2^-22).
+// fp32-faithful on the tensor cores from 16-bit operands (operand images and error analysis: common.cuh):
+//     acc += f16(X).f16(D) + bf16(X - f16(X)).bf16(f16(D)) + bf16(X).bf16(D - f16(D))
+// three kind::f16 MMAs (K = 16) per 16-element k-block, fp32 accumulation in TMEM.  History of this kernel at
+// B = 65536: 3xTF32, 6 MMA slots and 8 B per element: 2.50 ms (tensor pipe 83 % busy);  TF32 main product + two
+// bf16 corrections, 4 slots, 8 B: 2.41 ms, bound by the EPILOGUE (an L2 round trip for v_template in every
+// 32-column block), 2.08 ms with that load hoisted above the accumulator wait, then at the ~43 B/clk/SM the L2
+// delivers (ncu: 19.1 GB of operands in 2.9 M cycles);  keeping the TF32 part of X resident in smem cut the
+// operand stream by 25 % but left room for only 4 x 24 KB stages and became latency-bound (2.28 ms, rejected);
+// fp16 main product (same 11 significant bits as TF32): 3 slots, 6 B per element, 8 x 24 KB stages.
 //
 // v2 organisation: CTA PAIRS (cluster of 2 = one TPC, tcgen05 cta_group::2), persistent over 256 x 256
 // output tiles.  v1 (one CTA per 128 x 256 tile, 2 x 96 KB stages) pulled 688 KB of operands from L2 per
 // tile = 64 B/clk/SM at the tensor-pipe rate, more than the L2 delivers (~43 B/clk/SM): tensor pipe 50 %
-// busy.  A pair shares the D tile (each CTA stages one 128-column half), so a CTA reads 458 KB per
-// 128 x 256 outputs, and the smaller stages (32 KB) make a 6-deep ring.
+// busy.  A pair shares the D tile (each CTA stages one 128-column half), so a CTA reads 344 KB per
+// 128 x 256 outputs, and the smaller stages (24 KB) make an 8-deep ring.
 //   warp 0    producer : per k-block one 1-D bulk copy (TMA engine) of its 128 X rows and one of its D half
-//                        into a 6-stage smem ring; the operands sit in global memory as ready-made smem
+//                        into an 8-stage smem ring; the operands sit in global memory as ready-made smem
 //                        images (common.cuh)
-//   warp 1    leader CTA: one thread issues tcgen05.mma.cta_group::2.kind::tf32 (M=256, N=256, K=8) x 3
-//                        products x 28 k-steps per tile into one of two 256-column TMEM accumulators (each
+//   warp 1    leader CTA: one thread issues tcgen05.mma.cta_group::2.kind::f16 (M=256, N=256, K=16) x 3
+//                        products x 14 k-blocks per tile into one of two 256-column TMEM accumulators (each
 //                        CTA holds its 128 rows); commits are multicast to both CTAs' barriers.
 //             peer CTA : one thread relays "my stage is full" to the leader's peer_full barrier
 //   warps 2-5 epilogue : tcgen05.ld the accumulator (lane = sample row), transpose 32 x 32 blocks through
@@ -25,9 +32,9 @@ namespace smplb {
 
 using namespace tc;
 
-constexpr int TC_STAGES = 6;
-constexpr int TC_X_STAGE_FLOATS = 2 * (BL_KB / 4) * BL_BM * 4;   // hi+lo : 4096 floats = 16 KB
-constexpr int TC_D_STAGE_FLOATS = 2 * (BL_KB / 4) * BL_BH * 4;   // hi+lo of one half : 4096 floats = 16 KB
+constexpr int TC_STAGES = 8;
+constexpr int TC_X_STAGE_FLOATS = BL_SLAB;   // one X slab: 3 parts x 4 KB
+constexpr int TC_D_STAGE_FLOATS = BL_SLAB;   // one D half slab
 constexpr uint32_t TC_STAGE_BYTES = (TC_X_STAGE_FLOATS + TC_D_STAGE_FLOATS) * 4;
 constexpr int TC_THREADS = 192;
 constexpr int TC_TMEM_COLS = 512;
@@ -132,10 +139,10 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
         }
     } else {
       // ================= MMA issuer (leader CTA) =================
-      constexpr uint32_t idesc = umma_idesc(2, 2 * BL_BM, BL_BN);     // kind::tf32
-      constexpr uint32_t idesc16 = umma_idesc(1, 2 * BL_BM, BL_BN);   // kind::f16, bf16 operands
+      constexpr uint32_t idesc_h = umma_idesc(0, 2 * BL_BM, BL_BN);   // kind::f16, f16 operands
+      constexpr uint32_t idesc_b = umma_idesc(1, 2 * BL_BM, BL_BN);   // kind::f16, bf16 operands
       constexpr uint32_t LBO = BL_BM * 16, SBO = 128;                 // bytes; X and D halves are both 128 rows
-      constexpr uint32_t B16_0 = BL_SLAB * 2, B16_1 = BL_SLAB * 3;    // byte offsets of the bf16 parts in a slab
+      constexpr uint32_t PART = BL_PART16 * 2 / 16;                   // one 4 KB part in descriptor units
       static_assert(BL_BM == BL_BH, "one descriptor template for both operands");
       const uint64_t dtempl = umma_desc_kmajor_noswz(0, LBO, SBO);
       const uint32_t empty0 = smem_u32(&sm.empty[0]);
@@ -153,13 +160,9 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
           tc_fence_after();
           const uint64_t xd = dtempl + (uint64_t)(xb0 + s * (TC_X_STAGE_FLOATS * 4 / 16));
           const uint64_t dd = dtempl + (uint64_t)(db0 + s * (TC_D_STAGE_FLOATS * 4 / 16));
-#pragma unroll
-          for (int ks = 0; ks < BL_KB / 8; ++ks)   // Xh.Dh in TF32: two K = 8 steps
-            umma_tf32_ss_pair(dcol, xd + (uint64_t)(ks * 2 * LBO / 16), dd + (uint64_t)(ks * 2 * LBO / 16), idesc,
-                              (kb | ks) != 0, issue);
-          // corrections in bf16, one K = 16 step each: bf16(Xl).bf16(Dh) + bf16(X).bf16(Dl)
-          umma_f16_ss_pair(dcol, xd + (uint64_t)(B16_0 / 16), dd + (uint64_t)(B16_0 / 16), idesc16, 1, issue);
-          umma_f16_ss_pair(dcol, xd + (uint64_t)(B16_1 / 16), dd + (uint64_t)(B16_1 / 16), idesc16, 1, issue);
+          umma_f16_ss_pair(dcol, xd, dd, idesc_h, kb != 0, issue);                                  // f16(X).f16(D)
+          umma_f16_ss_pair(dcol, xd + (uint64_t)PART, dd + (uint64_t)PART, idesc_b, 1, issue);          // bf16(Xl).bf16(Dh)
+          umma_f16_ss_pair(dcol, xd + (uint64_t)(2 * PART), dd + (uint64_t)(2 * PART), idesc_b, 1, issue);   // bf16(X).bf16(Dl)
           umma_commit_pair(empty0 + s * 8, 3, issue);                                        // stage free in both CTAs
           if (kb == BL_NKB - 1) umma_commit_pair(smem_u32(&sm.acc_full[a]), 3, issue);       // accumulator complete
           if (++s == TC_STAGES) { s = 0; ph ^= 1; }

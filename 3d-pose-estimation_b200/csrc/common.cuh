@@ -1,5 +1,6 @@
 // Shared declarations of the smplb200 library (sm_100a only).
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -29,8 +30,9 @@
 #define BL_KB 16                // K elements per pipeline stage (k-block) = 4 chunks of 4
 #define BL_NKB (KPAD / BL_KB)   // 14 k-blocks
 #define BL_NT (VPP / BL_BN)     // 81 N tiles
-#define BL_XTILE (BL_NKB * 2 * (BL_KB / 4) * BL_BM * 4)   // floats per X m-tile image (57344)
-#define BL_DTILE (BL_NKB * 2 * (BL_KB / 4) * BL_BN * 4)   // floats per D n-tile image (114688)
+#define BL_SLAB (3 * BL_KB * BL_BM / 2)   // floats per (k-block, 128 rows) operand slab: 3 sixteen-bit parts = 12 KB
+#define BL_XTILE (BL_NKB * BL_SLAB)       // floats per X m-tile image (43008)
+#define BL_DTILE (BL_NKB * 2 * BL_SLAB)   // floats per D n-tile image (86016): [k-block][column half] slabs
 
 namespace smplb {
 
@@ -64,7 +66,7 @@ struct smplb_model {
   float* v_template_pad;  // [VPP]   v_template flattened (3v+c), zero padded
   // blend-shape basis D = [shapedirs; posedirs] : K=217 rows, padded to KPAD x VPP
   float* D32;             // [KPAD][VPP] fp32 (SIMT verification path, backward)
-  float* Dimg;            // [BL_NT][BL_DTILE] tf32 + bf16 operand image of D (tcgen05 B operand, dimg_*_off)
+  float* Dimg;            // [BL_NT][BL_DTILE] f16/bf16 operand image of D (tcgen05 B operand, dimg16_off)
   // folded joint regression: J = Jbar + JS * beta  (batch_smpl.py:91-101)
   float* Jbar;            // [24*3]
   float* JS;              // [24*3*10]
@@ -118,7 +120,7 @@ struct PrepParams {
   const float* theta;
   const float* Jbar;
   const float* JS;
-  float* Ximg;    // [ceil(B/128)][BL_XTILE] tf32 + bf16 operand image of [beta | pose feature] (ximg_*_off), nullable
+  float* Ximg;    // [ceil(B/128)][BL_XTILE] f16/bf16 operand image of [beta | pose feature] (ximg16_off), nullable
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
@@ -189,35 +191,26 @@ __host__ __device__ inline size_t dtimg_off(int k, int n, int hl) {
   return (size_t)(n / BB_KB) * BB_DSTAGE + (size_t)(((hl * (BB_KB / 4) + (n % BB_KB) / 4) * KPAD + k) * 4 + (n & 3));
 }
 
-// Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated as
-//     X.D ~= Xh.Dh (kind::tf32)  +  bf16(Xl).bf16(Dh)  +  bf16(X).bf16(Dl)   (kind::f16, bf16 operands)
-// with Xh = tf32(X), Xl = X - Xh (same for D): the two correction products only have to be good to ~2^-9
-// relative, and a bf16 MMA (K = 16) costs what a TF32 MMA (K = 8) costs, so the tensor time is 4/6 of 3xTF32.
-// Per 16-element k-block a 128-row operand slab is 16 KB:
-//     [0, 8 KB)    tf32 hi part, 4 K-chunks x 128 rows x 16 B
-//     [8, 12 KB)   bf16 part 0,  2 K-chunks x 128 rows x 16 B (8 elements)     X: bf16(Xl)   D: bf16(Dh)
-//     [12, 16 KB)  bf16 part 1                                                  X: bf16(X)    D: bf16(Dl)
-#define BL_SLAB 4096   // floats per (k-block, 128 rows) slab
-// float offset of the tf32 hi part of element (row b, k) of the X operand image
-__host__ __device__ inline size_t ximg_hi_off(int b, int k) {
-  return (size_t)(b / BL_BM) * BL_XTILE + (size_t)(k / BL_KB) * BL_SLAB +
-         (size_t)(((k % BL_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (k & 3);
-}
-// 16-bit-element offset of bf16 part `part` of element (row b, k) of the X operand image
-__host__ __device__ inline size_t ximg_b16_off(int b, int k, int part) {
-  return ((size_t)(b / BL_BM) * BL_XTILE + (size_t)(k / BL_KB) * BL_SLAB) * 2 + (size_t)(BL_SLAB + part * (BL_SLAB / 2)) +
+// Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated fp32-faithfully from 16-bit operands:
+//     X.D ~= f16(X).f16(D)  +  bf16(Xl).bf16(f16(D))  +  bf16(X).bf16(Dl),    Xl = X - f16(X), Dl = D - f16(D)
+// (kind::f16 MMAs, K = 16 each, fp32 accumulation).  fp16 carries the same 11 significant bits as TF32 at twice
+// the tensor rate and half the bytes; the two correction products are 2^-11 of the main one, so bf16's 8 bits
+// (and its fp32 exponent range: the residuals fall below the fp16 normal range) are enough for them.
+// Error ~2^-20 of the blend offsets (tests/test_blend_split.py).  3 MMA slots and 6 bytes per element against
+// 6 slots and 8 bytes for 3xTF32 (Xh.Dh + Xl.Dh + Xh.Dl, the first version of this round).
+// Per 16-element k-block a 128-row operand slab is 12 KB = three 4 KB parts, each 2 K-chunks x 128 rows x 16 B:
+//     part 0  f16(X)  | f16(D)         part 1  bf16(Xl) | bf16(f16(D))         part 2  bf16(X) | bf16(Dl)
+#define BL_PART16 (BL_KB * BL_BM)   // 16-bit elements per part (2048)
+// 16-bit-element offset of part `part` of element (row b, k) of the X operand image
+__host__ __device__ inline size_t ximg16_off(int b, int k, int part) {
+  return ((size_t)(b / BL_BM) * BL_XTILE + (size_t)(k / BL_KB) * BL_SLAB) * 2 + (size_t)part * BL_PART16 +
          (size_t)(((k % BL_KB) / 8) * BL_BM + (b % BL_BM)) * 8 + (k & 7);
 }
 // the same for element (column n, k) of the D operand image: slabs ordered [n-tile][k-block][column half]
-__host__ __device__ inline size_t dimg_hi_off(int n, int k) {
+__host__ __device__ inline size_t dimg16_off(int n, int k, int part) {
   const int half = (n % BL_BN) / BL_BH;
-  return (size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_SLAB +
-         (size_t)(((k % BL_KB) / 4) * BL_BH + (n % BL_BH)) * 4 + (k & 3);
-}
-__host__ __device__ inline size_t dimg_b16_off(int n, int k, int part) {
-  const int half = (n % BL_BN) / BL_BH;
-  return ((size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_SLAB) * 2 +
-         (size_t)(BL_SLAB + part * (BL_SLAB / 2)) + (size_t)(((k % BL_KB) / 8) * BL_BH + (n % BL_BH)) * 8 + (k & 7);
+  return ((size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_SLAB) * 2 + (size_t)part * BL_PART16 +
+         (size_t)(((k % BL_KB) / 8) * BL_BH + (n % BL_BH)) * 8 + (k & 7);
 }
 // fp32 -> bf16 bits, round to nearest even (finite inputs)
 __host__ __device__ inline unsigned short bf16_rne_bits(float x) {
@@ -231,6 +224,9 @@ __host__ __device__ inline float bf16_bits_to_float(unsigned short h) {
   c.u = (uint32_t)h << 16;
   return c.f;
 }
+// fp32 <-> fp16 bits, round to nearest even (subnormals included)
+__host__ __device__ inline unsigned short f16_rne_bits(float x) { return __half_as_ushort(__float2half_rn(x)); }
+__host__ __device__ inline float f16_bits_to_float(unsigned short h) { return __half2float(__ushort_as_half(h)); }
 int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
                          cudaStream_t st);
 // verts and kpv are each nullable (kpv: compact keypoint-vertex rows, see smplb_model)

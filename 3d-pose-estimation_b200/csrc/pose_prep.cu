@@ -55,11 +55,11 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
     for (int i = 0; i < KPAD / 32; ++i) {
       const int k = lane + 32 * i;
       const float v = x[k];
-      const float hi = tf32_rna(v);
       unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg);
-      p.Ximg[ximg_hi_off(b, k)] = hi;
-      x16[ximg_b16_off(b, k, 0)] = bf16_rne_bits(v - hi);
-      x16[ximg_b16_off(b, k, 1)] = bf16_rne_bits(v);
+      const unsigned short h = f16_rne_bits(v);
+      x16[ximg16_off(b, k, 0)] = h;
+      x16[ximg16_off(b, k, 1)] = bf16_rne_bits(v - f16_bits_to_float(h));
+      x16[ximg16_off(b, k, 2)] = bf16_rne_bits(v);
     }
   }
 

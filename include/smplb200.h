@@ -50,7 +50,7 @@ enum {
 /* flags for smplb_forward / smplb_workspace_bytes */
 enum {
   SMPLB_F_BLEND_SIMT = 1 << 0,   /* blend-shape contraction on CUDA cores (fp32 FFMA) instead of
-                                    the tcgen05 3xTF32 kernel — verification / bring-up path   */
+                                    the tcgen05 split-operand kernel — verification / bring-up path   */
   SMPLB_F_KEEP_VPOSED = 1 << 1,  /* keep v_posed in the workspace for smplb_backward           */
   SMPLB_F_NO_SKIN = 1 << 2,      /* get_skin=False and no keypoints wanted: joints-only path   */
   SMPLB_F_SKIN_SIMT = 1 << 3,    /* skinning on CUDA cores with the compressed <=4-nonzero weights instead
