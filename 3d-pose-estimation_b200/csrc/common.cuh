@@ -75,7 +75,7 @@ struct smplb_model {
   uint32_t* skin_idx;     // [NV] 4 x u8 joint ids
   float4* skin_w;         // [NV]
   int has_compressed;
-  float* Wimg;            // [SK_NVT][SK_WTILE] TF32 hi/lo operand image of the dense LBS weights
+  float* Wimg;            // [SK_NVT][SK_WTILE] f16/bf16 operand image of the dense LBS weights (wimg16_off)
   // backward tables
   int* ent_ptr;           // [SK_NVT][NJ+1] (vertex, weight) pairs of every (vertex tile, joint): skin_bwd.cu
   float2* ent;            // [nnz] {weight, vertex index inside the tile as int bits}
@@ -124,7 +124,7 @@ struct PrepParams {
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
-  float* Aimg;    // [ceil(B/20)][SK_AGRP] TF32 hi/lo operand image of A for the skinning GEMM, nullable
+  float* Aimg;    // [ceil(B/20)][SK_AGRP] f16/bf16 operand image of A for the skinning GEMM (aimg16_off), nullable
   const float* cam_pos;
   const float* cam_rot;
   const float* focal;
@@ -164,16 +164,23 @@ __host__ __device__ inline int vp_col(int v, int c) { return (v / SK_VT) * (3 * 
 // ---- operand images of the skinning GEMM (skin_tc.cu): T[v, (s,e)] = sum_j W[v,j] A[s][j][e] -------
 #define SK_S 16                         // samples per MMA group: N = 12 * 16 = 192
 #define SK_N (12 * SK_S)
-#define SK_KCH (NJ / 4)                 // 6 K-chunks (24 joints)
-#define SK_WTILE (2 * SK_KCH * SK_VT * 4)   // floats per W tile image  [hi|lo][chunk][128 rows][4]  (6144)
-#define SK_AGRP (2 * SK_KCH * SK_N * 4)     // floats per A group image [hi|lo][chunk][192 rows][4]  (9216)
-// element (sample b, joint j, component e = 3x4 row-major) of the A operand image
-__host__ __device__ inline size_t aimg_off(int b, int j, int e, int hl) {
-  return (size_t)(b / SK_S) * SK_AGRP + (size_t)(((hl * SK_KCH + j / 4) * SK_N + (b % SK_S) * 12 + e) * 4 + (j & 3));
+#define SK_KPAD 32                      // joints padded to two K = 16 steps (pad columns are zero in both images)
+#define SK_KCH (SK_KPAD / 8)            // 4 K-chunks of 8 sixteen-bit elements
+#define SK_WPART (SK_KCH * SK_VT * 8)   // 16-bit elements per part of a W tile image (4096 = 8 KB)
+#define SK_APART (SK_KCH * SK_N * 8)    // 16-bit elements per part of an A group image (6144 = 12 KB)
+#define SK_WTILE (3 * SK_WPART / 2)     // floats per W tile image  [part][chunk][128 rows][8 x 16 bit]  (6144)
+#define SK_AGRP (3 * SK_APART / 2)      // floats per A group image [part][chunk][192 rows][8 x 16 bit]  (9216)
+// Both operands of the skinning GEMM T = W.A use the 16-bit split of the blend GEMM (see ximg16_off):
+//     W.A ~= f16(W).f16(A) + bf16(W - f16(W)).bf16(f16(A)) + bf16(W).bf16(A - f16(A))
+// parts: W [f16(W) | bf16(Wl) | bf16(W)],  A [f16(A) | bf16(f16(A)) | bf16(Al)].
+// 16-bit-element offset of component e (3x4 row-major) of joint j of sample b in the A operand image
+__host__ __device__ inline size_t aimg16_off(int b, int j, int e, int part) {
+  return (size_t)(b / SK_S) * (SK_AGRP * 2) + (size_t)part * SK_APART +
+         (size_t)(((j / 8) * SK_N + (b % SK_S) * 12 + e) * 8 + (j & 7));
 }
-// element (vertex v, joint j) of the W operand image
-__host__ __device__ inline size_t wimg_off(int v, int j, int hl) {
-  return (size_t)(v / SK_VT) * SK_WTILE + (size_t)(((hl * SK_KCH + j / 4) * SK_VT + (v % SK_VT)) * 4 + (j & 3));
+// 16-bit-element offset of (vertex v, joint j) in the W operand image
+__host__ __device__ inline size_t wimg16_off(int v, int j, int part) {
+  return (size_t)(v / SK_VT) * (SK_WTILE * 2) + (size_t)part * SK_WPART + (size_t)(((j / 8) * SK_VT + (v % SK_VT)) * 8 + (j & 7));
 }
 
 // ---- operand images of the transposed blend GEMM (blend_bwd.cu): g_X[b,k] = sum_n g_vposed[b,n] D[k,n] ----

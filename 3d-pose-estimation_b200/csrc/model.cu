@@ -77,13 +77,15 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   std::vector<uint32_t> sidx(NV);
   std::vector<float4> sw(NV);
   int has_compressed = 1;
-  std::vector<float> Wimg((size_t)SK_NVT * SK_WTILE, 0.f);
+  std::vector<float> Wimg((size_t)SK_NVT * SK_WTILE, 0.f);   // zero: joints 24..31 of the padded K stay 0
+  unsigned short* w16 = reinterpret_cast<unsigned short*>(Wimg.data());
   for (int v = 0; v < NV; ++v)
     for (int j = 0; j < NJ; ++j) {
       const float x = weights[(size_t)v * NJ + j];
-      const float hi = tf32_rna_host(x);
-      Wimg[wimg_off(v, j, 0)] = hi;
-      Wimg[wimg_off(v, j, 1)] = tf32_rna_host(x - hi);
+      const unsigned short h = f16_rne_bits(x);
+      w16[wimg16_off(v, j, 0)] = h;
+      w16[wimg16_off(v, j, 1)] = bf16_rne_bits(x - f16_bits_to_float(h));
+      w16[wimg16_off(v, j, 2)] = bf16_rne_bits(x);
     }
   for (int v = 0; v < NV; ++v) {
     int n = 0;

@@ -93,6 +93,13 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
     }
   }
 
+  if (!act && p.Aimg) {
+    // joints 24..31 of the padded K: the W columns are zero, these must be finite -> zero (workspace is not cleared).
+    // Per (part, component e) the 8 pad joints are one 16-byte unit: 36 units per sample, spread over lanes 24..31.
+    unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg);
+    for (int u = lane - NJ; u < 36; u += 32 - NJ)
+      *reinterpret_cast<uint4*>(a16 + aimg16_off(b, NJ, u % 12, u / 12)) = make_uint4(0u, 0u, 0u, 0u);
+  }
   if (act) {
     if (p.joints) {
       float* o = p.joints + ((size_t)b * NJ + j) * 3;
@@ -113,16 +120,19 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       }
     }
     if (p.Aimg) {
-      // skinning-GEMM B operand: component e of joint j of sample b, TF32 hi/lo split (skin_tc.cu)
+      // skinning-GEMM B operand: component e of joint j of sample b in the 16-bit split format (common.cuh)
+      unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg);
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
         const float tr = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
         const float row[4] = {GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr};
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          const float hi = tf32_rna(row[c]);
-          p.Aimg[aimg_off(b, j, r * 4 + c, 0)] = hi;
-          p.Aimg[aimg_off(b, j, r * 4 + c, 1)] = tf32_rna(row[c] - hi);
+          const unsigned short h = f16_rne_bits(row[c]);
+          const float hf = f16_bits_to_float(h);
+          a16[aimg16_off(b, j, r * 4 + c, 0)] = h;
+          a16[aimg16_off(b, j, r * 4 + c, 1)] = bf16_rne_bits(hf);
+          a16[aimg16_off(b, j, r * 4 + c, 2)] = bf16_rne_bits(row[c] - hf);
         }
       }
     }

@@ -6,8 +6,10 @@
 //
 // The weight blend is the reference's own matmul W[6890,24] x A[24,12]; doing it per thread from shared
 // memory costs 192 B of smem gather per vertex-sample and was 4x off the HBM roofline (profiles/r01), so
-// it runs on the tensor cores instead, in 3xTF32 (fp32-faithful):
-//   MMA: D[128 vertices, 192 = 16 samples x 12] += W_tile[128, 24] . A_group[192, 24]^T   (9 x M128 N192 K8)
+// it runs on the tensor cores instead, fp32-faithful from 16-bit split operands like the blend GEMM (common.cuh:
+// f16 main product + two bf16 correction products; 3xTF32 = 9 K8 MMAs before, and the tensor work matters even in
+// this HBM-bound kernel because the whole step runs at the board's power cap):
+//   MMA: D[128 vertices, 192 = 16 samples x 12] += W_tile[128, 32] . A_group[192, 32]^T   (6 x M128 N192 K16, K padded)
 //   accumulator in TMEM: lane = vertex, 12 columns per sample = the 3x4 blended transform of that vertex.
 // CTA = one vertex tile (W tile resident in smem) x a chunk of sample groups, persistent over units:
 //   warp 0    producer : bulk copies (TMA engine): A group image (2-stage ring) + the 16 v_posed tile rows of
@@ -30,8 +32,8 @@ constexpr uint32_t SKT_VP_ROW_BYTES = 3 * SK_VT * 4;   // 1536
 constexpr int SKT_OUT_PITCH = 3 * SK_VT + 2;
 
 struct SktSmem {
-  float w[SK_WTILE];                          // 24 576 B  W tile image (hi|lo)
-  float a[SKT_ASTAGES][SK_AGRP];              // 36 864 B  per stage: A group image (hi|lo)
+  float w[SK_WTILE];                          // 24 576 B  W tile image (3 parts)
+  float a[SKT_ASTAGES][SK_AGRP];              // 36 864 B  per stage: A group image (3 parts)
   float vp[SKT_VSTAGES][SK_S][3 * SK_VT];     // 24 576 B  per stage: v_posed tile rows of the group
   float out[SK_S][SKT_OUT_PITCH];             // 24 704 B  verts staging (AoS); pitch 386: the keypoint-vertex
                                               //           copy reads 16 samples x 2 slots per warp conflict-free
@@ -108,9 +110,10 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(2, SK_VT, SK_N);
+      constexpr uint32_t idesc_h = umma_idesc(0, SK_VT, SK_N);   // kind::f16, f16 operands
+      constexpr uint32_t idesc_b = umma_idesc(1, SK_VT, SK_N);   // kind::f16, bf16 operands
       constexpr uint32_t W_LBO = SK_VT * 16, A_LBO = SK_N * 16, SBO = 128;
-      constexpr uint32_t W_HL = SK_KCH * W_LBO, A_HL = SK_KCH * A_LBO;
+      constexpr uint32_t W_PART = SK_WPART * 2, A_PART = SK_APART * 2;   // bytes per operand part
       const uint32_t wb = smem_u32(sm.w);
       uint32_t it = 0, ul = 0;
       for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++ul) {
@@ -125,14 +128,13 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           const uint32_t ab = smem_u32(sm.a[sa]);
           const uint32_t dcol = tmem + (uint32_t)ac * SK_N;
 #pragma unroll
-          for (int ks = 0; ks < NJ / 8; ++ks) {
-            const uint64_t wh = umma_desc_kmajor_noswz(wb + ks * 2 * W_LBO, W_LBO, SBO);
-            const uint64_t wl = umma_desc_kmajor_noswz(wb + W_HL + ks * 2 * W_LBO, W_LBO, SBO);
-            const uint64_t ah = umma_desc_kmajor_noswz(ab + ks * 2 * A_LBO, A_LBO, SBO);
-            const uint64_t al = umma_desc_kmajor_noswz(ab + A_HL + ks * 2 * A_LBO, A_LBO, SBO);
-            umma_tf32_ss(dcol, wh, ah, idesc, ks != 0);
-            umma_tf32_ss(dcol, wl, ah, idesc, 1);
-            umma_tf32_ss(dcol, wh, al, idesc, 1);
+          for (int ks = 0; ks < SK_KPAD / 16; ++ks) {   // f16(W).f16(A) + bf16(Wl).bf16(Ah) + bf16(W).bf16(Al)
+#pragma unroll
+            for (int pt = 0; pt < 3; ++pt) {
+              const uint64_t wd = umma_desc_kmajor_noswz(wb + pt * W_PART + ks * 2 * W_LBO, W_LBO, SBO);
+              const uint64_t ad = umma_desc_kmajor_noswz(ab + pt * A_PART + ks * 2 * A_LBO, A_LBO, SBO);
+              umma_f16_ss(dcol, wd, ad, pt == 0 ? idesc_h : idesc_b, (ks | pt) != 0);
+            }
           }
           umma_commit(&sm.aempty[sa]);
           umma_commit(&sm.acc_full[ac]);

@@ -54,7 +54,7 @@ enum {
   SMPLB_F_KEEP_VPOSED = 1 << 1,  /* keep v_posed in the workspace for smplb_backward           */
   SMPLB_F_NO_SKIN = 1 << 2,      /* get_skin=False and no keypoints wanted: joints-only path   */
   SMPLB_F_SKIN_SIMT = 1 << 3,    /* skinning on CUDA cores with the compressed <=4-nonzero weights instead
-                                    of the tcgen05 3xTF32 weight blend — verification path       */
+                                    of the tcgen05 split-operand weight blend — verification path       */
   SMPLB_F_SCRATCH_VERTS = 1 << 4 /* SIMT skinning path only: keypoints wanted but no verts buffer given, the workspace holds verts (the tensor-core path needs no verts for keypoints) */
 };
 
