@@ -6,6 +6,8 @@
 
 #include <vector>
 
+#include <cmath>
+
 #include "common.cuh"
 
 namespace smplb {
@@ -65,6 +67,18 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
     return fail(SMPLB_E_INVALID_ARG, "smplb_model_create: null argument");
   if (NK < 1 || NK > NKMAX) return fail(SMPLB_E_BAD_SHAPE, "smplb_model_create: NK out of range");
   *out = nullptr;
+  // The tensor-core kernels split their operands into an fp16 main part + bf16 residuals (common.cuh): model
+  // constants must be finite and inside the fp16 range (SMPL's are metres and unit weights).
+  {
+    auto in_range = [](const float* p, size_t n) {
+      for (size_t i = 0; i < n; ++i)
+        if (!(std::fabs(p[i]) <= 65504.0f)) return false;   // also rejects NaN
+      return true;
+    };
+    if (!in_range(shapedirs, (size_t)NB * NV3) || !in_range(posedirs, (size_t)NP * NV3) ||
+        !in_range(weights, (size_t)NV * NJ))
+      return fail(SMPLB_E_UNSUPPORTED, "smplb_model_create: shapedirs / posedirs / weights must be finite and |x| <= 65504");
+  }
 
   // ---- kinematic tree (kintree_table[0]; parent[i] < i as in batch_lbs.py:122-127) ----
   Tree tree;

@@ -47,3 +47,24 @@ def test_argument_validation_without_gpu():
     n2 = L.smplb_workspace_bytes(None, 2048, 0)
     assert n1 >= 1024 * 20736 * 4 and n2 > n1
     assert L.smplb_workspace_bytes(None, 1024, _lib.F_NO_SKIN) < 1024 * 4096
+
+
+def test_model_outside_fp16_range_is_rejected_before_any_cuda_call():
+    """The tensor-core kernels split operands into an fp16 main part + bf16 residuals (csrc/common.cuh), so
+    smplb_model_create refuses model constants that are not finite or exceed the fp16 range."""
+    import numpy as np
+    L = _lib.lib()
+    f = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+    vt = np.zeros(6890 * 3, np.float32)
+    sd = np.zeros(10 * 20670, np.float32)
+    pd = np.zeros(207 * 20670, np.float32)
+    jr = np.zeros(6890 * 24, np.float32)
+    w = np.zeros(6890 * 24, np.float32)
+    kr = np.zeros(6890 * 19, np.float32)
+    par = np.array([-1, 0, 0, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 9, 9, 12, 13, 14, 16, 17, 18, 19, 20, 21], np.int32)
+    for bad in (1e5, np.nan, -np.inf):
+        pd[12345] = bad
+        h = C.c_void_p()
+        rc = L.smplb_model_create(C.byref(h), 0, f(vt), f(sd), f(pd), f(jr), f(w), f(kr), 19,
+                                  par.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert rc == _lib.E_UNSUPPORTED and b'65504' in L.smplb_last_error()
