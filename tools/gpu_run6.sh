@@ -1,5 +1,7 @@
 #!/bin/bash
-# full GPU suite on the default path, forward parity with the L2-chunked schedule, then a chunk-size scan of the bench
+# full GPU suite on the default path, forward parity with the L2-chunked schedule, then a chunk-size scan of the bench.
+# RECORD ONLY: the env-switched chunked schedule (SMPLB_FWD_CHUNK / SMPLB_FWD_PINGPONG in smplb_forward) was measured
+# with this script, lost (profiles/r01_blend_v4_ncu_summary.md) and was removed again; the variables are no-ops now.
 set -u
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -8 > gpurun_out/tests_all.log
