@@ -1,22 +1,25 @@
 // K2 blend-shape GEMM on the 5th-generation tensor cores (batch_smpl.py:91-95, :113-115):
 //     v_posed[B, 20670] = [beta | pose_feature][B, 217] . [shapedirs; posedirs][217, 20670] + v_template
 // fp32-faithful on the tensor cores from 16-bit operands (operand images and error analysis: common.cuh):
-//     acc += f16(X).f16(D) + bf16(X - f16(X)).bf16(f16(D)) + bf16(X).bf16(D - f16(D))
+//     acc += f16(X).f16(D) + f16(X - f16(X)).f16(D) + bf16(X).bf16(D - f16(D))
 // three kind::f16 MMAs (K = 16) per 16-element k-block, fp32 accumulation in TMEM.  History of this kernel at
 // B = 65536: 3xTF32, 6 MMA slots and 8 B per element: 2.50 ms (tensor pipe 83 % busy);  TF32 main product + two
 // bf16 corrections, 4 slots, 8 B: 2.41 ms, bound by the EPILOGUE (an L2 round trip for v_template in every
 // 32-column block), 2.08 ms with that load hoisted above the accumulator wait, then at the ~43 B/clk/SM the L2
 // delivers (ncu: 19.1 GB of operands in 2.9 M cycles);  keeping the TF32 part of X resident in smem cut the
 // operand stream by 25 % but left room for only 4 x 24 KB stages and became latency-bound (2.28 ms, rejected);
-// fp16 main product (same 11 significant bits as TF32): 3 slots, 6 B per element, 8 x 24 KB stages.
+// fp16 main product (same 11 significant bits as TF32): 3 slots, 6 B per element, 8 x 24 KB stages: 1.67 ms;
+// the ring depth, not the L2 bandwidth, is what that version waited on (ring bytes / consumption rate = 3000
+// cycles of cover; the X-stationary variants traded ring for stream one for one), so the second product now
+// reuses the f16(D) part (f16(Xl) instead of bf16(Xl).bf16(f16 D)): D slabs 12 -> 8 KB, 10 x 20 KB stages.
 //
 // v2 organisation: CTA PAIRS (cluster of 2 = one TPC, tcgen05 cta_group::2), persistent over 256 x 256
 // output tiles.  v1 (one CTA per 128 x 256 tile, 2 x 96 KB stages) pulled 688 KB of operands from L2 per
 // tile = 64 B/clk/SM at the tensor-pipe rate, more than the L2 delivers (~43 B/clk/SM): tensor pipe 50 %
-// busy.  A pair shares the D tile (each CTA stages one 128-column half), so a CTA reads 344 KB per
-// 128 x 256 outputs, and the smaller stages (24 KB) make an 8-deep ring.
+// busy.  A pair shares the D tile (each CTA stages one 128-column half), so a CTA reads 287 KB per
+// 128 x 256 outputs, and the smaller stages (20 KB) make a 10-deep ring.
 //   warp 0    producer : per k-block one 1-D bulk copy (TMA engine) of its 128 X rows and one of its D half
-//                        into an 8-stage smem ring; the operands sit in global memory as ready-made smem
+//                        into a 10-stage smem ring; the operands sit in global memory as ready-made smem
 //                        images (common.cuh)
 //   warp 1    leader CTA: one thread issues tcgen05.mma.cta_group::2.kind::f16 (M=256, N=256, K=16) x 3
 //                        products x 14 k-blocks per tile into one of two 256-column TMEM accumulators (each
@@ -32,9 +35,9 @@ namespace smplb {
 
 using namespace tc;
 
-constexpr int TC_STAGES = 8;
+constexpr int TC_STAGES = 10;
 constexpr int TC_X_STAGE_FLOATS = BL_SLAB;   // one X slab: 3 parts x 4 KB
-constexpr int TC_D_STAGE_FLOATS = BL_SLAB;   // one D half slab
+constexpr int TC_D_STAGE_FLOATS = BL_DSLAB;  // one D half slab: 2 parts x 4 KB
 constexpr uint32_t TC_STAGE_BYTES = (TC_X_STAGE_FLOATS + TC_D_STAGE_FLOATS) * 4;
 constexpr int TC_THREADS = 192;
 constexpr int TC_TMEM_COLS = 512;
@@ -161,8 +164,8 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
           const uint64_t xd = dtempl + (uint64_t)(xb0 + s * (TC_X_STAGE_FLOATS * 4 / 16));
           const uint64_t dd = dtempl + (uint64_t)(db0 + s * (TC_D_STAGE_FLOATS * 4 / 16));
           umma_f16_ss_pair(dcol, xd, dd, idesc_h, kb != 0, issue);                                  // f16(X).f16(D)
-          umma_f16_ss_pair(dcol, xd + (uint64_t)PART, dd + (uint64_t)PART, idesc_b, 1, issue);          // bf16(Xl).bf16(Dh)
-          umma_f16_ss_pair(dcol, xd + (uint64_t)(2 * PART), dd + (uint64_t)(2 * PART), idesc_b, 1, issue);   // bf16(X).bf16(Dl)
+          umma_f16_ss_pair(dcol, xd + (uint64_t)PART, dd, idesc_h, 1, issue);                       // f16(Xl).f16(D)
+          umma_f16_ss_pair(dcol, xd + (uint64_t)(2 * PART), dd + (uint64_t)PART, idesc_b, 1, issue);   // bf16(X).bf16(Dl)
           umma_commit_pair(empty0 + s * 8, 3, issue);                                        // stage free in both CTAs
           if (kb == BL_NKB - 1) umma_commit_pair(smem_u32(&sm.acc_full[a]), 3, issue);       // accumulator complete
           if (++s == TC_STAGES) { s = 0; ph ^= 1; }

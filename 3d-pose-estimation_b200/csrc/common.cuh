@@ -32,7 +32,8 @@
 #define BL_NT (VPP / BL_BN)     // 81 N tiles
 #define BL_SLAB (3 * BL_KB * BL_BM / 2)   // floats per (k-block, 128 rows) operand slab: 3 sixteen-bit parts = 12 KB
 #define BL_XTILE (BL_NKB * BL_SLAB)       // floats per X m-tile image (43008)
-#define BL_DTILE (BL_NKB * 2 * BL_SLAB)   // floats per D n-tile image (86016): [k-block][column half] slabs
+#define BL_DSLAB (2 * BL_KB * BL_BH / 2)  // floats per (k-block, 128 columns) D slab: 2 sixteen-bit parts = 8 KB
+#define BL_DTILE (BL_NKB * 2 * BL_DSLAB)  // floats per D n-tile image (57344): [k-block][column half] slabs
 
 namespace smplb {
 
@@ -199,14 +200,16 @@ __host__ __device__ inline size_t dtimg_off(int k, int n, int hl) {
 }
 
 // Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated fp32-faithfully from 16-bit operands:
-//     X.D ~= f16(X).f16(D)  +  bf16(Xl).bf16(f16(D))  +  bf16(X).bf16(Dl),    Xl = X - f16(X), Dl = D - f16(D)
+//     X.D ~= f16(X).f16(D)  +  f16(Xl).f16(D)  +  bf16(X).bf16(Dl),    Xl = X - f16(X), Dl = D - f16(D)
 // (kind::f16 MMAs, K = 16 each, fp32 accumulation).  fp16 carries the same 11 significant bits as TF32 at twice
-// the tensor rate and half the bytes; the two correction products are 2^-11 of the main one, so bf16's 8 bits
-// (and its fp32 exponent range: the residuals fall below the fp16 normal range) are enough for them.
-// Error ~2^-20 of the blend offsets (tests/test_blend_split.py).  3 MMA slots and 6 bytes per element against
-// 6 slots and 8 bytes for 3xTF32 (Xh.Dh + Xl.Dh + Xh.Dl, the first version of this round).
-// Per 16-element k-block a 128-row operand slab is 12 KB = three 4 KB parts, each 2 K-chunks x 128 rows x 16 B:
-//     part 0  f16(X)  | f16(D)         part 1  bf16(Xl) | bf16(f16(D))         part 2  bf16(X) | bf16(Dl)
+// the tensor rate and half the bytes; the two correction products are 2^-11 of the main one.  Xl (inputs are O(1))
+// stays an fp16 number: normal for |X| >= 0.12, below that its absolute error is <= 2^-25, which is what matters
+// against the vertex scale; so the second product reuses the f16(D) part.  Dl (~5e-6 for SMPL's bases) is below the
+// fp16 normal range and is carried in bf16 (8 bits, fp32 exponent range), with bf16(X) as its partner.
+// Error ~2^-20 of the blend offsets (tests/test_blend_split.py).  3 MMA slots, 6 B per X element and 4 B per D element
+// against 6 slots and 8 B for 3xTF32 (Xh.Dh + Xl.Dh + Xh.Dl, the first version of this round).
+// Per 16-element k-block a 128-row slab is made of 4 KB parts, each 2 K-chunks x 128 rows x 16 B:
+//     X (12 KB): f16(X) | f16(Xl) | bf16(X)          D (8 KB): f16(D) | bf16(Dl)
 #define BL_PART16 (BL_KB * BL_BM)   // 16-bit elements per part (2048)
 // 16-bit-element offset of part `part` of element (row b, k) of the X operand image
 __host__ __device__ inline size_t ximg16_off(int b, int k, int part) {
@@ -216,7 +219,7 @@ __host__ __device__ inline size_t ximg16_off(int b, int k, int part) {
 // the same for element (column n, k) of the D operand image: slabs ordered [n-tile][k-block][column half]
 __host__ __device__ inline size_t dimg16_off(int n, int k, int part) {
   const int half = (n % BL_BN) / BL_BH;
-  return ((size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_SLAB) * 2 + (size_t)part * BL_PART16 +
+  return ((size_t)(n / BL_BN) * BL_DTILE + (size_t)((k / BL_KB) * 2 + half) * BL_DSLAB) * 2 + (size_t)part * BL_PART16 +
          (size_t)(((k % BL_KB) / 8) * BL_BH + (n % BL_BH)) * 8 + (k & 7);
 }
 // fp32 -> bf16 bits, round to nearest even (finite inputs)

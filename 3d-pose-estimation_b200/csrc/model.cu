@@ -138,8 +138,7 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
       const unsigned short h = f16_rne_bits(x);
       const float hi = f16_bits_to_float(h);
       d16[dimg16_off(n, k, 0)] = h;
-      d16[dimg16_off(n, k, 1)] = bf16_rne_bits(hi);
-      d16[dimg16_off(n, k, 2)] = bf16_rne_bits(x - hi);
+      d16[dimg16_off(n, k, 1)] = bf16_rne_bits(x - hi);
     }
   std::vector<float> vt(VPP, 0.f);
   for (int v = 0; v < NV; ++v)

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg);
       const unsigned short h = f16_rne_bits(v);
       x16[ximg16_off(b, k, 0)] = h;
-      x16[ximg16_off(b, k, 1)] = bf16_rne_bits(v - f16_bits_to_float(h));
+      x16[ximg16_off(b, k, 1)] = f16_rne_bits(v - f16_bits_to_float(h));
       x16[ximg16_off(b, k, 2)] = bf16_rne_bits(v);
     }
   }
