@@ -169,11 +169,13 @@ __host__ __device__ inline int vp_col(int v, int c) { return (v / SK_VT) * (3 * 
 #define SK_KCH (SK_KPAD / 8)            // 4 K-chunks of 8 sixteen-bit elements
 #define SK_WPART (SK_KCH * SK_VT * 8)   // 16-bit elements per part of a W tile image (4096 = 8 KB)
 #define SK_APART (SK_KCH * SK_N * 8)    // 16-bit elements per part of an A group image (6144 = 12 KB)
-#define SK_WTILE (3 * SK_WPART / 2)     // floats per W tile image  [part][chunk][128 rows][8 x 16 bit]  (6144)
-#define SK_AGRP (3 * SK_APART / 2)      // floats per A group image [part][chunk][192 rows][8 x 16 bit]  (9216)
-// Both operands of the skinning GEMM T = W.A use the 16-bit split of the blend GEMM (see ximg16_off):
-//     W.A ~= f16(W).f16(A) + bf16(W - f16(W)).bf16(f16(A)) + bf16(W).bf16(A - f16(A))
-// parts: W [f16(W) | bf16(Wl) | bf16(W)],  A [f16(A) | bf16(f16(A)) | bf16(Al)].
+#define SK_WTILE (2 * SK_WPART / 2)     // floats per W tile image  [part 2][chunk][128 rows][8 x 16 bit]  (4096)
+#define SK_AGRP (2 * SK_APART / 2)      // floats per A group image [part 2][chunk][192 rows][8 x 16 bit]  (6144)
+// Both operands of the skinning GEMM T = W.A are split into an fp16 main part and the fp16 residual:
+//     W.A ~= f16(W).f16(A) + f16(Wl).f16(A) + f16(W).f16(Al),     Wl = W - f16(W), Al = A - f16(A)
+// (weights in [0,1], rotations in [-1,1], translations in metres: a residual is a normal fp16 number when the value
+// is >= 0.25 and otherwise has an absolute error <= 2^-25, which is what counts against the vertex scale).
+// parts: W [f16(W) | f16(Wl)],  A [f16(A) | f16(Al)].
 // 16-bit-element offset of component e (3x4 row-major) of joint j of sample b in the A operand image
 __host__ __device__ inline size_t aimg16_off(int b, int j, int e, int part) {
   return (size_t)(b / SK_S) * (SK_AGRP * 2) + (size_t)part * SK_APART +

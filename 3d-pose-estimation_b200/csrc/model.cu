@@ -98,8 +98,7 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
       const float x = weights[(size_t)v * NJ + j];
       const unsigned short h = f16_rne_bits(x);
       w16[wimg16_off(v, j, 0)] = h;
-      w16[wimg16_off(v, j, 1)] = bf16_rne_bits(x - f16_bits_to_float(h));
-      w16[wimg16_off(v, j, 2)] = bf16_rne_bits(x);
+      w16[wimg16_off(v, j, 1)] = f16_rne_bits(x - f16_bits_to_float(h));
     }
   for (int v = 0; v < NV; ++v) {
     int n = 0;

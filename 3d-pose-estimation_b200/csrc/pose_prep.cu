@@ -95,9 +95,9 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
 
   if (!act && p.Aimg) {
     // joints 24..31 of the padded K: the W columns are zero, these must be finite -> zero (workspace is not cleared).
-    // Per (part, component e) the 8 pad joints are one 16-byte unit: 36 units per sample, spread over lanes 24..31.
+    // Per (part, component e) the 8 pad joints are one 16-byte unit: 24 units per sample, spread over lanes 24..31.
     unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg);
-    for (int u = lane - NJ; u < 36; u += 32 - NJ)
+    for (int u = lane - NJ; u < 24; u += 32 - NJ)
       *reinterpret_cast<uint4*>(a16 + aimg16_off(b, NJ, u % 12, u / 12)) = make_uint4(0u, 0u, 0u, 0u);
   }
   if (act) {
@@ -131,8 +131,7 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
           const unsigned short h = f16_rne_bits(row[c]);
           const float hf = f16_bits_to_float(h);
           a16[aimg16_off(b, j, r * 4 + c, 0)] = h;
-          a16[aimg16_off(b, j, r * 4 + c, 1)] = bf16_rne_bits(hf);
-          a16[aimg16_off(b, j, r * 4 + c, 2)] = bf16_rne_bits(row[c] - hf);
+          a16[aimg16_off(b, j, r * 4 + c, 1)] = f16_rne_bits(row[c] - hf);
         }
       }
     }

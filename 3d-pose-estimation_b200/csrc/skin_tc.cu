@@ -7,13 +7,13 @@
 // The weight blend is the reference's own matmul W[6890,24] x A[24,12]; doing it per thread from shared
 // memory costs 192 B of smem gather per vertex-sample and was 4x off the HBM roofline (profiles/r01), so
 // it runs on the tensor cores instead, fp32-faithful from 16-bit split operands like the blend GEMM (common.cuh:
-// f16 main product + two bf16 correction products; 3xTF32 = 9 K8 MMAs before, and the tensor work matters even in
+// f16 main parts + f16 residuals, three products; 3xTF32 = 9 K8 MMAs before, and the tensor work matters even in
 // this HBM-bound kernel because the whole step runs at the board's power cap):
 //   MMA: D[128 vertices, 192 = 16 samples x 12] += W_tile[128, 32] . A_group[192, 32]^T   (6 x M128 N192 K16, K padded)
 //   accumulator in TMEM: lane = vertex, 12 columns per sample = the 3x4 blended transform of that vertex.
 // CTA = one vertex tile (W tile resident in smem) x a chunk of sample groups, persistent over units:
 //   warp 0    producer : bulk copies (TMA engine): A group image (2-stage ring) + the 16 v_posed tile rows of
-//                        the group (4-stage ring = the HBM prefetch depth)
+//                        the group (5-stage ring = the HBM prefetch depth)
 //   warp 1    MMA      : tcgen05.mma.kind::tf32 into one of two 192-column TMEM accumulators
 //   warps 2-9 epilogue : tcgen05.ld T, apply to v_posed (thread = vertex), transpose through smem so the
 //                        verts rows are written as contiguous 8-byte-aligned runs (streaming stores)
@@ -27,13 +27,13 @@ constexpr int SKT_EPI_WARPS = 8;
 constexpr int SKT_THREADS = 64 + 32 * SKT_EPI_WARPS;   // producer warp + MMA warp + epilogue warps
 constexpr int SKT_TMEM_COLS = 512;
 constexpr int SKT_ASTAGES = 2;   // A-image ring (released by the MMA)
-constexpr int SKT_VSTAGES = 4;   // v_posed ring (released by the epilogue): HBM prefetch depth
+constexpr int SKT_VSTAGES = 5;   // v_posed ring (released by the epilogue): HBM prefetch depth
 constexpr uint32_t SKT_VP_ROW_BYTES = 3 * SK_VT * 4;   // 1536
 constexpr int SKT_OUT_PITCH = 3 * SK_VT + 2;
 
 struct SktSmem {
-  float w[SK_WTILE];                          // 24 576 B  W tile image (3 parts)
-  float a[SKT_ASTAGES][SK_AGRP];              // 36 864 B  per stage: A group image (3 parts)
+  float w[SK_WTILE];                          // 16 384 B  W tile image (2 parts)
+  float a[SKT_ASTAGES][SK_AGRP];              // 24 576 B  per stage: A group image (2 parts)
   float vp[SKT_VSTAGES][SK_S][3 * SK_VT];     // 24 576 B  per stage: v_posed tile rows of the group
   float out[SK_S][SKT_OUT_PITCH];             // 24 704 B  verts staging (AoS); pitch 386: the keypoint-vertex
                                               //           copy reads 16 samples x 2 slots per warp conflict-free
@@ -111,7 +111,6 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
     // ================= MMA issuer =================
     if (lane == 0) {
       constexpr uint32_t idesc_h = umma_idesc(0, SK_VT, SK_N);   // kind::f16, f16 operands
-      constexpr uint32_t idesc_b = umma_idesc(1, SK_VT, SK_N);   // kind::f16, bf16 operands
       constexpr uint32_t W_LBO = SK_VT * 16, A_LBO = SK_N * 16, SBO = 128;
       constexpr uint32_t W_PART = SK_WPART * 2, A_PART = SK_APART * 2;   // bytes per operand part
       const uint32_t wb = smem_u32(sm.w);
@@ -128,13 +127,14 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           const uint32_t ab = smem_u32(sm.a[sa]);
           const uint32_t dcol = tmem + (uint32_t)ac * SK_N;
 #pragma unroll
-          for (int ks = 0; ks < SK_KPAD / 16; ++ks) {   // f16(W).f16(A) + bf16(Wl).bf16(Ah) + bf16(W).bf16(Al)
-#pragma unroll
-            for (int pt = 0; pt < 3; ++pt) {
-              const uint64_t wd = umma_desc_kmajor_noswz(wb + pt * W_PART + ks * 2 * W_LBO, W_LBO, SBO);
-              const uint64_t ad = umma_desc_kmajor_noswz(ab + pt * A_PART + ks * 2 * A_LBO, A_LBO, SBO);
-              umma_f16_ss(dcol, wd, ad, pt == 0 ? idesc_h : idesc_b, (ks | pt) != 0);
-            }
+          for (int ks = 0; ks < SK_KPAD / 16; ++ks) {   // f16(W).f16(A) + f16(Wl).f16(A) + f16(W).f16(Al)
+            const uint64_t w0 = umma_desc_kmajor_noswz(wb + ks * 2 * W_LBO, W_LBO, SBO);
+            const uint64_t w1 = umma_desc_kmajor_noswz(wb + W_PART + ks * 2 * W_LBO, W_LBO, SBO);
+            const uint64_t a0 = umma_desc_kmajor_noswz(ab + ks * 2 * A_LBO, A_LBO, SBO);
+            const uint64_t a1 = umma_desc_kmajor_noswz(ab + A_PART + ks * 2 * A_LBO, A_LBO, SBO);
+            umma_f16_ss(dcol, w0, a0, idesc_h, ks != 0);
+            umma_f16_ss(dcol, w1, a0, idesc_h, 1);
+            umma_f16_ss(dcol, w0, a1, idesc_h, 1);
           }
           umma_commit(&sm.aempty[sa]);
           umma_commit(&sm.acc_full[ac]);
