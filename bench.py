@@ -678,7 +678,7 @@ def main():
                             '(BASELINE configs[3] shard size; global batch %d)' % (B, B * world),
                 'model': 'synthetic SMPL-shaped (6890 verts, 24 joints, 10 betas, <=4 LBS weights/vertex), seed 0',
                 'outputs': 'verts[B,6890,3], J_transformed[B,24,3], keypoints[B,19,3], Rs, uv, px[B,24,2]',
-                'blend_gemm': 'tcgen05 kind::f16: f16 main product + 2 bf16 correction products, fp32 accumulate (fp32-faithful, 3e-7 of the vertex scale)' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
+                'blend_gemm': 'tcgen05 kind::f16: f16 main product + f16/bf16 residual products, fp32 accumulate (fp32-faithful, 2e-7 of the vertex scale)' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
                 'sharding': 'batch shards, one rank per GPU, no forward collective',
                 'l2': 'working set %.2f GB per step exceeds the 126 MB L2 (no flush needed)' % (
                     B * (82944 + 82680) / 1e9),

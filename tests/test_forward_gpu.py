@@ -254,7 +254,7 @@ def test_forward_host_chunked_pipeline_matches_device_call(gpu_model):
 
 
 def test_blend_split_precision(gpu_model, oracle64):
-    """The blend GEMM evaluates X.D as f16(X).f16(D) + bf16(Xl).bf16(Dh) + bf16(X).bf16(Dl) (blend_tc.cu):
+    """The blend GEMM evaluates X.D as f16(X).f16(D) + f16(Xl).f16(D) + bf16(X).bf16(Dl) (blend_tc.cu):
     worst-case inputs for the split (|beta| = 3 everywhere, large joint rotations so the pose feature R - I
     reaches its range [-2, 2]) must stay 5x inside the 1e-5 budget."""
     B = 384
