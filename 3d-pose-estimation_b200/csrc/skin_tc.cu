@@ -2,7 +2,7 @@
 //     T[b,v]   = sum_j weights[v,j] * A[b,j]              (:122-127, tile(W) x A never materialised)
 //     verts[b,v] = T[b,v][:3,:3] . v_posed[b,v] + T[b,v][:3,3]   (:128-132)
 // One pass over HBM: read v_posed (82 944 B / sample, internal SoA tile layout) + the A operand image
-// (2 304 B / sample, L2 resident across the 54 vertex tiles), write verts (82 680 B / sample).
+// (1 536 B / sample, L2 resident across the 54 vertex tiles), write verts (82 680 B / sample).
 //
 // The weight blend is the reference's own matmul W[6890,24] x A[24,12]; doing it per thread from shared
 // memory costs 192 B of smem gather per vertex-sample and was 4x off the HBM roofline (profiles/r01), so
@@ -14,7 +14,7 @@
 // CTA = one vertex tile (W tile resident in smem) x a chunk of sample groups, persistent over units:
 //   warp 0    producer : bulk copies (TMA engine): A group image (2-stage ring) + the 16 v_posed tile rows of
 //                        the group (5-stage ring = the HBM prefetch depth)
-//   warp 1    MMA      : tcgen05.mma.kind::tf32 into one of two 192-column TMEM accumulators
+//   warp 1    MMA      : tcgen05.mma.kind::f16 into one of two 192-column TMEM accumulators
 //   warps 2-9 epilogue : tcgen05.ld T, apply to v_posed (thread = vertex), transpose through smem so the
 //                        verts rows are written as contiguous 8-byte-aligned runs (streaming stores)
 #include "tc_common.cuh"
