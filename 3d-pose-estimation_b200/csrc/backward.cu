@@ -226,7 +226,8 @@ __global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwd
 __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, const float* __restrict__ cpos,
                                    const float* __restrict__ cang, const float* __restrict__ foc, int tiled,
                                    const float* __restrict__ g_uv, float* __restrict__ g_pts,
-                                   float* __restrict__ g_cpos, float* __restrict__ g_cang) {
+                                   float* __restrict__ g_cpos, float* __restrict__ g_cang,
+                                   float* __restrict__ g_foc) {
   const int ncam = tiled ? N : N / P;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= ncam) return;
@@ -235,7 +236,7 @@ __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, 
   const float ax = cang[3 * c], ay = cang[3 * c + 1], az = cang[3 * c + 2];
   rodrigues_cam(ax, ay, az, Rc);
   const float cx = cpos[3 * c], cy = cpos[3 * c + 1], cz = cpos[3 * c + 2], f = foc[c];
-  float gc[3] = {0.f, 0.f, 0.f}, gRc[9];
+  float gc[3] = {0.f, 0.f, 0.f}, gRc[9], gf = 0.f;
 #pragma unroll
   for (int e = 0; e < 9; ++e) gRc[e] = 0.f;
   for (int k = 0; k < np; ++k) {
@@ -243,6 +244,7 @@ __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, 
     float q[3], u, v, gq[3];
     project_point(Rc, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cx, cy, cz, f, u, v, q);
     project_bwd_q(q, f, g_uv[2 * i], g_uv[2 * i + 1], gq);
+    gf += (g_uv[2 * i] * q[0] + g_uv[2 * i + 1] * q[1]) / q[2];   // uv = f q_xy / q_z (project.py:35-46)
     const float d[3] = {pts[3 * i] - cx, pts[3 * i + 1] - cy, pts[3 * i + 2] - cz};
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
@@ -256,6 +258,7 @@ __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, 
   if (g_cpos) {
     g_cpos[3 * c] = gc[0]; g_cpos[3 * c + 1] = gc[1]; g_cpos[3 * c + 2] = gc[2];
   }
+  if (g_foc) g_foc[c] = gf;
   if (g_cang) {
     float gr[3];
     rodrigues_cam_bwd(ax, ay, az, gRc, gr);
@@ -323,6 +326,7 @@ using namespace smplb;
 extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io* io, void* workspace,
                                   size_t workspace_bytes, int32_t flags, void* stream) {
   if (!m || !io) return fail(SMPLB_E_INVALID_ARG, "smplb_backward: null model or io");
+  if (int32_t rc = check_current_device(m->device, "smplb_backward")) return rc;
   if (io->B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_backward: negative batch");
   if (io->B == 0) return SMPLB_OK;
   if (!io->beta || !io->theta || !io->g_beta || !io->g_theta)
@@ -383,7 +387,7 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
 extern "C" int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts, const float* cams_pos,
                                           const float* cams_angles, const float* focal_lens, int32_t cam_tiled,
                                           const float* g_uv, float* g_pts, float* g_cams_pos, float* g_cams_angles,
-                                          void* stream) {
+                                          float* g_focal_lens, void* stream) {
   if (N < 0 || P < 1) return fail(SMPLB_E_BAD_SHAPE, "smplb_project_backward: N >= 0 and P >= 1 required");
   if (!cam_tiled && N % P != 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_project_backward: N must be a multiple of P");
   if (N == 0) return SMPLB_OK;
@@ -392,7 +396,7 @@ extern "C" int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts
   const int ncam = cam_tiled ? N : N / P;
   project_bwd_kernel<<<(ncam + 127) / 128, 128, 0, (cudaStream_t)stream>>>(N, P, pts, cams_pos, cams_angles,
                                                                            focal_lens, cam_tiled, g_uv, g_pts,
-                                                                           g_cams_pos, g_cams_angles);
+                                                                           g_cams_pos, g_cams_angles, g_focal_lens);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

@@ -150,19 +150,14 @@ int blend_bwd_slices(int B, int n_sm) {
 int32_t launch_blend_bwd(const smplb_model* m, int B, const float* g_img, float* g_X, int* n_slices_out,
                          cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
-  static int n_sm[64] = {};
-  const int dev = m->device & 63;
+  static KernelSetup setup;
   const size_t smem = sizeof(BbSmem);
-  if (!n_sm[dev]) {
-    int v = 0;
-    SMPLB_CUDA_CHECK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, m->device));
-    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(blend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    n_sm[dev] = v;
-  }
+  int n_sm = 0;
+  if (int32_t rc = setup.ensure(m->device, blend_bwd_kernel, smem, &n_sm)) return rc;
   const int n_mtiles = (B + BL_BM - 1) / BL_BM;
   const int n_slices = blend_bwd_slices(B, 148);   // fixed constant: the workspace size must not depend on the device
   const int n_units = n_mtiles * n_slices;
-  const int grid = n_units < n_sm[dev] ? n_units : n_sm[dev];
+  const int grid = n_units < n_sm ? n_units : n_sm;
   blend_bwd_kernel<<<grid, BB_THREADS, smem, st>>>(B, n_mtiles, n_slices, g_img, m->DTimg, g_X);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   *n_slices_out = n_slices;

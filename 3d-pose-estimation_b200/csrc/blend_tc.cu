@@ -223,22 +223,15 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
   }
 }
 
-void free_tmap_cache(smplb_model* m) { (void)m; }
-
 int32_t launch_blend_tc(const smplb_model* m, int B, const float* Ximg, float* vposed, cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
-  static int n_sm[64] = {};
-  const int dev = m->device & 63;
+  static KernelSetup setup;
   const size_t smem = sizeof(TcSmem);
-  if (!n_sm[dev]) {
-    int v = 0;
-    SMPLB_CUDA_CHECK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, m->device));
-    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(blend_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    n_sm[dev] = v;
-  }
+  int n_sm = 0;
+  if (int32_t rc = setup.ensure(m->device, blend_tc_kernel, smem, &n_sm)) return rc;
   const int n_mtiles = (B + BL_BM - 1) / BL_BM;
   const int n_tiles = ((n_mtiles + 1) / 2) * BL_NT;
-  const int n_cl = n_tiles < n_sm[dev] / 2 ? n_tiles : n_sm[dev] / 2;
+  const int n_cl = n_tiles < n_sm / 2 ? n_tiles : n_sm / 2;
   const int grid = 2 * n_cl;   // CTA pairs
   blend_tc_kernel<<<grid, TC_THREADS, smem, st>>>(B, n_mtiles, Ximg, m->Dimg, m->v_template_pad, vposed);
   SMPLB_CUDA_CHECK(cudaGetLastError());

@@ -82,6 +82,7 @@ extern "C" size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t
 static int32_t check_forward(const smplb_model* m, const smplb_forward_io* io, void* ws, size_t ws_bytes,
                              int32_t flags) {
   if (!m || !io) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: null model or io");
+  if (int32_t rc = check_current_device(m->device, "smplb_forward")) return rc;
   if (io->B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_forward: negative batch");
   if (io->B == 0) return SMPLB_OK;
   if (!io->beta || !io->theta) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: beta/theta are required");

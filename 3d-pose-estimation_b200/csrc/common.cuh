@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <mutex>
 #include <string>
 
 #include "../../include/smplb200.h"
@@ -46,6 +47,35 @@ int32_t fail(int32_t code, const std::string& msg);
     if (_e != cudaSuccess)                                                                  \
       return smplb::fail(SMPLB_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
   } while (0)
+
+// The kernels launch on the CURRENT device: every entry point that takes a model / mesh handle checks that it is the
+// handle's device (SMPLB_E_INVALID_ARG otherwise) instead of silently configuring or launching on another GPU.
+int32_t check_current_device(int device, const char* who);
+
+// One-time, thread-safe, per-device kernel setup (dynamic shared memory opt-in + SM count).  A launcher keeps one
+// `static KernelSetup` per kernel; std::call_once makes concurrent first calls from several host threads safe, and the
+// attribute is set on the device the handle lives on (the caller has verified that it is the current one).
+struct KernelSetup {
+  std::once_flag once[64];
+  int n_sm[64] = {};
+  cudaError_t err[64] = {};
+  template <class Kernel>
+  int32_t ensure(int device, Kernel kernel, size_t smem_bytes, int* n_sm_out) {
+    const int d = device & 63;
+    std::call_once(once[d], [&] {
+      int v = 0;
+      cudaError_t e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device);
+      if (e == cudaSuccess && smem_bytes > 48 * 1024)
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+      n_sm[d] = v;
+      err[d] = e;
+    });
+    if (err[d] != cudaSuccess)
+      return fail(SMPLB_E_CUDA, std::string("kernel setup: ") + cudaGetErrorString(err[d]));
+    if (n_sm_out) *n_sm_out = n_sm[d];
+    return SMPLB_OK;
+  }
+};
 
 // Kinematic tree, passed by value to the kernels (batch_smpl.py:54, batch_lbs.py:122-127).
 struct Tree {
@@ -93,8 +123,6 @@ struct smplb_model {
   int* kpc_tile_ptr;      // [SK_NVT+1] first compact slot of every vertex tile
   int* kpc_src;           // [kpv_pitch] float index 3*lv+c inside the tile's staged verts row, -1 = pad
   int* kpc_slot;          // [nnz] compact slot of the vertex of every regressor entry
-  // J_regressor CSR by joint (for d(J)/d(beta) in backward: JS is enough) — not needed
-  void* tmap_cache;       // host-side cache of TMA descriptors (blend_tc.cu)
 };
 
 #define NM_BIG_ORDER 16

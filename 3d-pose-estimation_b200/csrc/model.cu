@@ -20,6 +20,17 @@ int32_t fail(int32_t code, const std::string& msg) {
 }
 const char* last_error() { return g_err.c_str(); }
 
+int32_t check_current_device(int device, const char* who) {
+  int cur = -1;
+  cudaError_t e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return fail(SMPLB_E_CUDA, std::string(who) + ": cudaGetDevice: " + cudaGetErrorString(e));
+  if (cur != device)
+    return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": the handle lives on device " + std::to_string(device) +
+                                         " but the current device is " + std::to_string(cur) +
+                                         " (cudaSetDevice to the handle's device before the call)");
+  return SMPLB_OK;
+}
+
 template <typename T>
 static cudaError_t upload(T** dptr, const std::vector<T>& h) {
   size_t bytes = h.size() * sizeof(T);
@@ -261,10 +272,6 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   return SMPLB_OK;
 }
 
-namespace smplb {
-void free_tmap_cache(smplb_model* m);
-}
-
 extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   if (!m) return SMPLB_OK;
   int prev = 0;
@@ -287,7 +294,6 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->kpc_tile_ptr);
   cudaFree(m->kpc_src);
   cudaFree(m->kpc_slot);
-  smplb::free_tmap_cache(m);
   cudaSetDevice(prev);
   delete m;
   return SMPLB_OK;

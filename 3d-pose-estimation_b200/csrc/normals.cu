@@ -259,15 +259,11 @@ extern "C" int32_t smplb_mesh_normals(const smplb_mesh* m, int32_t B, const floa
   if (m->T <= 0 || !m->vpair) return fail(SMPLB_E_UNSUPPORTED, "smplb_mesh_normals: mesh without triangles");
   const size_t smem = (size_t)6 * m->V * sizeof(float) + (((size_t)m->V + 15) & ~(size_t)15);
   if (smem > 220 * 1024) return fail(SMPLB_E_UNSUPPORTED, "smplb_mesh_normals: more than 9000 vertices per mesh");
-  static int n_sm[64] = {};
-  const int dev = m->device & 63;
-  if (!n_sm[dev]) {
-    int v = 0;
-    SMPLB_CUDA_CHECK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, m->device));
-    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(normals_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-    n_sm[dev] = v;
-  }
-  const int grid = B < n_sm[dev] ? B : n_sm[dev];
+  if (int32_t rc = check_current_device(m->device, "smplb_mesh_normals")) return rc;
+  static KernelSetup setup;
+  int n_sm = 0;
+  if (int32_t rc = setup.ensure(m->device, normals_kernel, 220 * 1024, &n_sm)) return rc;
+  const int grid = B < n_sm ? B : n_sm;
   normals_kernel<<<grid, NM_THREADS, smem, (cudaStream_t)stream>>>(B, m->V, m->T, m->max_order, m->tri, m->vptr, m->vpair,
                                                                    m->vfan, m->big_v, m->n_big, verts, normals);
   SMPLB_CUDA_CHECK(cudaGetLastError());

@@ -408,6 +408,7 @@ extern "C" size_t smplb_rasterize_workspace_bytes(const smplb_mesh* m, int32_t B
 static int32_t raster_check(const char* who, const smplb_mesh* m, int32_t B, int32_t W, int32_t H, const void* ws,
                             size_t ws_bytes) {
   if (!m) return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": null mesh");
+  if (int32_t rc = check_current_device(m->device, who)) return rc;
   if (B < 0) return fail(SMPLB_E_BAD_SHAPE, std::string(who) + ": negative batch");
   if (W <= 0 || H <= 0) return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": image width and height must be > 0");
   if ((size_t)W * H > (1u << 30)) return fail(SMPLB_E_UNSUPPORTED, std::string(who) + ": image too large");
@@ -579,6 +580,7 @@ extern "C" int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const fl
                                         const float* light_intensities, int32_t L, const float* ambient, int32_t W,
                                         int32_t H, float* rgba, void* workspace, size_t workspace_bytes, void* stream) {
   if (!m) return fail(SMPLB_E_INVALID_ARG, "smplb_render_diffuse: null mesh");
+  if (int32_t rc = check_current_device(m->device, "smplb_render_diffuse")) return rc;
   if (B < 0 || L < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_render_diffuse: negative batch or light count");
   if (W <= 0 || H <= 0) return fail(SMPLB_E_INVALID_ARG, "smplb_render_diffuse: image width and height must be > 0");
   if (B == 0) return SMPLB_OK;

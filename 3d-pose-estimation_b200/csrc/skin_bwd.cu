@@ -140,11 +140,8 @@ int32_t launch_skin_bwd_gA(const smplb_model* m, int B, const float* g_verts, co
                            cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
   const size_t smem = sizeof(GaSmem);
-  static bool attr_done[64] = {};
-  if (!attr_done[m->device & 63]) {
-    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(skin_bwd_gA_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done[m->device & 63] = true;
-  }
+  static KernelSetup setup;
+  if (int32_t rc = setup.ensure(m->device, skin_bwd_gA_kernel, smem, nullptr)) return rc;
   skin_bwd_gA_kernel<<<(B + GA_SAMPLES - 1) / GA_SAMPLES, GA_WARPS * 32, smem, st>>>(B, g_verts, vposed, m->ent_ptr,
                                                                                      m->ent, g_A);
   SMPLB_CUDA_CHECK(cudaGetLastError());

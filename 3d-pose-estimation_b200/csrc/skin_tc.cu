@@ -336,25 +336,20 @@ template <int MODE>
 static int32_t launch_skin_tc_mode(const smplb_model* m, int B, const float* in, const float* Aimg, float* out,
                                    float* kpv, cudaStream_t st) {
   if (B <= 0) return SMPLB_OK;
-  static int n_sm[64] = {};
-  const int dev = m->device & 63;
+  static KernelSetup setup;   // one per MODE instantiation
   const size_t smem = sizeof(SktSmem);
-  if (!n_sm[dev]) {
-    int v = 0;
-    SMPLB_CUDA_CHECK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, m->device));
-    SMPLB_CUDA_CHECK(cudaFuncSetAttribute(skin_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    n_sm[dev] = v;
-  }
+  int n_sm = 0;
+  if (int32_t rc = setup.ensure(m->device, skin_tc_kernel<MODE>, smem, &n_sm)) return rc;
   const int n_groups = (B + SK_S - 1) / SK_S;
   // units = 54 vertex tiles x n_chunks sample chunks over a whole number of CTA waves
   // 7 waves when every unit still covers >= 32 sample groups (tail of the last wave 1 % instead of 3 %: 2.12 -> 2.10 ms
   // at B = 65536), else 3: every unit reloads the 24 KB W tile and refills its pipeline
-  int n_chunks = (7 * n_sm[dev]) / SK_NVT;
-  if (n_groups < 32 * n_chunks) n_chunks = (3 * n_sm[dev]) / SK_NVT;
+  int n_chunks = (7 * n_sm) / SK_NVT;
+  if (n_groups < 32 * n_chunks) n_chunks = (3 * n_sm) / SK_NVT;
   if (n_chunks < 1) n_chunks = 1;
   if (n_chunks > n_groups) n_chunks = n_groups;
   const int n_units = SK_NVT * n_chunks;
-  const int grid = n_units < n_sm[dev] ? n_units : n_sm[dev];
+  const int grid = n_units < n_sm ? n_units : n_sm;
   skin_tc_kernel<MODE><<<grid, SKT_THREADS, smem, st>>>(B, n_groups, n_chunks, in, Aimg, m->Wimg, out, kpv, m->kpv_pitch,
                                                         m->kpc_tile_ptr, m->kpc_src);
   SMPLB_CUDA_CHECK(cudaGetLastError());

@@ -57,7 +57,8 @@ class FitIO(C.Structure):
                 ('m_beta', C.c_void_p), ('v_beta', C.c_void_p),
                 ('loss', C.c_void_p), ('scratch', C.c_void_p),
                 ('cfg', LossCfg), ('n_total', C.c_int64), ('step', C.c_int32),
-                ('lr', C.c_float), ('beta1', C.c_float), ('beta2', C.c_float), ('eps', C.c_float)]
+                ('lr', C.c_float), ('beta1', C.c_float), ('beta2', C.c_float), ('eps', C.c_float),
+                ('step_dev', C.c_void_p)]
 
 
 # name -> (restype, argtypes); every symbol include/smplb200.h declares
@@ -87,7 +88,7 @@ SYMBOLS = {
                                    C.c_int32, C.c_void_p]),
     'smplb_project_backward': (C.c_int32, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
-                                           C.c_void_p, C.c_void_p]),
+                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_fit_scratch_bytes': (C.c_size_t, [C.c_int32]),
     'smplb_fit_step': (C.c_int32, [C.c_void_p, C.POINTER(FitIO), C.c_void_p]),
     'smplb_mesh_create': (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32, C.c_void_p, C.c_int32, C.c_int32]),
@@ -114,6 +115,9 @@ SYMBOLS = {
                                    C.c_int32, C.c_void_p, C.c_void_p]),
     'smplb_timing_begin': (C.c_int32, [C.c_int32]),
     'smplb_timing_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
+    'smplb_adam_tick': (C.c_int32, [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
+    'smplb_adam_step_dev': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_float, C.c_float, C.c_float, C.c_void_p]),
     'smplb_adam_step': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_int32, C.c_float, C.c_float, C.c_float, C.c_float,
                                     C.c_void_p]),

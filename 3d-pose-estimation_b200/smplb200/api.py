@@ -233,7 +233,8 @@ def project(points, cams_pos, cams_angles, focal_lens, P=1, cam_tiled=True):
     return uv
 
 
-def project_backward(points, cams_pos, cams_angles, focal_lens, g_uv, P=1, cam_tiled=True):
+def project_backward(points, cams_pos, cams_angles, focal_lens, g_uv, P=1, cam_tiled=True, want_focal=False):
+    """Adjoint of project(): (g_pts, g_cam_pos, g_cam_angles) and, with want_focal, g_focal_lens as a 4th value."""
     dev = _cuda_dev(points)
     pts = _dev_f32(points, dev)
     N = pts.shape[0]
@@ -244,11 +245,12 @@ def project_backward(points, cams_pos, cams_angles, focal_lens, g_uv, P=1, cam_t
     g_pts = torch.empty((N, 3), dtype=torch.float32, device=dev)
     g_cp = torch.empty_like(cp)
     g_ca = torch.empty_like(ca)
+    g_fl = torch.empty_like(fl) if want_focal else None
     with torch.cuda.device(dev):
         check(_lib.lib().smplb_project_backward(N, P, _ptr(pts), _ptr(cp), _ptr(ca), _ptr(fl),
                                                 int(bool(cam_tiled)), _ptr(g), _ptr(g_pts),
-                                                _ptr(g_cp), _ptr(g_ca), _stream(dev)))
-    return g_pts, g_cp, g_ca
+                                                _ptr(g_cp), _ptr(g_ca), _ptr(g_fl), _stream(dev)))
+    return (g_pts, g_cp, g_ca, g_fl) if want_focal else (g_pts, g_cp, g_ca)
 
 
 def orth_proj(X, camera):
@@ -304,6 +306,26 @@ def adam_step(x, g, m, v, t, lr=2e-4, beta1=0.9, beta2=0.999, eps=1e-8):
     with torch.cuda.device(dev):
         check(_lib.lib().smplb_adam_step(x.numel(), _ptr(x), _ptr(g), _ptr(m), _ptr(v), int(t),
                                          lr, beta1, beta2, eps, _stream(dev)))
+    return x
+
+
+def adam_tick(step_dev, lr_t_dev, lr=2e-4, beta1=0.9, beta2=0.999):
+    """t = ++step_dev[0] (int32 device counter), lr_t_dev[0] = lr sqrt(1-b2^t)/(1-b1^t): once per optimiser step;
+    graph-capturable (the counter advances on every replay)."""
+    dev = step_dev.device
+    assert step_dev.is_cuda and step_dev.dtype == torch.int32 and lr_t_dev.dtype == torch.float32
+    with torch.cuda.device(dev):
+        check(_lib.lib().smplb_adam_tick(_ptr(step_dev), lr, beta1, beta2, _ptr(lr_t_dev), _stream(dev)))
+    return lr_t_dev
+
+
+def adam_step_dev(x, g, m, v, lr_t_dev, beta1=0.9, beta2=0.999, eps=1e-8):
+    """In-place TF1 Adam (pose_model_3d.py:393) with lr_t read from device memory (see adam_tick)."""
+    dev = x.device
+    assert x.is_cuda and x.is_contiguous() and x.dtype == torch.float32
+    with torch.cuda.device(dev):
+        check(_lib.lib().smplb_adam_step_dev(x.numel(), _ptr(x), _ptr(g), _ptr(m), _ptr(v), _ptr(lr_t_dev),
+                                             beta1, beta2, eps, _stream(dev)))
     return x
 
 

@@ -33,7 +33,9 @@ class Fitter:
         self.g_beta, self.g_theta = z(B, NB), z(B, NJ * 3)
         self.m_theta, self.v_theta = z(B, NJ * 3), z(B, NJ * 3)
         self.m_beta, self.v_beta = (z(B, NB), z(B, NB)) if fit_beta else (None, None)
-        self.loss = z(3)
+        self.loss = z(4)                                   # [share of the mean, capped, gate, Adam lr_t]
+        # Adam's step counter lives on the device (smplb_fit_io.step_dev): a captured step advances it on every replay
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         L = _lib.lib()
         self.scratch = torch.empty(L.smplb_fit_scratch_bytes(B), dtype=torch.uint8, device=dev)
         cfg = dict(DEFAULT_CAM)
@@ -44,23 +46,35 @@ class Fitter:
         self.hyper = (lr, beta1, beta2, eps)
         self.t = 0
 
-    def _io(self, step):
+    def _io(self, step, loss):
         p = lambda t: None if t is None else C.c_void_p(t.data_ptr())
         lr, b1, b2, eps = self.hyper
         return FitIO(self.B, p(self.beta), p(self.theta), p(self.cam_pos), p(self.cam_rot), p(self.focal),
                      p(self.gt_px), p(self.px), p(self.g_px), p(self.g_beta), p(self.g_theta), p(self.m_theta),
-                     p(self.v_theta), p(self.m_beta), p(self.v_beta), p(self.loss), p(self.scratch), self.losscfg,
-                     self.n_total, step, lr, b1, b2, eps)
+                     p(self.v_theta), p(self.m_beta), p(self.v_beta), p(loss), p(self.scratch), self.losscfg,
+                     self.n_total, step, lr, b1, b2, eps, p(self.step_dev))
 
-    def step(self):
+    def step(self, loss_out=None):
         """One fused fitting step (5-6 kernel launches on the current stream).  Returns the device loss tensor
-        [uncapped share, capped, gate] without synchronising."""
-        self.t += 1
-        io = self._io(self.t)
+        [uncapped share, capped, gate, lr_t] without synchronising.  loss_out: another 4-float device tensor to
+        receive them (e.g. a row of a per-step log that is all-reduced once every k steps)."""
+        self.t += 1                    # host mirror only; the kernels read the device counter
+        loss = self.loss if loss_out is None else loss_out
+        if loss.numel() < 4 or loss.dtype != torch.float32 or not loss.is_contiguous():
+            raise ValueError('loss_out must be a contiguous float32 tensor of >= 4 elements')
+        io = self._io(self.t, loss)
         with torch.cuda.device(self.dev):
             check(_lib.lib().smplb_fit_step(self.model._h, C.byref(io),
                                             C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)))
-        return self.loss
+        return loss
+
+    def reset_optimizer(self):
+        """Zero the Adam moments and the device step counter (stream-ordered)."""
+        self.t = 0
+        self.step_dev.zero_()
+        for t in (self.m_theta, self.v_theta, self.m_beta, self.v_beta):
+            if t is not None:
+                t.zero_()
 
 
 class MeshFitter:
@@ -83,6 +97,8 @@ class MeshFitter:
         self.m_theta, self.v_theta = z(B, NJ * 3), z(B, NJ * 3)
         self.m_beta, self.v_beta = (z(B, NB), z(B, NB)) if fit_beta else (None, None)
         self.loss = z(1)
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)    # device-side Adam step counter (graph-safe)
+        self.lr_t = z(1)
         self.out = {}
         self.scratch = torch.empty(int(_lib.lib().smplb_mse_scratch_bytes()), dtype=torch.uint8, device=dev)
         self.scales = (mesh_scale, joint_scale)
@@ -102,7 +118,8 @@ class MeshFitter:
                      g_out=self.g_joints, scratch=self.scratch)
         g_beta, g_theta = m.backward(self.beta, self.theta, g_verts=self.g_verts, g_joints=self.g_joints)
         lr, b1, b2, eps = self.hyper
-        api.adam_step(self.theta, g_theta, self.m_theta, self.v_theta, self.t, lr, b1, b2, eps)
+        api.adam_tick(self.step_dev, self.lr_t, lr, b1, b2)
+        api.adam_step_dev(self.theta, g_theta, self.m_theta, self.v_theta, self.lr_t, b1, b2, eps)
         if self.m_beta is not None:
-            api.adam_step(self.beta, g_beta, self.m_beta, self.v_beta, self.t, lr, b1, b2, eps)
+            api.adam_step_dev(self.beta, g_beta, self.m_beta, self.v_beta, self.lr_t, b1, b2, eps)
         return self.loss

@@ -13,8 +13,10 @@ class _Project(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_uv):
         pts, cpos, cang, foc = ctx.saved_tensors
-        g_pts, g_cp, g_ca = api.project_backward(pts, cpos, cang, foc, g_uv.contiguous(), P=1, cam_tiled=True)
-        return g_pts, g_cp, g_ca, None
+        # the reference project() is differentiable in all four arguments (project.py:22-46)
+        g_pts, g_cp, g_ca, g_f = api.project_backward(pts, cpos, cang, foc, g_uv.contiguous(), P=1, cam_tiled=True,
+                                                      want_focal=True)
+        return g_pts, g_cp, g_ca, g_f
 
 
 def project(points_world_space, cams_pos, cams_angles, focal_lens):

@@ -17,7 +17,9 @@
  *     no hidden device synchronisation, no allocation on the hot calls; the caller owns the
  *     workspace (`smplb_workspace_bytes`);
  *   - a model handle is immutable after creation: concurrent calls from several host threads /
- *     streams are legal when each call uses its own workspace.
+ *     streams are legal when each call uses its own workspace;
+ *   - the kernels launch on the CURRENT CUDA device of the calling thread: it must be the device
+ *     the model / mesh handle was created on (cudaSetDevice first), else SMPLB_E_INVALID_ARG.
  */
 #ifndef SMPLB200_H_
 #define SMPLB200_H_
@@ -184,24 +186,35 @@ typedef struct {
 int32_t smplb_backward(const smplb_model* m, const smplb_backward_io* io, void* workspace,
                        size_t workspace_bytes, int32_t flags, void* stream);
 
-/* Backward of project() wrt points and camera (pose_model_3d.py:243-245 path):
- * g_uv[N,2] -> g_pts[N,3] (nullable), g_cam_pos / g_cam_angles ([N,3] tiled or [N/P,3]), nullable */
+/* Backward of project() wrt points and camera (pose_model_3d.py:243-245 path; project.py:30-42 is differentiable in
+ * the focal length too): g_uv[N,2] -> g_pts[N,3], g_cam_pos / g_cam_angles ([N,3] tiled or [N/P,3]),
+ * g_focal_lens ([N] tiled or [N/P]); every output nullable. */
 int32_t smplb_project_backward(int32_t N, int32_t P, const float* pts, const float* cams_pos,
                                const float* cams_angles, const float* focal_lens,
                                int32_t cam_tiled, const float* g_uv, float* g_pts,
-                               float* g_cams_pos, float* g_cams_angles, void* stream);
+                               float* g_cams_pos, float* g_cams_angles, float* g_focal_lens, void* stream);
 
-/* tf.train.AdamOptimizer update (pose_model_3d.py:393): eps outside the bias correction. */
+/* tf.train.AdamOptimizer update (pose_model_3d.py:393): eps outside the bias correction.  `t` (1-based) is a host
+ * value baked into the launch: do not capture this call in a CUDA graph (use the _dev pair below). */
 int32_t smplb_adam_step(int64_t n, float* x, const float* g, float* m, float* v, int32_t t,
                         float lr, float beta1, float beta2, float eps, void* stream);
+/* The same update with the step counter on the DEVICE, so that a captured step advances Adam's bias correction on
+ * every graph replay: smplb_adam_tick does t = ++(*step_dev) and writes lr_t(t) = lr sqrt(1-b2^t)/(1-b1^t) to
+ * lr_t_dev[0] (once per optimiser step); smplb_adam_step_dev applies the update to one variable with that lr_t. */
+int32_t smplb_adam_tick(int32_t* step_dev, float lr, float beta1, float beta2, float* lr_t_dev, void* stream);
+int32_t smplb_adam_step_dev(int64_t n, float* x, const float* g, float* m, float* v, const float* lr_t_dev,
+                            float beta1, float beta2, float eps, void* stream);
 
 /* One Adam step of iterative fitting on the 2D re-projection loss with per-sample pose (and, when m_beta /
  * v_beta are given, shape) as the variables: the loss block of deps/pose_3d/pose_model_3d.py:194-238 driven by
  * the optimiser of :393-401, joint-only path (no vertices).  theta / beta / m / v are updated in place.
  * loss[0] = scale * sum((px - gt_px)^2) / n_total (this shard's share of the global mean; n_total = global
  * B*24*2 so that the shares of several GPUs add up under an all-reduce), loss[1] = min(cap, loss[0]),
- * loss[2] = 1 when the cap is inactive else 0 (the gradient gate of tf.minimum, :237).
- * Stream-ordered, allocation-free: capturable in a CUDA graph. */
+ * loss[2] = 1 when the cap is inactive else 0 (the gradient gate of tf.minimum, :237), loss[3] = Adam's lr_t of this
+ * step.  The cap acts on the GLOBAL mean, so reproj_cap > 0 requires n_total == B*48 (SMPLB_E_UNSUPPORTED otherwise).
+ * Stream-ordered, allocation-free: capturable in a CUDA graph when step_dev is given (the step counter then lives on
+ * the device and every replay advances the bias correction; with step_dev == NULL the host value `step` is used and
+ * a captured launch would freeze it). */
 typedef struct {
   int32_t B;
   float* beta;            /* [B,10]  updated when m_beta != NULL */
@@ -218,12 +231,13 @@ typedef struct {
   float* v_theta;
   float* m_beta;          /* nullable pair */
   float* v_beta;
-  float* loss;            /* [3] device */
+  float* loss;            /* [4] device */
   void* scratch;          /* smplb_fit_scratch_bytes(B) device bytes */
   smplb_losscfg cfg;
   int64_t n_total;
-  int32_t step;           /* 1-based */
+  int32_t step;           /* 1-based; ignored when step_dev != NULL */
   float lr, beta1, beta2, eps;
+  int32_t* step_dev;      /* device, nullable: steps done so far (start at 0); incremented by the call */
 } smplb_fit_io;
 size_t smplb_fit_scratch_bytes(int32_t B);
 int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, void* stream);

@@ -85,18 +85,19 @@ def test_project_backward(tiled):
     ca = rng.normal(0, 0.1, size=(nc, 3))
     fl = np.full(nc, 0.05)
     w = rng.normal(size=(N, 2))
-    tp, tcp, tca = _t64(pts, True), _t64(cp, True), _t64(ca, True)
+    tp, tcp, tca, tfl = _t64(pts, True), _t64(cp, True), _t64(ca, True), _t64(fl, True)
     if tiled:
-        uv = rt.project(tp, tcp, tca, _t64(fl))
+        uv = rt.project(tp, tcp, tca, tfl)
     else:
-        uv = rt.project(tp, rt.tile_cam(tcp, P), rt.tile_cam(tca, P), rt.tile_cam(_t64(fl), P))
+        uv = rt.project(tp, rt.tile_cam(tcp, P), rt.tile_cam(tca, P), rt.tile_cam(tfl, P))
     (uv * _t64(w)).sum().backward()
-    g_pts, g_cp, g_ca = smplb200.project_backward(pts.astype(np.float32), cp.astype(np.float32),
-                                                  ca.astype(np.float32), fl.astype(np.float32),
-                                                  w.astype(np.float32), P=P, cam_tiled=tiled)
+    g_pts, g_cp, g_ca, g_fl = smplb200.project_backward(pts.astype(np.float32), cp.astype(np.float32),
+                                                        ca.astype(np.float32), fl.astype(np.float32),
+                                                        w.astype(np.float32), P=P, cam_tiled=tiled, want_focal=True)
     assert maxrel(g_pts.cpu().numpy(), tp.grad.numpy()) <= GTOL
     assert maxrel(g_cp.cpu().numpy(), tcp.grad.numpy()) <= GTOL
     assert maxrel(g_ca.cpu().numpy(), tca.grad.numpy()) <= GTOL
+    assert maxrel(g_fl.cpu().numpy(), tfl.grad.numpy()) <= GTOL          # project.py:35-42 is differentiable in f
 
 
 def test_dropin_project_autograd():
@@ -107,14 +108,16 @@ def test_dropin_project_autograd():
     pts = torch.tensor(rng.normal(0, 0.5, size=(N, 3)), dtype=torch.float32, device='cuda', requires_grad=True)
     cp = torch.tensor(np.tile([[0.0, -0.35, -4.0]], (N, 1)), dtype=torch.float32, device='cuda', requires_grad=True)
     ca = torch.tensor(rng.normal(0, 0.05, size=(N, 3)), dtype=torch.float32, device='cuda', requires_grad=True)
-    fl = torch.full((N,), 0.05, device='cuda')
+    fl = torch.full((N,), 0.05, device='cuda', requires_grad=True)      # a learnable focal length
     uv = project(pts, cp, ca, fl)
     uv.square().sum().backward()
     tp, tcp, tca = _t64(pts.detach().cpu().numpy(), True), _t64(cp.detach().cpu().numpy(), True), _t64(ca.detach().cpu().numpy(), True)
-    rt.project(tp, tcp, tca, _t64(fl.cpu().numpy())).square().sum().backward()
+    tfl = _t64(fl.detach().cpu().numpy(), True)
+    rt.project(tp, tcp, tca, tfl).square().sum().backward()
     assert maxrel(pts.grad.cpu().numpy(), tp.grad.numpy()) <= GTOL
     assert maxrel(cp.grad.cpu().numpy(), tcp.grad.numpy()) <= GTOL
     assert maxrel(ca.grad.cpu().numpy(), tca.grad.numpy()) <= GTOL
+    assert maxrel(fl.grad.cpu().numpy(), tfl.grad.numpy()) <= GTOL
 
 
 @pytest.mark.parametrize('B,with_kp', [(3, False), (40, True), (130, False)])

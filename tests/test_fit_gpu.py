@@ -70,23 +70,77 @@ def test_reference_cap_gates_the_gradient(gpu_model):
 
 
 def test_fit_step_in_cuda_graph(gpu_model, synth_dd):
-    """The step is allocation-free and stream-ordered: replaying it from a CUDA graph gives the same result."""
-    B = 64
+    """The step is allocation-free and stream-ordered, and Adam's step counter lives on the device: N replays of ONE
+    captured step equal N eager steps (the bias correction lr_t advances on every replay, pose_model_3d.py:393)."""
+    B, N = 64, 6
     inp = syn.make_inputs(B, seed=9, dtype=np.float32)
     tgt = syn.make_inputs(B, seed=10, dtype=np.float32)
     out = gpu_model.forward(inp['beta'], tgt['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=4)
     gt_px = out['px'].clone()
     fa = Fitter(gpu_model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, lr=1e-2)
     fb = Fitter(gpu_model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, lr=1e-2)
-    fa.step()
+    la = [fa.step().clone() for _ in range(N)]
     s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(s):
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=s):
-            fb.step()                                     # captured with step = 1 (bias correction of step 1)
-    fb.theta.copy_(torch.as_tensor(inp['theta']).cuda()); fb.m_theta.zero_(); fb.v_theta.zero_()
-    g.replay()
+            fb.step()                                     # captured once; nothing runs during capture
+    torch.cuda.current_stream().wait_stream(s)
+    lb = []
+    for _ in range(N):
+        g.replay()
+        lb.append(fb.loss.clone())
     torch.cuda.synchronize()
+    assert int(fb.step_dev) == N and int(fa.step_dev) == N
+    assert torch.equal(fa.theta, fb.theta)
+    assert torch.equal(torch.stack(la), torch.stack(lb))
+    # lr_t of step N against the formula (TF1: lr sqrt(1 - b2^t) / (1 - b1^t))
+    want = 1e-2 * np.sqrt(1 - 0.999 ** N) / (1 - 0.9 ** N)
+    assert abs(float(lb[-1][3]) - want) <= 1e-5 * want
+    # a frozen counter (the round-1 behaviour) would differ: lr_t(1) != lr_t(N)
+    assert abs(float(lb[0][3]) - float(lb[-1][3])) > 1e-3 * want
+
+
+def test_cap_with_sharded_mean_is_rejected(gpu_model):
+    """The cap of pose_model_3d.py:237 gates on the GLOBAL loss; a shard cannot decide it."""
+    from smplb200._lib import SmplbError, E_UNSUPPORTED
+    B = 8
+    inp = syn.make_inputs(B, seed=2, dtype=np.float32)
+    gt_px = np.zeros((B, 24, 2), np.float32)
+    f = Fitter(gpu_model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, reproj_cap=1.0 / 24,
+               n_total=2 * B * 48)
+    with pytest.raises(SmplbError) as e:
+        f.step()
+    assert e.value.code == E_UNSUPPORTED
+
+
+def test_mesh_fit_in_cuda_graph(gpu_model, synth_dd):
+    """MeshFitter (forward -> mse_grad x2 -> vertex backward -> Adam with the device step counter) replayed from one
+    CUDA graph equals the eager steps."""
+    from smplb200.fit import MeshFitter
+    B, N = 40, 4
+    inp = syn.make_inputs(B, seed=31, dtype=np.float32)
+    tgt = syn.make_inputs(B, seed=32, dtype=np.float32)
+    o = gpu_model.forward(inp['beta'], tgt['theta'], want_kp=False, want_Rs=False)
+    gv, gj = o['verts'].clone(), o['joints'].clone()
+    fa = MeshFitter(gpu_model, inp['beta'], inp['theta'], gv, gj, lr=1e-2)
+    fb = MeshFitter(gpu_model, inp['beta'], inp['theta'], gv, gj, lr=1e-2)
+    fb.step()                                             # allocates fb's buffers outside the capture
+    fb.theta.copy_(fa.theta); fb.m_theta.zero_(); fb.v_theta.zero_(); fb.step_dev.zero_()
+    for _ in range(N):
+        fa.step()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            fb.step()
+    torch.cuda.current_stream().wait_stream(s)
+    for _ in range(N):
+        g.replay()
+    torch.cuda.synchronize()
+    assert int(fb.step_dev) == N
     assert torch.equal(fa.theta, fb.theta)
 
 
