@@ -5,9 +5,12 @@
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 A "step" is one pass of the hot path (pose_prep -> blend GEMM -> skinning, with the fused
-projection of the 24 posed joints) over one batch of B synthetic samples per GPU, inputs resident
-in HBM.  Default workload: B = 65536 samples per GPU (BASELINE.json configs[3]/north_star target;
-weak scaling: every rank owns its own 65536-sample shard, no collective on the forward path).
+projection of the 24 posed joints) over one batch of synthetic samples, inputs resident in HBM.
+Default workload = BASELINE.json configs[3] as written: a GLOBAL batch of 65536 samples sharded over
+the N GPUs (rank r owns samples [r*B/N, (r+1)*B/N), smplb200.dist.shard_range; strong scaling, no
+collective on the forward path).  At N > 1 the 4-kernel step is replayed from one CUDA graph (the
+8192-sample shard of N = 8 takes ~0.5 ms); per-kernel times come from an eager pass with event hooks
+right after the timed region.  `--scaling weak` keeps --batch samples PER GPU (the round-1 protocol).
 `e2e` times the same step through the C ABI with HOST buffers (smplb_forward_host: H2D of
 beta/theta/camera from pinned memory, kernels, D2H of verts/joints/keypoints/2D keypoints).
 `--impl reference` times the reference's CPU op sequence (oracle/ref_torch.py port of the TF graph,
@@ -15,6 +18,7 @@ all host threads) on a bounded sample of the same workload.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import sys
@@ -44,6 +48,53 @@ def peaks():
         return float(d['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
     except Exception:
         return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def tensor_peaks():
+    """bf16 dense burst / sustained TFLOP/s (MEASURED_PEAKS.json, else the recipe's fallback) and the TF32 rate
+    measured on this pool by tools/measure_tf32_peak.py (profiles/r02_tf32_peak.json)."""
+    out = {'bf16_burst': 1590.0, 'bf16_sustained': 1400.0, 'tf32_burst': None, 'source': 'fallback (B200_PROFILING.md)'}
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            d = json.load(f)
+        out.update(bf16_burst=float(d['bf16_tflops']), bf16_sustained=float(d['bf16_tflops_sustained']),
+                   source='measured (MEASURED_PEAKS.json)')
+    except Exception:
+        pass
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'r02_tf32_peak.json')) as f:
+            d = json.load(f)
+        out['tf32_burst'], out['tf32_sustained'] = float(d['tf32_tflops']), float(d['tf32_tflops_sustained'])
+    except Exception:
+        pass
+    return out
+
+
+def blob_sha(path):
+    data = open(path, 'rb').read()
+    return hashlib.sha1(b'blob %d\0' % len(data) + data).hexdigest()
+
+
+def ncu_record(name, batch):
+    """A committed ncu record (tools/ncu_to_profiles.py) is only used while the kernel sources it was captured from
+    are unchanged (git blob hashes) and the batch matches; else None."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', name)) as f:
+            rec = json.load(f)
+        if int(rec.get('batch', -1)) != batch:
+            return None
+        for src, sha in rec['sources'].items():
+            if blob_sha(os.path.join(PKG, 'csrc', src)) != sha:
+                return None
+        return rec
+    except Exception:
+        return None
+
+
+DTYPE = 'f32 (fp16/bf16 split-operand tensor products, fp32 accumulate)'
+# tensor work ISSUED by blend_tc_kernel per sample: 3 kind::f16 products over the padded 224 x 20736 operand images
+BLEND_FLOP_ISSUED = 3 * 2 * 224 * 20736
+BLEND_FLOP_FP32EQ = 2 * 217 * 20670
 
 
 class ClockSampler(threading.Thread):
@@ -113,7 +164,20 @@ def cpu_reference_rate(B_chunk, min_seconds, max_chunks, seed=1000):
     return n * B_chunk / el, cores, n * B_chunk, el, step
 
 
-def run_reference(args, rank):
+def workload_config(args, world):
+    """config block shared by both arms (the driver compares them)."""
+    if args.scaling == 'strong':
+        wl = ('SMPL forward + 24-joint perspective projection, global batch %d sharded over %d GPU(s) '
+              '(BASELINE configs[3]: rank r owns samples [r*B/N, (r+1)*B/N))' % (args.batch, world))
+    else:
+        wl = ('SMPL forward + 24-joint perspective projection, %d samples per GPU on %d GPU(s) (weak scaling, global '
+              'batch %d)' % (args.batch, world, args.batch * world))
+    return {'workload': wl,
+            'model': 'synthetic SMPL-shaped (6890 verts, 24 joints, 10 betas, <=4 LBS weights/vertex), seed 0',
+            'outputs': 'verts[B,6890,3], J_transformed[B,24,3], keypoints[B,19,3], Rs, uv, px[B,24,2]'}
+
+
+def run_reference(args, rank, world):
     if rank != 0:
         return
     rate, cores, ns, el, step = cpu_reference_rate(args.ref_chunk, 0.0, 1)
@@ -124,16 +188,15 @@ def run_reference(args, rank):
         step()
     el = time.perf_counter() - t0
     val = args.steps * args.ref_chunk / el
-    sample = '%d steps x %d samples of the B=%d/GPU workload, fp32, torch-CPU port of the TF op sequence' % (
-        args.steps, args.ref_chunk, args.batch)
+    sample = '%d steps x %d samples of the same workload, fp32, torch-CPU port of the TF op sequence incl. tile(W)' % (
+        args.steps, args.ref_chunk)
+    cfg = workload_config(args, world)
+    cfg['cpu_sample'] = 'bounded sample: %d samples per step' % args.ref_chunk
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * el / args.steps,
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
-        'data': 'synthetic',
-        'config': {'workload': 'SMPL forward + 24-joint perspective projection, B=%d per GPU '
-                               '(CPU arm: bounded sample, %d samples per step)' % (args.batch, args.ref_chunk),
-                   'model': 'synthetic SMPL-shaped (6890 verts, 24 joints, 10 betas), seed 0'},
+        'higher_is_better': True, 'scaling': args.scaling, 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic', 'config': cfg,
         'cpu_baseline': {'value': val, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': val, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
@@ -163,38 +226,47 @@ def run_fit(args, rank, local_rank, world, dist):
         gt_px = model.forward(inp['beta'], tgt['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=4)['px'].clone()
         f = Fitter(model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, focal=inp['focal'], lr=2e-4,
                    n_total=B * world * 48)
-    gl = torch.zeros(1, device=dev)
+    # The loss scalar is only logged: with --allreduce-every k the k per-step values are written into a
+    # [k,4] device log by the fit kernels themselves (smplb_fit_io.loss may point anywhere) and summed over the ranks
+    # by ONE NCCL all-reduce per k steps, instead of one 25-35 us collective serialised into every 44 us step.
+    k = max(1, args.allreduce_every)
+    use_graph = bool(args.graph)
+    log = torch.zeros((k, 4), device=dev)
 
-    def step():
-        # in-stream all-reduce: at ~50 us per step the loop is host-launch-bound, and the side-stream variant
-        # (smplb200.dist.SideStreamAllReduce) costs more host time per step than the 24 us collective it hides
-        l = f.step()
-        gl.copy_(l[:1])
-        sd.allreduce_scalars(gl)
+    def step_block():
+        for i in range(k):
+            if mesh:
+                l = f.step()
+                log[i, :1].copy_(l[:1])
+            else:
+                f.step(loss_out=log[i])
+        sd.allreduce_scalars(log)          # columns 0 (loss share) sum to the global mean; the others are per rank
 
-    for _ in range(args.warmup):
-        step()
-    first = float(gl)
+    n_blocks = (args.steps + k - 1) // k
+    steps = n_blocks * k
+    for _ in range(max(1, (args.warmup + k - 1) // k)):
+        step_block()
+    first = float(log[0, 0])
     graph = None
-    if args.graph:
-        # the whole step -- kernels and, with several GPUs, the NCCL all-reduce of the loss scalar -- replayed from
-        # one CUDA graph: the 50 us step is host-launch-bound otherwise
+    if use_graph:
+        # k steps and their one collective replayed from one CUDA graph; Adam's step counter lives on the device, so
+        # every replay advances the bias correction
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
-            step()          # the collective once on the capture stream before capturing it
+            step_block()        # the collective once on the capture stream before capturing it
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=s):
-                step() if world > 1 else f.step()
+                step_block()
         torch.cuda.current_stream().wait_stream(s)
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
-        graph.replay() if graph is not None else step()
+    for _ in range(n_blocks):
+        graph.replay() if graph is not None else step_block()
     e1.record()
     torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
@@ -203,14 +275,17 @@ def run_fit(args, rank, local_rank, world, dist):
     if rank == 0:
         ms = float(t[0])
         print(json.dumps({
-            'metric': 'smpl_fit_sample_steps_per_s', 'value': world * B * args.steps / (ms * 1e-3), 'unit': 'sample-steps/s',
-            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms / args.steps,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'metric': 'smpl_fit_sample_steps_per_s', 'value': world * B * steps / (ms * 1e-3), 'unit': 'sample-steps/s',
+            'n_gpus': world, 'steps': steps, 'warmup': args.warmup, 'ms_per_step': ms / steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if not mesh else DTYPE,
+            'data': 'synthetic',
             'config': {'workload': ('SMPL fitting, fwd+bwd of the %s + TF1 Adam on theta, B=%d per GPU (BASELINE configs[2])'
                                     % ('3D mesh + joint loss (backward through the vertices)' if mesh else
                                        '2D re-projection loss', B)), 'cuda_graph': graph is not None,
-                       'collective': 'all-reduce of 1 loss scalar per step' if world > 1 else 'none'},
-            'gpu_launches': (15 if mesh else 5) * args.steps, 'loss_first': first, 'loss_last': float(f.loss[0]) * (1 if world == 1 else 1)}),
+                       'collective': ('NCCL all-reduce of the [%d,4] loss log once every %d step(s)' % (k, k)) if world > 1 else 'none',
+                       'adam_step_counter': 'device (advances on graph replays)'},
+            'gpu_launches': (15 if mesh else 5) * steps, 'loss_first': first, 'loss_last': float(log[k - 1, 0]),
+            'adam_steps_done': int(f.step_dev)}),
             flush=True)
     if graph is not None:
         # a captured NCCL collective keeps the communicator busy: drop the graph before tearing the group down
@@ -224,31 +299,36 @@ def run_fit(args, rank, local_rank, world, dist):
 
 
 def run_sweep(args, rank, local_rank, world, dist):
-    """BASELINE config 5: batch-size sweep 1..65536 per GPU, forward (+projection) and forward+backward
-    (mesh + joint loss gradients through the vertex path), per-kernel times and roofline fractions.
-    Each rank runs its own shard (weak scaling, no collective); the time is the max over ranks."""
+    """BASELINE config 5: batch-size sweep 1..65536, forward (+projection) and forward+backward (mesh + joint loss
+    gradients through the vertex path), per-kernel times and roofline fractions, at 1/2/4/8 GPUs.  Under --scaling
+    strong (default) B is the GLOBAL batch and rank r runs its shard_range slice (ranks without samples idle); under
+    weak every rank runs B samples.  No collective; the time is the max over ranks."""
     import smplb200
-    from smplb200 import synthetic as syn, _lib
+    from smplb200 import synthetic as syn, _lib, dist as sd
     dev = torch.device('cuda', local_rank)
     model = smplb200.Model(syn.make_synthetic_smpl(0), device=local_rank)
     L = _lib.lib()
     peak, peak_src = peaks()
-    try:
-        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
-            tf32_peak = float(json.load(f)['bf16_tflops']) / 2.0      # TF32 dense = half the bf16 rate
-    except Exception:
-        tf32_peak = 1125.0
+    tp = tensor_peaks()
     rows = []
     Bs = [1 << i for i in range(0, 17)]
     if args.batch != 65536:
         Bs = [b for b in Bs if b <= args.batch]
-    for B in Bs:
-        inp = syn.make_inputs(B, seed=1000 + rank)
-        d = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
-        out = {}
-        g_verts = torch.randn((B, 6890, 3), device=dev) * (1.0 / (B * 20670))
-        g_joints = torch.randn((B, 24, 3), device=dev) * (1.0 / (B * 72))
+    for Bg in Bs:
+        if args.scaling == 'strong':
+            b0, b1 = sd.shard_range(Bg, rank, world)
+            B, B_global = b1 - b0, Bg
+        else:
+            B, B_global = Bg, Bg * world
         steps = max(3, min(args.steps, int(2e6 / max(B, 1)) + 3))
+        res = {'B_global': B_global, 'B_per_gpu_max': (B_global + world - 1) // world if args.scaling == 'strong' else Bg,
+               'steps': steps}
+        if B > 0:
+            inp = syn.make_inputs(B, seed=1000 + rank)
+            d = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
+            out = {}
+            g_verts = torch.randn((B, 6890, 3), device=dev) * (1.0 / (B_global * 20670))
+            g_joints = torch.randn((B, 24, 3), device=dev) * (1.0 / (B_global * 72))
 
         def fwd(flags=0):
             model.forward(d['beta'], d['theta'], d['cam_pos'], d['cam_rot'], d['focal'], flags=flags, out=out)
@@ -257,40 +337,48 @@ def run_sweep(args, rank, local_rank, world, dist):
             fwd(_lib.F_KEEP_VPOSED)
             model.backward(d['beta'], d['theta'], g_verts=g_verts, g_joints=g_joints)
 
-        res = {'B_per_gpu': B, 'steps': steps}
         for name, fn in (('fwd', fwd), ('fwd_bwd', fwdbwd)):
-            for _ in range(3):
+            for _ in range(3 if B > 0 else 0):
                 fn()
             torch.cuda.synchronize()
             if dist is not None:
                 dist.barrier()
             kt = None
-            if name == 'fwd':
-                L.smplb_timing_begin(steps)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(steps):
-                fn()
-            e1.record()
-            torch.cuda.synchronize()
-            if name == 'fwd':
-                kms = (C.c_float * (4 * steps))()
-                nc = C.c_int32(0)
-                L.smplb_timing_end(kms, C.byref(nc))
-                kt = np.array(list(kms), dtype=np.float64).reshape(-1, 4)[:nc.value].mean(axis=0)
-            t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+            ms_local = 0.0
+            if B > 0:
+                if name == 'fwd':
+                    L.smplb_timing_begin(steps)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(steps):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                if name == 'fwd':
+                    kms = (C.c_float * (4 * steps))()
+                    nc = C.c_int32(0)
+                    L.smplb_timing_end(kms, C.byref(nc))
+                    kt = np.array(list(kms), dtype=np.float64).reshape(-1, 4)[:nc.value].mean(axis=0)
+                ms_local = e0.elapsed_time(e1) / steps
+            t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
             if dist is not None:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t[0])
             res[name + '_ms'] = ms
-            res[name + '_samples_per_s'] = world * B / (ms * 1e-3)
-            if kt is not None:
-                res['kernel_ms'] = {'pose_prep': kt[0], 'blend_gemm': kt[1], 'skinning': kt[2], 'keypoints': kt[3]}
+            res[name + '_samples_per_s'] = B_global / (ms * 1e-3)
+            if kt is not None and rank == 0:
+                res['kernel_ms_rank0'] = {'pose_prep': kt[0], 'blend_gemm': kt[1], 'skinning': kt[2], 'keypoints': kt[3]}
                 res['skin_hbm_frac'] = SKIN_BYTES_PER_SAMPLE * B / (kt[2] * 1e-3) / 1e9 / peak
-                res['blend_tf32_util_fp32eq'] = 8970780.0 * B / (kt[1] * 1e-3) / 1e12 / tf32_peak
-                res['blend_tf32_util_issued'] = 3 * res['blend_tf32_util_fp32eq']
+                res['blend_frac_of_bf16_burst_issued'] = BLEND_FLOP_ISSUED * B / (kt[1] * 1e-3) / 1e12 / tp['bf16_burst']
+                res['blend_tflops_fp32_equivalent'] = BLEND_FLOP_FP32EQ * B / (kt[1] * 1e-3) / 1e12
+        # backward roofline: SURVEY 8d algorithmic bytes of the vertex path (read g_verts + v_posed, write g_vposed)
+        if 'fwd_bwd_ms' in res and 'fwd_ms' in res:
+            bwd = max(res['fwd_bwd_ms'] - res['fwd_ms'], 1e-9)
+            res['bwd_ms'] = bwd
+            res['bwd_hbm_frac_algorithmic'] = 248040.0 * res['B_per_gpu_max'] / (bwd * 1e-3) / 1e9 / peak
         rows.append(res)
-        del g_verts, out, d
+        if B > 0:
+            del g_verts, out, d
     cpu_rows = []
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # the CPU port of the reference op sequence at B in {1, 32, 256, 1024} (BASELINE configs[0] is the
@@ -307,11 +395,13 @@ def run_sweep(args, rank, local_rank, world, dist):
             cpu_rows.append({'B': Bc, 'ms': 1e3 * med, 'samples_per_s': Bc / med, 'reps': len(ts), 'cores': cores,
                              'kind': 'port'})
     if rank == 0:
-        print(json.dumps({'metric': 'smpl_sweep', 'n_gpus': world, 'scaling': 'weak', 'dtype': 'f32', 'data': 'synthetic',
+        print(json.dumps({'metric': 'smpl_sweep', 'n_gpus': world, 'scaling': args.scaling, 'dtype': DTYPE, 'data': 'synthetic',
                           'cpu_port_rows': cpu_rows,
-                          'peaks': {'hbm_gbs': peak, 'tf32_tflops': tf32_peak, 'source': peak_src},
+                          'peaks': {'hbm_gbs': peak, 'tensor': tp, 'source': peak_src},
                           'config': {'workload': 'BASELINE configs[4]: batch sweep, fwd+projection and fwd+bwd '
-                                                 '(g_verts + g_joints -> g_theta, g_beta), B per GPU'},
+                                                 '(g_verts + g_joints -> g_theta, g_beta); %s' % (
+                                                     'global batch sharded over the ranks' if args.scaling == 'strong'
+                                                     else 'B per GPU')},
                           'rows': rows}), flush=True)
     if dist is not None:
         dist.barrier()
@@ -533,7 +623,15 @@ def main():
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=5)
-    ap.add_argument('--batch', type=int, default=65536, help='samples per GPU per step')
+    ap.add_argument('--batch', type=int, default=65536,
+                    help='samples per step: the GLOBAL batch under --scaling strong (default), per GPU under weak')
+    ap.add_argument('--scaling', default='strong', choices=['strong', 'weak'],
+                    help='strong: --batch is the global batch, sharded over the ranks (BASELINE configs[3]); '
+                         'weak: --batch samples per GPU')
+    ap.add_argument('--graph', action=argparse.BooleanOptionalAction, default=None,
+                    help='replay the step from one CUDA graph (default: on when more than one GPU; fit mode: off)')
+    ap.add_argument('--allreduce-every', type=int, default=1,
+                    help='fit mode: all-reduce the logged loss scalars once every k steps (k steps per graph)')
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--blend', default='tc', choices=['tc', 'simt'])
     ap.add_argument('--e2e-steps', type=int, default=3)
@@ -544,7 +642,6 @@ def main():
     ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep', 'raster', 'normals'],
                     help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
     ap.add_argument('--loss', choices=['reproj', 'mesh'], default='reproj', help='fit mode: which loss drives the step')
-    ap.add_argument('--graph', action='store_true', help='fit mode: replay the step from a CUDA graph')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else max(args.warmup, 1)
 
@@ -552,7 +649,7 @@ def main():
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     if args.impl == 'reference':
-        run_reference(args, rank)
+        run_reference(args, rank, world)
         return
 
     assert torch.cuda.is_available(), 'bench.py needs a CUDA device (no CPU fallback)'
@@ -577,10 +674,22 @@ def main():
             dist.barrier()
             dist.destroy_process_group()
         return
+    run_forward(args, rank, local_rank, world, dist)
+
+
+def run_forward(args, rank, local_rank, world, dist):
+    """The headline metric: SMPL forward + projection samples/s (BASELINE configs[1]/[3])."""
+    import smplb200
+    from smplb200 import synthetic as syn, _lib, dist as sd
     dev = torch.device('cuda', local_rank)
     dd = syn.make_synthetic_smpl(0)
     model = smplb200.Model(dd, device=local_rank)
-    B = args.batch
+    if args.scaling == 'strong':
+        b0, b1 = sd.shard_range(args.batch, rank, world)      # contiguous slice of the global batch
+        B, B_global = b1 - b0, args.batch
+    else:
+        B, B_global = args.batch, args.batch * world
+    use_graph = args.graph if args.graph is not None else world > 1
     flags = (_lib.F_BLEND_SIMT | _lib.F_SKIN_SIMT) if args.blend == 'simt' else 0
     inp = syn.make_inputs(B, seed=1000 + rank)
     d = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
@@ -597,18 +706,39 @@ def main():
 
     for _ in range(args.warmup):
         step()
+    graph = None
+    if use_graph and B > 0:
+        # the whole step (pose_prep, blend GEMM, skinning, keypoints) as one graph launch: at B/N = 8192 the step is
+        # ~0.5 ms and four separate launches + ctypes calls would show
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                step()
+        torch.cuda.current_stream().wait_stream(side)
+        for _ in range(args.warmup):
+            graph.replay()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     L = _lib.lib()
-    L.smplb_timing_begin(args.steps)
+    if graph is None:
+        L.smplb_timing_begin(args.steps)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        step()
+        graph.replay() if graph is not None else step()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    if graph is not None:
+        # per-kernel times: the same steps once more, eager, with the library's event hooks (outside the timed region:
+        # events cannot be read back from inside a graph)
+        L.smplb_timing_begin(args.steps)
+        for _ in range(args.steps):
+            step()
+        torch.cuda.synchronize()
     kms = (C.c_float * (4 * args.steps))()
     ncalls = C.c_int32(0)
     L.smplb_timing_end(kms, C.byref(ncalls))
@@ -616,7 +746,7 @@ def main():
 
     # ---- e2e: host buffers through smplb_forward_host --------------------------------------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and B > 0:
         NK = model.NK
         hb = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
         ho = {'verts': torch.empty((B, 6890, 3), dtype=torch.float32).pin_memory(),
@@ -648,54 +778,72 @@ def main():
         h2d = sum(hb[k].numel() * 4 for k in hb)
         d2h = sum(ho[k].numel() * 4 for k in ho)
         e2e = (el, h2d, d2h)
+    elif not args.no_e2e:
+        barrier()
+        barrier()
     sampler.stop_flag = True
     sampler.join()
 
-    t_all = torch.tensor([ms, e2e[0] if e2e else 0.0], dtype=torch.float64, device=dev)
+    t_all = torch.tensor([ms, e2e[0] if e2e else 0.0, float(kt[:, :].sum(axis=1).mean()) if len(kt) else 0.0],
+                         dtype=torch.float64, device=dev)
+    io_bytes = torch.tensor([e2e[1] if e2e else 0, e2e[2] if e2e else 0], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t_all, op=dist.ReduceOp.MAX)
-    ms_max, e2e_max = float(t_all[0]), float(t_all[1])
+        dist.all_reduce(io_bytes, op=dist.ReduceOp.SUM)
+    ms_max, e2e_max, ksum_max = float(t_all[0]), float(t_all[1]), float(t_all[2])
 
     if rank == 0:
         peak, peak_src = peaks()
+        tp = tensor_peaks()
         skin_ms = float(kt[:, 2].mean()) if len(kt) else float('nan')
+        blend_ms = float(kt[:, 1].mean()) if len(kt) else float('nan')
         achieved = SKIN_BYTES_PER_SAMPLE * B / (skin_ms * 1e-3) / 1e9
-        traffic = None
-        try:
-            with open(os.path.join(ROOT, 'profiles', 'skin_traffic.json')) as f:
-                tj = json.load(f)
-            if int(tj.get('batch', -1)) == B:
-                traffic = tj.get('dram_bytes_per_launch')
-        except Exception:
-            pass
+        tr = ncu_record('skin_traffic.json', B)
+        gr = ncu_record('blend_tensor_pipe.json', B)
+        issued_tflops = BLEND_FLOP_ISSUED * B / (blend_ms * 1e-3) / 1e12
+        cfg = workload_config(args, world)
+        cfg.update({
+            'samples_per_gpu': B, 'global_batch': B_global, 'cuda_graph': graph is not None,
+            'blend_gemm': 'tcgen05 kind::f16: f16 main product + f16/bf16 residual products, fp32 accumulate (fp32-faithful, 2e-7 of the vertex scale; |beta| and model constants <= 65504)' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
+            'sharding': 'contiguous batch shards, one rank per GPU, no forward collective',
+            'l2': 'working set %.2f GB per GPU per step exceeds the 126 MB L2 (no flush needed)' % (
+                B * (82944 + 82680) / 1e9),
+        })
         line = {
-            'metric': METRIC, 'value': world * B * args.steps / (ms_max * 1e-3), 'unit': UNIT,
+            'metric': METRIC, 'value': B_global * args.steps / (ms_max * 1e-3), 'unit': UNIT,
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
-            'ms_per_step': ms_max / args.steps, 'higher_is_better': True, 'scaling': 'weak',
-            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {
-                'workload': 'SMPL forward + 24-joint perspective projection, B=%d samples per GPU per step '
-                            '(BASELINE configs[3] shard size; global batch %d)' % (B, B * world),
-                'model': 'synthetic SMPL-shaped (6890 verts, 24 joints, 10 betas, <=4 LBS weights/vertex), seed 0',
-                'outputs': 'verts[B,6890,3], J_transformed[B,24,3], keypoints[B,19,3], Rs, uv, px[B,24,2]',
-                'blend_gemm': 'tcgen05 kind::f16: f16 main product + f16/bf16 residual products, fp32 accumulate (fp32-faithful, 2e-7 of the vertex scale)' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
-                'sharding': 'batch shards, one rank per GPU, no forward collective',
-                'l2': 'working set %.2f GB per step exceeds the 126 MB L2 (no flush needed)' % (
-                    B * (82944 + 82680) / 1e9),
-            },
+            'ms_per_step': ms_max / args.steps, 'higher_is_better': True, 'scaling': args.scaling,
+            'vs_baseline': None, 'dtype': DTYPE, 'data': 'synthetic', 'config': cfg,
             'clocks': sampler.summary(),
             'gpu_launches': 4 * args.steps,
-            'kernel_ms': {'pose_prep': float(kt[:, 0].mean()), 'blend_gemm': float(kt[:, 1].mean()),
-                          'skinning': skin_ms, 'keypoints': float(kt[:, 3].mean())} if len(kt) else None,
-            'roofline': {'bound': 'hbm', 'kernel': 'skin_tc_kernel (LBS: tcgen05 weight blend + apply, v_posed -> verts)',
+            'kernel_ms': {'pose_prep': float(kt[:, 0].mean()), 'blend_gemm': blend_ms,
+                          'skinning': skin_ms, 'keypoints': float(kt[:, 3].mean()),
+                          'sum_max_over_ranks': ksum_max,
+                          'source': 'CUDA events around each launch, rank 0, %s' % (
+                              'eager pass right after the graph-timed region' if graph is not None
+                              else 'inside the timed region')} if len(kt) else None,
+            'roofline': {'bound': 'hbm', 'kernel': 'skin_tc_kernel<0> (LBS: tcgen05 weight blend + apply, v_posed -> verts)',
                          'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                         'traffic': traffic, 'peak_source': peak_src,
-                         'algorithmic_bytes_per_launch': SKIN_BYTES_PER_SAMPLE * B},
+                         'traffic': tr['dram_bytes_per_launch'] if tr else None,
+                         'traffic_source': ('ncu dram__bytes_read+write, %s @ %s' % (tr['report'], tr['captured_at_commit'])) if tr
+                         else 'no ncu record for this source revision / batch',
+                         'peak_source': peak_src, 'algorithmic_bytes_per_launch': SKIN_BYTES_PER_SAMPLE * B},
+            'roofline_gemm': {'bound': 'tensor', 'kernel': 'blend_tc_kernel ([B,217] x [217,20670] as 3 kind::f16 products, M256 N256 K16, cta_group::2)',
+                              'flops_issued_per_launch': BLEND_FLOP_ISSUED * B,
+                              'achieved_tflops_issued': issued_tflops,
+                              'achieved_tflops_fp32_equivalent': BLEND_FLOP_FP32EQ * B / (blend_ms * 1e-3) / 1e12,
+                              'frac_of_bf16_burst': issued_tflops / tp['bf16_burst'],
+                              'frac_of_bf16_sustained': issued_tflops / tp['bf16_sustained'],
+                              'peaks_tflops': tp,
+                              'tensor_pipe_active_pct': gr['tensor_pipe_active_pct'] if gr else None,
+                              'tensor_pipe_source': ('ncu sm__pipe_tensor_cycles_active, %s @ %s, SM clock %.2f GHz' % (
+                                  gr['report'], gr['captured_at_commit'], gr['sm_clock_ghz'])) if gr
+                              else 'no ncu record for this source revision / batch'},
         }
         if e2e:
-            line['e2e'] = {'value': world * B * args.e2e_steps / e2e_max, 'unit': UNIT,
-                           'h2d_bytes_per_step': e2e[1], 'd2h_bytes_per_step': e2e[2],
-                           'steps': args.e2e_steps, 'note': 'smplb_forward_host, pinned host buffers, PCIe-bound'}
+            line['e2e'] = {'value': B_global * args.e2e_steps / e2e_max, 'unit': UNIT,
+                           'h2d_bytes_per_step': int(io_bytes[0]), 'd2h_bytes_per_step': int(io_bytes[1]),
+                           'steps': args.e2e_steps, 'note': 'smplb_forward_host, pinned host buffers, PCIe-bound; bytes summed over ranks'}
         if not args.no_cpu_baseline and world == 1:     # CPU baseline: rank 0 at N=1 only
             rate, cores, ns, el, _ = cpu_reference_rate(args.ref_chunk, args.cpu_seconds, 1000)
             line['cpu_baseline'] = {
@@ -703,6 +851,8 @@ def main():
                 'sample': '%d samples (%d-sample chunks, %.1f s) of the same workload; torch-CPU fp32 port of '
                           'the reference TF op sequence incl. tile(W)' % (ns, args.ref_chunk, el)}
         print(json.dumps(line), flush=True)
+    if graph is not None:
+        graph.reset()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
