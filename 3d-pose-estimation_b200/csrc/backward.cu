@@ -269,7 +269,7 @@ __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, 
 struct BwdScratch {
   float* g_A;     // [B,24,12]
   float* g_X;     // [n_slices][B,KPAD]
-  float* g_img;   // TF32 hi/lo operand image of g_vposed: [ceil(B/128)][BB_NKB][BB_GSTAGE]
+  float* g_img;   // bf16 split operand image of g_vposed (gimg16_off): [ceil(B/128)][BB_NKB][BB_ASTAGE x 16 bit]
   float* g_vtot;  // [B,NV3] g_verts + regressor^T g_kp (only touched when g_kp is given)
   size_t total;
 };
@@ -284,8 +284,8 @@ static BwdScratch carve_bwd(void* base, int B) {
   };
   const size_t b = (size_t)(B > 0 ? B : 0);
   w.g_A = take(b * NJ * 12 * 4);
-  w.g_X = take((size_t)blend_bwd_slices(B, 148) * b * KPAD * 4);
-  w.g_img = take(((b + BL_BM - 1) / BL_BM) * (size_t)BB_NKB * BB_GSTAGE * 4);
+  w.g_X = take((size_t)blend_bwd_slices(B) * b * KPAD * 4);
+  w.g_img = take(((b + BL_BM - 1) / BL_BM) * (size_t)BB_NKB * BB_ASTAGE * 2);
   w.g_vtot = take(b * NV3 * 4);
   w.total = off;
   return w;
@@ -352,12 +352,16 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
       if (rc != SMPLB_OK) return rc;
       gy = s.g_vtot;
     }
+    timing_mark_bwd(0, st);
     rc = launch_skin_bwd_gA(m, B, gy, w.vposed, s.g_A, st);                 // g_A  = sum_v w (g_y (x) [v_posed;1])
     if (rc != SMPLB_OK) return rc;
+    timing_mark_bwd(1, st);
     rc = launch_skin_bwd_vposed(m, B, gy, w.Aimg, s.g_img, st);             // g_vp = T^T g_y  (operand image)
     if (rc != SMPLB_OK) return rc;
+    timing_mark_bwd(2, st);
     rc = launch_blend_bwd(m, B, s.g_img, s.g_X, &n_slices, st);             // g_X  = g_vp . D^T
     if (rc != SMPLB_OK) return rc;
+    timing_mark_bwd(3, st);
     g_A = s.g_A;
     g_X = s.g_X;
   }
@@ -381,6 +385,7 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   p.tree = m->tree;
   joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
   SMPLB_CUDA_CHECK(cudaGetLastError());
+  if (vertex_path) timing_mark_bwd(4, st);
   return SMPLB_OK;
 }
 

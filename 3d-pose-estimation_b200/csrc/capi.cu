@@ -29,27 +29,24 @@ Workspace carve(void* base, int B, int flags, int kpv_pitch) {
   return w;
 }
 
-// ---- optional per-kernel timing (bench.py roofline): events recorded on the launching stream ----
+// ---- optional per-kernel timing (bench.py rooflines): events recorded on the launching stream ----
 struct TimingState {
-  std::vector<cudaEvent_t> ev;   // 5 events per forward call: before prep, after prep, after blend, after skin, after keypoints
+  std::vector<cudaEvent_t> ev;   // 5 events per call: 4 intervals
   int max_calls = 0;
   int ncalls = 0;
 };
-static thread_local TimingState g_timing;
+static thread_local TimingState g_timing;       // forward: prep | blend | skin | keypoints
+static thread_local TimingState g_timing_bwd;   // backward (vertex path): g_A reduction | g_vposed | transposed GEMM | joint path
 
-static inline void timing_mark(int slot, cudaStream_t st) {
-  TimingState& t = g_timing;
+static inline void timing_mark_in(TimingState& t, int slot, cudaStream_t st) {
   if (t.max_calls == 0 || t.ncalls >= t.max_calls) return;
   cudaEventRecord(t.ev[(size_t)t.ncalls * 5 + slot], st);
   if (slot == 4) ++t.ncalls;
 }
+static inline void timing_mark(int slot, cudaStream_t st) { timing_mark_in(g_timing, slot, st); }
+void timing_mark_bwd(int slot, cudaStream_t st) { timing_mark_in(g_timing_bwd, slot, st); }
 
-}  // namespace smplb
-
-using namespace smplb;
-
-extern "C" int32_t smplb_timing_begin(int32_t max_calls) {
-  TimingState& t = g_timing;
+static int32_t timing_begin_in(TimingState& t, int32_t max_calls) {
   for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
   t.ev.clear();
   t.ncalls = 0;
@@ -59,9 +56,8 @@ extern "C" int32_t smplb_timing_begin(int32_t max_calls) {
   return SMPLB_OK;
 }
 
-extern "C" int32_t smplb_timing_end(float* ms_out, int32_t* ncalls_out) {
-  TimingState& t = g_timing;
-  if (!ncalls_out) return fail(SMPLB_E_INVALID_ARG, "smplb_timing_end: null ncalls_out");
+static int32_t timing_end_in(TimingState& t, float* ms_out, int32_t* ncalls_out, const char* who) {
+  if (!ncalls_out) return fail(SMPLB_E_INVALID_ARG, std::string(who) + ": null ncalls_out");
   *ncalls_out = t.ncalls;
   for (int i = 0; i < t.ncalls && ms_out; ++i) {
     SMPLB_CUDA_CHECK(cudaEventSynchronize(t.ev[(size_t)i * 5 + 4]));
@@ -73,6 +69,23 @@ extern "C" int32_t smplb_timing_end(float* ms_out, int32_t* ncalls_out) {
   t.max_calls = 0;
   t.ncalls = 0;
   return SMPLB_OK;
+}
+
+}  // namespace smplb
+
+using namespace smplb;
+
+extern "C" int32_t smplb_timing_begin(int32_t max_calls) {
+  int32_t rc = timing_begin_in(g_timing, max_calls);
+  return rc != SMPLB_OK ? rc : timing_begin_in(g_timing_bwd, max_calls);
+}
+
+extern "C" int32_t smplb_timing_end(float* ms_out, int32_t* ncalls_out) {
+  return timing_end_in(g_timing, ms_out, ncalls_out, "smplb_timing_end");
+}
+
+extern "C" int32_t smplb_timing_bwd_end(float* ms_out, int32_t* ncalls_out) {
+  return timing_end_in(g_timing_bwd, ms_out, ncalls_out, "smplb_timing_bwd_end");
 }
 
 extern "C" size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags) {

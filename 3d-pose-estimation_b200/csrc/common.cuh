@@ -110,7 +110,7 @@ struct smplb_model {
   // backward tables
   int* ent_ptr;           // [SK_NVT][NJ+1] (vertex, weight) pairs of every (vertex tile, joint): skin_bwd.cu
   float2* ent;            // [nnz] {weight, vertex index inside the tile as int bits}
-  float* DTimg;           // [BB_NKB][BB_DSTAGE] TF32 hi/lo image of D^T (blend_bwd.cu B operand)
+  float* DTimg;           // [BB_NKB][BB_DSTAGE x 16 bit] bf16 split image of D^T (blend_bwd.cu B operand, dtimg16_off)
   // keypoint regressor (joint_regressor, batch_smpl.py:63-69), CSR by keypoint, fixed summation order
   int* kp_ptr;            // [NK+1]
   int* kp_vtx;            // [nnz] vertex id
@@ -215,18 +215,30 @@ __host__ __device__ inline size_t wimg16_off(int v, int j, int part) {
 }
 
 // ---- operand images of the transposed blend GEMM (blend_bwd.cu): g_X[b,k] = sum_n g_vposed[b,n] D[k,n] ----
-// A operand = g_vposed (rows = samples, K = the 20736 internal columns): [m_tile][k_block][hi|lo][chunk][row][4]
-// B operand = D^T      (rows = k 0..223,  K = columns)                 :         [k_block][hi|lo][chunk][row][4]
-#define BB_KB 32                                      // columns per pipeline stage
-#define BB_NKB (VPP / BB_KB)                          // 648 k-blocks of 32 columns
-#define BB_GSTAGE (2 * (BB_KB / 4) * BL_BM * 4)       // floats per A stage (8192)
-#define BB_DSTAGE (2 * (BB_KB / 4) * KPAD * 4)        // floats per B stage (14336)
-__host__ __device__ inline size_t gimg_off(int b, int n, int hl) {
-  return (size_t)(b / BL_BM) * ((size_t)BB_NKB * BB_GSTAGE) + (size_t)(n / BB_KB) * BB_GSTAGE +
-         (size_t)(((hl * (BB_KB / 4) + (n % BB_KB) / 4) * BL_BM + (b % BL_BM)) * 4 + (n & 3));
+// 16-bit split operands like the forward GEMMs, but bf16 parts (gradient magnitudes, ~1/(B*20670) for a mean loss,
+// leave the fp16 range; tcgen05 kind::f16 needs both operands of one MMA in the same format -- probed,
+// profiles/r02_mma_probe.txt):   g.D ~= g1.D1 + g2.D1 + g1.D2,   x1 = bf16(x), x2 = bf16(x - x1)   (error ~2^-16)
+// A operand = g_vposed, rows = samples, K = the 20736 internal columns, stored MN-MAJOR: 8 consecutive samples of one
+//   column are 16 contiguous bytes, which is what a thread of skin_tc_kernel<1> holds (thread = vertex, 8 samples) --
+//   it writes the image straight from registers, no transposition through shared memory:
+//   [m_tile of 128 samples][k_block of 64 columns][part 2][sample group m/8: 16][column group k/8: 8][k%8][m%8]
+// B operand = D^T, rows = k 0..223 split in two halves of 112 (one per CTA of the pair), K-major:
+//   [k_block][half 2][part 2][column group: 8][row group r/8: 14][r%8][k%8]
+#define BB_KB 64                                      // internal columns per pipeline stage (4 K16 steps)
+#define BB_NKB (VPP / BB_KB)                          // 324 k-blocks
+#define BB_APART (BL_BM * BB_KB)                      // 16-bit elements per part of an A stage (16 KB)
+#define BB_ASTAGE (2 * BB_APART)                      // elements per A stage: [g1 | g2] (32 KB)
+#define BB_NH (KPAD / 2)                              // 112 rows of D^T per CTA of the pair
+#define BB_DPART (BB_NH * BB_KB)                      // elements per part of a D^T half stage (14 KB)
+#define BB_DSTAGE (2 * 2 * BB_DPART)                  // elements per k-block: [half][D1 | D2] (56 KB)
+__host__ __device__ inline size_t gimg16_off(int b, int n, int part) {
+  return ((size_t)(b / BL_BM) * BB_NKB + (size_t)(n / BB_KB)) * BB_ASTAGE + (size_t)part * BB_APART +
+         (size_t)(((b % BL_BM) / 8) * (BB_KB / 8) + (n % BB_KB) / 8) * 64 + (size_t)((n & 7) * 8 + (b & 7));
 }
-__host__ __device__ inline size_t dtimg_off(int k, int n, int hl) {
-  return (size_t)(n / BB_KB) * BB_DSTAGE + (size_t)(((hl * (BB_KB / 4) + (n % BB_KB) / 4) * KPAD + k) * 4 + (n & 3));
+__host__ __device__ inline size_t dtimg16_off(int k, int n, int part) {
+  const int half = k / BB_NH, r = k % BB_NH;
+  return ((size_t)((n / BB_KB) * 2 + half) * 2 + (size_t)part) * BB_DPART +
+         (size_t)(((n % BB_KB) / 8) * (BB_NH / 8) + r / 8) * 64 + (size_t)((r & 7) * 8 + (n & 7));
 }
 
 // Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated fp32-faithfully from 16-bit operands:
@@ -280,7 +292,8 @@ int32_t launch_gverts_total(const smplb_model* m, int B, const float* g_verts, c
                             cudaStream_t st);
 // g_X partial sums: [n_slices][B][KPAD]; returns the slice count through *n_slices
 int32_t launch_blend_bwd(const smplb_model* m, int B, const float* g_img, float* g_X, int* n_slices, cudaStream_t st);
-int blend_bwd_slices(int B, int n_sm);
+int blend_bwd_slices(int B);
+void timing_mark_bwd(int slot, cudaStream_t st);   // capi.cu: backward per-kernel event hooks (no-op unless enabled)
 int32_t launch_keypoints(const smplb_model* m, int B, const float* verts, float* kp, cudaStream_t st);
 int32_t launch_keypoints_compact(const smplb_model* m, int B, const float* kpv, float* kp, cudaStream_t st);
 

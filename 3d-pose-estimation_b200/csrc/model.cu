@@ -190,13 +190,14 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
     }
     eptr[(size_t)t * (NJ + 1) + NJ] = (int)ents.size();
   }
-  std::vector<float> DTimg((size_t)BB_NKB * BB_DSTAGE, 0.f);
+  std::vector<float> DTimg((size_t)BB_NKB * BB_DSTAGE / 2, 0.f);   // rows 217..223 stay zero
+  unsigned short* dt16 = reinterpret_cast<unsigned short*>(DTimg.data());
   for (int k = 0; k < KDIM; ++k)
     for (int n = 0; n < VPP; ++n) {
       const float x = D32[(size_t)k * VPP + n];
-      const float hi = tf32_rna_host(x);
-      DTimg[dtimg_off(k, n, 0)] = hi;
-      DTimg[dtimg_off(k, n, 1)] = tf32_rna_host(x - hi);
+      const unsigned short h = bf16_rne_bits(x);
+      dt16[dtimg16_off(k, n, 0)] = h;
+      dt16[dtimg16_off(k, n, 1)] = bf16_rne_bits(x - bf16_bits_to_float(h));
     }
 
   // ---- keypoint regressor CSR by keypoint (batch_smpl.py:63-69, :134-138) ----

@@ -44,9 +44,9 @@ struct SktSmem {
 
 // MODE 0: forward (above).  MODE 1: adjoint wrt v_posed, g_vposed[b,v] = T[b,v][:3,:3]^T g_verts[b,v]: same
 // weight-blend MMA; the epilogue reads g_verts straight from global (stride-3 loads, fetched ONE GROUP AHEAD so
-// the DRAM latency hides behind the previous group), stages the result in smem and writes it as the TF32 hi/lo
-// A-operand image of the transposed blend GEMM (blend_bwd.cu) in 256-byte runs; `vposed` = g_verts [B,6890,3],
-// `verts` = that image.
+// the DRAM latency hides behind the previous group) and writes the result from registers as the bf16 split
+// MN-major A-operand image of the transposed blend GEMM (blend_bwd.cu; 16-byte stores, 512 contiguous bytes per
+// warp); `vposed` = g_verts [B,6890,3], `verts` = that image.
 template <int MODE>
 __global__ void __launch_bounds__(SKT_THREADS, 1)
 skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vposed,
@@ -195,6 +195,7 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           if (g + 1 < g1) load_gy(g + 1, gyn);
           mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);
           tc_fence_after();
+          float res[3][SK_S / 2];   // g_vposed of this vertex: [component][sample of this warp's half]
 #pragma unroll
           for (int bt = 0; bt < SK_S / 8; ++bt) {
             uint32_t r0[16], r1[16], r2[16];
@@ -213,44 +214,41 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
             for (int k = 0; k < 4; ++k) {
               const float* t = T + 12 * k;
               const float* gg = gy[bt * 4 + k];
-              float* orow = sm.out[half * (SK_S / 2) + bt * 4 + k] + l4;     // internal column order: c * 128 + vertex
 #pragma unroll
               for (int c = 0; c < 3; ++c)
-                orow[c * SK_VT] = fmaf(t[c], gg[0], fmaf(t[4 + c], gg[1], t[8 + c] * gg[2]));   // (T.R^T gy)[c]
+                res[c][bt * 4 + k] = fmaf(t[c], gg[0], fmaf(t[4 + c], gg[1], t[8 + c] * gg[2]));   // (T.R^T gy)[c]
             }
           }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&sm.acc_empty[ac]);
-          named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging complete
-          // copy-out as the TF32 hi/lo operand image of the transposed blend GEMM (gimg_off): for every k-block of
-          // 32 columns and 16-byte K-chunk the group's 16 samples are 256 contiguous bytes, so a warp stores two
-          // full 256-byte runs per instruction (v1 scattered 4-byte stores: 5.7 ms, now bound by the 16 GB it moves)
+          // Straight from registers into the A-operand image of the transposed blend GEMM (gimg16_off, MN-major): the 8
+          // samples of this thread are one sample group of the image, i.e. 16 contiguous bytes per (column, part); the 32
+          // lanes of a warp (consecutive vertices = consecutive columns of one component) cover 512 contiguous bytes.
+          // bf16 split: g1 = bf16(g), g2 = bf16(g - g1).  (Round 1 staged a TF32 hi/lo image through shared memory:
+          // twice the bytes, two block barriers per group.)
           {
-            const int et = (int)threadIdx.x - 64;
-            const int i = et & 15;                                   // sample row of the group
-            const int b = g * SK_S + i;
-            float* gbase = verts + (size_t)(b / BL_BM) * ((size_t)BB_NKB * BB_GSTAGE) + (size_t)(b % BL_BM) * 4;
-            if (b < B) {
+            const int b0 = g * SK_S + half * (SK_S / 2);          // first sample of this thread's group (multiple of 8)
+            if (b0 < B) {
+              unsigned short* img = reinterpret_cast<unsigned short*>(verts);
 #pragma unroll
-              for (int p = 0; p < (3 * SK_VT / 4) / 16; ++p) {       // 96 four-column chunks / 16 per pass
-                const int ch = (et >> 4) + 16 * p;                   // chunk index inside the tile: 0..95
-                const int nl = ch * 4;                               // local column
-                const float2 v01 = *reinterpret_cast<const float2*>(&sm.out[i][nl]);
-                const float2 v23 = *reinterpret_cast<const float2*>(&sm.out[i][nl + 2]);
-                float4 hi, lo;
-                hi.x = tf32_rna_dev(v01.x); lo.x = tf32_rna_dev(v01.x - hi.x);
-                hi.y = tf32_rna_dev(v01.y); lo.y = tf32_rna_dev(v01.y - hi.y);
-                hi.z = tf32_rna_dev(v23.x); lo.z = tf32_rna_dev(v23.x - hi.z);
-                hi.w = tf32_rna_dev(v23.y); lo.w = tf32_rna_dev(v23.y - hi.w);
-                const int n = vt * (3 * SK_VT) + nl;                 // global internal column
-                float* dst = gbase + (size_t)(n / BB_KB) * BB_GSTAGE + (size_t)((n % BB_KB) / 4) * (BL_BM * 4);
-                __stcs(reinterpret_cast<float4*>(dst), hi);
-                __stcs(reinterpret_cast<float4*>(dst + (BB_KB / 4) * BL_BM * 4), lo);
+              for (int c = 0; c < 3; ++c) {
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int k2 = 0; k2 < 4; ++k2) {
+                  const float x0 = res[c][2 * k2], x1 = res[c][2 * k2 + 1];
+                  const uint32_t h0 = bf16_rne_bits(x0), h1 = bf16_rne_bits(x1);
+                  hi[k2] = h0 | (h1 << 16);
+                  lo[k2] = (uint32_t)bf16_rne_bits(x0 - __uint_as_float(h0 << 16)) |
+                           ((uint32_t)bf16_rne_bits(x1 - __uint_as_float(h1 << 16)) << 16);
+                }
+                const int n = vt * (3 * SK_VT) + c * SK_VT + l4;   // internal column
+                unsigned short* dst = img + gimg16_off(b0, n, 0);
+                __stcs(reinterpret_cast<uint4*>(dst), make_uint4(hi[0], hi[1], hi[2], hi[3]));
+                __stcs(reinterpret_cast<uint4*>(dst + BB_APART), make_uint4(lo[0], lo[1], lo[2], lo[3]));
               }
             }
           }
-          named_bar_sync(1, 32 * SKT_EPI_WARPS);   // staging reusable
           continue;
         }
         mbar_wait(&sm.vfull[sv], (it / SKT_VSTAGES) & 1);   // v_posed rows of this group have landed
@@ -362,7 +360,7 @@ int32_t launch_skin_tc(const smplb_model* m, int B, const float* vposed, const f
   return launch_skin_tc_mode<0>(m, B, vposed, Aimg, verts, kpv, st);
 }
 
-// g_verts [B,6890,3] -> TF32 hi/lo operand image of g_vposed (see gimg_off)
+// g_verts [B,6890,3] -> bf16 split operand image of g_vposed (gimg16_off)
 int32_t launch_skin_bwd_vposed(const smplb_model* m, int B, const float* g_verts, const float* Aimg, float* g_img,
                                cudaStream_t st) {
   return launch_skin_tc_mode<1>(m, B, g_verts, Aimg, g_img, nullptr, st);

@@ -95,6 +95,14 @@ __host__ __device__ constexpr uint32_t umma_idesc(int fmt, int M, int N) {
   return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(N >> 3) << 17) |
          ((uint32_t)(M >> 4) << 24);
 }
+// General form: separate operand formats (kind::f16 still wants afmt == bfmt: a mixed f16 x bf16 MMA raises an
+// illegal-instruction fault, profiles/r02_mma_probe.txt) and major-ness (0 = K-major, 1 = MN-major: a core matrix is
+// then 8 K-rows of 16 bytes = 8 consecutive M/N elements; same descriptor fields, LBO = K-group stride, SBO = M/N-group
+// stride -- verified on hardware by tools/mma_probe.cu T3/T4).
+__host__ __device__ constexpr uint32_t umma_idesc_ex(int afmt, int bfmt, int a_mn_major, int b_mn_major, int M, int N) {
+  return (1u << 4) | ((uint32_t)afmt << 7) | ((uint32_t)bfmt << 10) | ((uint32_t)a_mn_major << 15) |
+         ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 // D[tmem] (+)= A[smem] * B[smem]^T ; one thread issues for the CTA.
 __device__ __forceinline__ void umma_tf32_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                              uint32_t accumulate) {

@@ -115,6 +115,7 @@ SYMBOLS = {
                                    C.c_int32, C.c_void_p, C.c_void_p]),
     'smplb_timing_begin': (C.c_int32, [C.c_int32]),
     'smplb_timing_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
+    'smplb_timing_bwd_end': (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
     'smplb_adam_tick': (C.c_int32, [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     'smplb_adam_step_dev': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_float, C.c_float, C.c_float, C.c_void_p]),

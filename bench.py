@@ -312,8 +312,7 @@ def run_sweep(args, rank, local_rank, world, dist):
     tp = tensor_peaks()
     rows = []
     Bs = [1 << i for i in range(0, 17)]
-    if args.batch != 65536:
-        Bs = [b for b in Bs if b <= args.batch]
+    Bs = [b for b in Bs if args.sweep_min <= b <= args.batch]
     for Bg in Bs:
         if args.scaling == 'strong':
             b0, b1 = sd.shard_range(Bg, rank, world)
@@ -345,20 +344,23 @@ def run_sweep(args, rank, local_rank, world, dist):
                 dist.barrier()
             kt = None
             ms_local = 0.0
+            kb = None
             if B > 0:
-                if name == 'fwd':
-                    L.smplb_timing_begin(steps)
+                L.smplb_timing_begin(steps)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 for _ in range(steps):
                     fn()
                 e1.record()
                 torch.cuda.synchronize()
+                kms = (C.c_float * (4 * steps))()
+                nc = C.c_int32(0)
+                L.smplb_timing_end(kms, C.byref(nc))
                 if name == 'fwd':
-                    kms = (C.c_float * (4 * steps))()
-                    nc = C.c_int32(0)
-                    L.smplb_timing_end(kms, C.byref(nc))
                     kt = np.array(list(kms), dtype=np.float64).reshape(-1, 4)[:nc.value].mean(axis=0)
+                L.smplb_timing_bwd_end(kms, C.byref(nc))
+                if name == 'fwd_bwd' and nc.value:
+                    kb = np.array(list(kms), dtype=np.float64).reshape(-1, 4)[:nc.value].mean(axis=0)
                 ms_local = e0.elapsed_time(e1) / steps
             t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
             if dist is not None:
@@ -371,6 +373,17 @@ def run_sweep(args, rank, local_rank, world, dist):
                 res['skin_hbm_frac'] = SKIN_BYTES_PER_SAMPLE * B / (kt[2] * 1e-3) / 1e9 / peak
                 res['blend_frac_of_bf16_burst_issued'] = BLEND_FLOP_ISSUED * B / (kt[1] * 1e-3) / 1e12 / tp['bf16_burst']
                 res['blend_tflops_fp32_equivalent'] = BLEND_FLOP_FP32EQ * B / (kt[1] * 1e-3) / 1e12
+            if kb is not None and rank == 0:
+                # per-kernel algorithmic bytes per sample: g_A reduction reads g_verts + v_posed; the skinning adjoint
+                # reads g_verts and writes the bf16 split g_vposed image (4 B per element); the GEMM reads that image
+                res['kernel_ms_bwd_rank0'] = {'skin_bwd_gA': kb[0], 'skin_tc<1> g_vposed': kb[1], 'blend_bwd_gemm': kb[2],
+                                              'joint_bwd': kb[3]}
+                res['roofline_bwd'] = {
+                    'skin_bwd_gA': {'bytes_per_sample': 82680 + 82944, 'hbm_frac': (82680 + 82944) * B / (kb[0] * 1e-3) / 1e9 / peak},
+                    'skin_tc<1>': {'bytes_per_sample': 82680 + 82944, 'hbm_frac': (82680 + 82944) * B / (kb[1] * 1e-3) / 1e9 / peak},
+                    'blend_bwd_gemm': {'bytes_per_sample': 82944, 'hbm_frac': 82944 * B / (kb[2] * 1e-3) / 1e9 / peak,
+                                       'tflops_issued': BLEND_FLOP_ISSUED * B / (kb[2] * 1e-3) / 1e12,
+                                       'frac_of_bf16_burst': BLEND_FLOP_ISSUED * B / (kb[2] * 1e-3) / 1e12 / tp['bf16_burst']}}
         # backward roofline: SURVEY 8d algorithmic bytes of the vertex path (read g_verts + v_posed, write g_vposed)
         if 'fwd_bwd_ms' in res and 'fwd_ms' in res:
             bwd = max(res['fwd_bwd_ms'] - res['fwd_ms'], 1e-9)
@@ -639,6 +652,7 @@ def main():
     ap.add_argument('--cpu-seconds', type=float, default=12.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--sweep-min', type=int, default=1, help='sweep mode: smallest batch of the sweep')
     ap.add_argument('--mode', default='forward', choices=['forward', 'fit', 'sweep', 'raster', 'normals'],
                     help="forward: the headline metric; fit: BASELINE config 3 (fitting steps on the 2D re-projection loss)")
     ap.add_argument('--loss', choices=['reproj', 'mesh'], default='reproj', help='fit mode: which loss drives the step')

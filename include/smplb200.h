@@ -316,6 +316,9 @@ int32_t smplb_mse_grad(int64_t n, const float* pred, const float* target, float 
  * milliseconds. */
 int32_t smplb_timing_begin(int32_t max_calls);
 int32_t smplb_timing_end(float* ms_out_host, int32_t* ncalls_out_host);
+/* The same for smplb_backward calls with vertex gradients made since smplb_timing_begin:
+ * ms_out[call][4] = {g_A reduction, g_vposed (skinning adjoint), transposed blend GEMM, joint path}. */
+int32_t smplb_timing_bwd_end(float* ms_out_host, int32_t* ncalls_out_host);
 
 #ifdef __cplusplus
 }
