@@ -24,19 +24,25 @@ namespace smplb {
 using namespace tc;
 
 constexpr int SKT_EPI_WARPS = 8;
-constexpr int SKT_THREADS = 64 + 32 * SKT_EPI_WARPS;   // producer warp + MMA warp + epilogue warps
+constexpr int SKT_THREADS = 96 + 32 * SKT_EPI_WARPS;   // row-producer warp + MMA warp + epilogue warps + operand-producer warp
 constexpr int SKT_TMEM_COLS = 512;
 constexpr int SKT_ASTAGES = 2;   // A-image ring (released by the MMA)
 constexpr int SKT_VSTAGES = 5;   // v_posed ring (released by the epilogue): HBM prefetch depth
 constexpr uint32_t SKT_VP_ROW_BYTES = 3 * SK_VT * 4;   // 1536
 constexpr int SKT_OUT_PITCH = 3 * SK_VT + 2;
+constexpr int SKT_GY_PITCH = 3 * SK_VT + 4;   // MODE 1: g_verts row of a tile + 16 bytes (rows of odd samples are 8 bytes off a 16-byte boundary)
 
 struct SktSmem {
   float w[SK_WTILE];                          // 16 384 B  W tile image (2 parts)
   float a[SKT_ASTAGES][SK_AGRP];              // 24 576 B  per stage: A group image (2 parts)
-  float vp[SKT_VSTAGES][SK_S][3 * SK_VT];     // 24 576 B  per stage: v_posed tile rows of the group
-  float out[SK_S][SKT_OUT_PITCH];             // 24 704 B  verts staging (AoS); pitch 386: the keypoint-vertex
-                                              //           copy reads 16 samples x 2 slots per warp conflict-free
+  union {
+    struct {
+      float vp[SKT_VSTAGES][SK_S][3 * SK_VT];   // 24 576 B  per stage: v_posed tile rows of the group
+      float out[SK_S][SKT_OUT_PITCH];           // 24 704 B  verts staging (AoS); pitch 386: the keypoint-vertex
+                                                //           copy reads 16 samples x 2 slots per warp conflict-free
+    };
+    float gy[SKT_VSTAGES][SK_S][SKT_GY_PITCH];  // MODE 1: 24 832 B per stage: g_verts tile rows of the group
+  };
   uint64_t afull[SKT_ASTAGES], aempty[SKT_ASTAGES], vfull[SKT_VSTAGES], vempty[SKT_VSTAGES];
   uint64_t acc_full[2], acc_empty[2], w_full, w_empty;
   uint32_t tmem_base;
@@ -52,7 +58,7 @@ __global__ void __launch_bounds__(SKT_THREADS, 1)
 skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vposed,
                const float* __restrict__ Aimg, const float* __restrict__ Wimg, float* __restrict__ verts,
                float* __restrict__ kpv, int kpv_pitch, const int* __restrict__ kpc_tile_ptr,
-               const int* __restrict__ kpc_src) {
+               const int* __restrict__ kpc_src, int gy_ring) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SktSmem& sm = *reinterpret_cast<SktSmem*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -82,7 +88,42 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
   const uint32_t tmem = sm.tmem_base;
 
   if (warp == 0) {
-    // ================= producer =================
+    // ================= row producer: the 16 tile rows of every sample group, one bulk copy per lane =================
+    // (one thread issuing the 16 copies and their addresses was the bottleneck of the MODE 1 kernel: ~2500 cycles per group)
+    uint32_t itv = 0;   // ring counter (MODE 1: units of the last tile do not use the ring)
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+      const int vt = u % SK_NVT, ch = u / SK_NVT;
+      const int g0 = (int)((long long)ch * n_groups / n_chunks), g1 = (int)((long long)(ch + 1) * n_groups / n_chunks);
+      if (MODE == 1 && !(gy_ring && vt != SK_NVT - 1)) continue;
+      for (int g = g0; g < g1; ++g, ++itv) {
+        const int sv = itv % SKT_VSTAGES;
+        const int ns = min(SK_S, B - g * SK_S);
+        if (lane == 0) mbar_wait(&sm.vempty[sv], ((itv / SKT_VSTAGES) & 1) ^ 1);
+        __syncwarp();
+        if (MODE == 0) {
+          if (lane == 0) mbar_arrive_expect_tx(&sm.vfull[sv], ns * SKT_VP_ROW_BYTES);
+          __syncwarp();
+          if (lane < ns)
+            bulk_g2s(sm.vp[sv][lane], vposed + ((size_t)g * SK_S + lane) * VPP + (size_t)vt * (3 * SK_VT), SKT_VP_ROW_BYTES,
+                     &sm.vfull[sv]);
+        } else {
+          // g_verts rows [B][20670] are only 8-byte aligned (82 680 = 16 * 5167 + 8): a row segment that starts 8 bytes
+          // off a 16-byte boundary is copied from 8 bytes earlier (valid memory: the previous tile or sample) and the
+          // epilogue skips those two floats.  The last tile (1272 bytes per row, not a multiple of 16) is read with
+          // plain loads instead.
+          const char* r = reinterpret_cast<const char*>(vposed + ((size_t)g * SK_S + (lane < ns ? lane : 0)) * NV3 +
+                                                        (size_t)vt * (3 * SK_VT));
+          const uint32_t mis = (uint32_t)((uintptr_t)r & 15u);   // 0 or 8
+          const uint32_t n_mis = __popc(__ballot_sync(0xffffffffu, lane < ns && mis != 0));
+          if (lane == 0) mbar_arrive_expect_tx(&sm.vfull[sv], ns * SKT_VP_ROW_BYTES + 16 * n_mis);
+          __syncwarp();
+          if (lane < ns) bulk_g2s(sm.gy[sv][lane], r - mis, SKT_VP_ROW_BYTES + 2 * mis, &sm.vfull[sv]);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2 + SKT_EPI_WARPS) {
+    // ================= operand producer: W tile per unit, A group image per sample group (2-stage ring) =================
     if (lane == 0) {
       uint32_t it = 0, ul = 0;
       for (int u = blockIdx.x; u < n_units; u += gridDim.x, ++ul) {
@@ -92,14 +133,7 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
         mbar_arrive_expect_tx(&sm.w_full, SK_WTILE * 4);
         bulk_g2s(sm.w, Wimg + (size_t)vt * SK_WTILE, SK_WTILE * 4, &sm.w_full);
         for (int g = g0; g < g1; ++g, ++it) {
-          const int sv = it % SKT_VSTAGES, sa = it % SKT_ASTAGES;
-          const int ns = min(SK_S, B - g * SK_S);
-          if (MODE == 0) {
-            mbar_wait(&sm.vempty[sv], ((it / SKT_VSTAGES) & 1) ^ 1);
-            mbar_arrive_expect_tx(&sm.vfull[sv], ns * SKT_VP_ROW_BYTES);
-            const float* src = vposed + (size_t)g * SK_S * VPP + (size_t)vt * (3 * SK_VT);
-            for (int i = 0; i < ns; ++i) bulk_g2s(sm.vp[sv][i], src + (size_t)i * VPP, SKT_VP_ROW_BYTES, &sm.vfull[sv]);
-          }
+          const int sa = it % SKT_ASTAGES;
           mbar_wait(&sm.aempty[sa], ((it / SKT_ASTAGES) & 1) ^ 1);
           mbar_arrive_expect_tx(&sm.afull[sa], SK_AGRP * 4);
           bulk_g2s(sm.a[sa], Aimg + (size_t)g * SK_AGRP, SK_AGRP * 4, &sm.afull[sa]);
@@ -149,7 +183,13 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
     const int half = (warp - 2) >> 2;             // samples [8*half, 8*half+8) of the group
     const int l4 = q * 32 + lane;                 // TMEM lane = vertex within the tile
     const int ew = warp - 2;                      // 0..7: copy-out rows 2*ew, 2*ew+1
-    uint32_t it = 0;
+    uint32_t it = 0, itv = 0;                     // itv: MODE 1 g_verts ring counter (units of the last tile skip the ring)
+    // MODE 1: float offset of this thread's vertex inside the staged rows of even / odd samples (a row starts
+    // 0 or 2 floats into its 16-byte unit: NV3 = 2 (mod 4), groups start at even samples)
+    const int gy_sh0 = (int)(((uintptr_t)vposed >> 2) & 3);
+    const int gy_off0 = gy_sh0 + 3 * l4, gy_off1 = ((gy_sh0 + 2) & 3) + 3 * l4;
+    // MODE 1: 16-bit-element offset of this thread's column inside the g_vposed image (gimg16_off without the sample terms)
+    const size_t img_col = (size_t)(l4 >> 6) * BB_ASTAGE + (size_t)(((l4 & 63) >> 3) * 64 + (l4 & 7) * 8);
     for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
       const int vt = u % SK_NVT, ch = u / SK_NVT;
       const int g0 = (int)((long long)ch * n_groups / n_chunks), g1 = (int)((long long)(ch + 1) * n_groups / n_chunks);
@@ -167,7 +207,6 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           if (sl < ks1) ksrc[p] = __ldg(kpc_src + sl);
         }
       }
-      float gyn[SK_S / 2][3];   // MODE 1: next group's g_verts (prefetch)
       for (int g = g0; g < g1; ++g, ++it) {
         const int sv = it % SKT_VSTAGES, ac = it & 1;
         const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)ac * SK_N + half * (SK_S / 2) * 12;
@@ -175,25 +214,16 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           // ---- adjoint wrt v_posed ----
           const int v = vt * SK_VT + l4;
           const bool vok = v < NV;
-          // g_verts of this thread's vertex for its 8 samples: fetched one group ahead (gyn), so the DRAM latency
-          // hides behind the previous group's work instead of stalling the first use
-          auto load_gy = [&](int gg, float (&dst)[SK_S / 2][3]) {
-#pragma unroll
-            for (int k = 0; k < SK_S / 2; ++k) {
-              const int b = gg * SK_S + half * (SK_S / 2) + k;
-              const float* src = vposed + (size_t)(b < B ? b : B - 1) * NV3 + 3 * (size_t)(vok ? v : 0);
-#pragma unroll
-              for (int r = 0; r < 3; ++r) dst[k][r] = vok ? __ldg(src + r) : 0.f;
-            }
-          };
-          float gy[SK_S / 2][3];
-          if (g == g0) load_gy(g, gyn);
-#pragma unroll
-          for (int k = 0; k < SK_S / 2; ++k)
-#pragma unroll
-            for (int r = 0; r < 3; ++r) gy[k][r] = gyn[k][r];
-          if (g + 1 < g1) load_gy(g + 1, gyn);
-          mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);
+          // g_verts of this thread's vertex: from the bulk-copy ring (5 groups of prefetch; stride-3 smem reads are
+          // conflict-free), or with plain loads for the last tile / an unaligned buffer (1/54 of the work)
+          const bool ring = gy_ring && vt != SK_NVT - 1;
+          int sr = 0;
+          if (ring) {
+            sr = itv % SKT_VSTAGES;
+            mbar_wait_spin(smem_u32(&sm.vfull[sr]), (itv / SKT_VSTAGES) & 1);
+            ++itv;
+          }
+          mbar_wait_spin(smem_u32(&sm.acc_full[ac]), (it >> 1) & 1);
           tc_fence_after();
           float res[3][SK_S / 2];   // g_vposed of this vertex: [component][sample of this warp's half]
 #pragma unroll
@@ -202,22 +232,39 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
             tmem_ld16(tbase + bt * 48, r0);
             tmem_ld16(tbase + bt * 48 + 16, r1);
             tmem_ld16(tbase + bt * 48 + 32, r2);
-            tmem_ld_wait();
-            float T[48];
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              T[e] = __uint_as_float(r0[e]);
-              T[16 + e] = __uint_as_float(r1[e]);
-              T[32 + e] = __uint_as_float(r2[e]);
-            }
+            float gy[4][3];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const float* t = T + 12 * k;
-              const float* gg = gy[bt * 4 + k];
+              const int i = half * (SK_S / 2) + bt * 4 + k;
+              const int b = g * SK_S + i;
+              if (ring) {
+                const float* row = sm.gy[sr][i] + ((k & 1) ? gy_off1 : gy_off0);
+#pragma unroll
+                for (int r = 0; r < 3; ++r) gy[k][r] = row[r];
+              } else {
+                const float* src = vposed + (size_t)(b < B ? b : B - 1) * NV3 + 3 * (size_t)(vok ? v : 0);
+#pragma unroll
+                for (int r = 0; r < 3; ++r) gy[k][r] = vok ? __ldg(src + r) : 0.f;
+              }
+            }
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              // rows of T for sample k: r0 = T[0..15], r1 = T[16..31], r2 = T[32..47]; sample k uses T[12k .. 12k+11]
+              float t[12];
+#pragma unroll
+              for (int e = 0; e < 12; ++e) {
+                const int idx = 12 * k + e;
+                t[e] = __uint_as_float(idx < 16 ? r0[idx & 15] : (idx < 32 ? r1[idx & 15] : r2[idx & 15]));
+              }
 #pragma unroll
               for (int c = 0; c < 3; ++c)
-                res[c][bt * 4 + k] = fmaf(t[c], gg[0], fmaf(t[4 + c], gg[1], t[8 + c] * gg[2]));   // (T.R^T gy)[c]
+                res[c][bt * 4 + k] = fmaf(t[c], gy[k][0], fmaf(t[4 + c], gy[k][1], t[8 + c] * gy[k][2]));   // (T.R^T gy)[c]
             }
+          }
+          if (ring) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.vempty[sr]);
           }
           tc_fence_before();
           __syncwarp();
@@ -230,20 +277,20 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           {
             const int b0 = g * SK_S + half * (SK_S / 2);          // first sample of this thread's group (multiple of 8)
             if (b0 < B) {
-              unsigned short* img = reinterpret_cast<unsigned short*>(verts);
+              // gimg16_off(b0, vt * 384 + c * 128 + l4, part): the component moves two k-blocks, the part BB_APART
+              unsigned short* img = reinterpret_cast<unsigned short*>(verts) +
+                                    ((size_t)(b0 / BL_BM) * BB_NKB + (size_t)vt * 6) * BB_ASTAGE +
+                                    (size_t)((b0 % BL_BM) / 8) * ((BB_KB / 8) * 64) + img_col;
 #pragma unroll
               for (int c = 0; c < 3; ++c) {
                 uint32_t hi[4], lo[4];
 #pragma unroll
-                for (int k2 = 0; k2 < 4; ++k2) {
+                for (int k2 = 0; k2 < 4; ++k2) {   // one cvt.rn.bf16x2.f32 per pair and part
                   const float x0 = res[c][2 * k2], x1 = res[c][2 * k2 + 1];
-                  const uint32_t h0 = bf16_rne_bits(x0), h1 = bf16_rne_bits(x1);
-                  hi[k2] = h0 | (h1 << 16);
-                  lo[k2] = (uint32_t)bf16_rne_bits(x0 - __uint_as_float(h0 << 16)) |
-                           ((uint32_t)bf16_rne_bits(x1 - __uint_as_float(h1 << 16)) << 16);
+                  hi[k2] = pack_bf16x2(x0, x1);
+                  lo[k2] = pack_bf16x2(x0 - __uint_as_float(hi[k2] << 16), x1 - __uint_as_float(hi[k2] & 0xffff0000u));
                 }
-                const int n = vt * (3 * SK_VT) + c * SK_VT + l4;   // internal column
-                unsigned short* dst = img + gimg16_off(b0, n, 0);
+                unsigned short* dst = img + (size_t)c * (2 * BB_ASTAGE);
                 __stcs(reinterpret_cast<uint4*>(dst), make_uint4(hi[0], hi[1], hi[2], hi[3]));
                 __stcs(reinterpret_cast<uint4*>(dst + BB_APART), make_uint4(lo[0], lo[1], lo[2], lo[3]));
               }
@@ -251,8 +298,8 @@ skin_tc_kernel(int B, int n_groups, int n_chunks, const float* __restrict__ vpos
           }
           continue;
         }
-        mbar_wait(&sm.vfull[sv], (it / SKT_VSTAGES) & 1);   // v_posed rows of this group have landed
-        mbar_wait(&sm.acc_full[ac], (it >> 1) & 1);         // blended transforms are in TMEM
+        mbar_wait_spin(smem_u32(&sm.vfull[sv]), (it / SKT_VSTAGES) & 1);   // v_posed rows of this group have landed
+        mbar_wait_spin(smem_u32(&sm.acc_full[ac]), (it >> 1) & 1);         // blended transforms are in TMEM
         tc_fence_after();
 #pragma unroll
         for (int bt = 0; bt < SK_S / 8; ++bt) {
@@ -348,8 +395,11 @@ static int32_t launch_skin_tc_mode(const smplb_model* m, int B, const float* in,
   if (n_chunks > n_groups) n_chunks = n_groups;
   const int n_units = SK_NVT * n_chunks;
   const int grid = n_units < n_sm ? n_units : n_sm;
+  // MODE 1: g_verts rows go through the bulk-copy ring when the buffer is 8-byte aligned (any contiguous fp32
+  // [B,6890,3] tensor whose base is; a view that starts at an odd float falls back to plain loads)
+  const int gy_ring = (MODE == 1 && (((uintptr_t)in) & 7u) == 0) ? 1 : 0;
   skin_tc_kernel<MODE><<<grid, SKT_THREADS, smem, st>>>(B, n_groups, n_chunks, in, Aimg, m->Wimg, out, kpv, m->kpv_pitch,
-                                                        m->kpc_tile_ptr, m->kpc_src);
+                                                        m->kpc_tile_ptr, m->kpc_src, gy_ring);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
