@@ -25,6 +25,10 @@ Workspace carve(void* base, int B, int flags, int kpv_pitch) {
   w.verts = (skin && (flags & SMPLB_F_SCRATCH_VERTS)) ? take(b * NV3 * sizeof(float)) : nullptr;
   w.bwd = (flags & SMPLB_F_KEEP_VPOSED) ? take(backward_scratch_bytes(B)) : nullptr;
   w.kpv = (skin && kpv_pitch > 0) ? take(((b + SK_S - 1) / SK_S) * SK_S * (size_t)kpv_pitch * sizeof(float)) : nullptr;
+  const bool fused = skin && (flags & SMPLB_F_FUSED);
+  const size_t n_ch = (b + FF_CH - 1) / FF_CH;
+  w.Ximg2 = fused ? take(n_ch * 2 * FF_XHALF * 2) : nullptr;
+  w.Aimg2 = fused ? take(n_ch * FF_NG * 2 * FF_AGH * 2) : nullptr;
   w.total = off;
   return w;
 }
@@ -106,6 +110,8 @@ static int32_t check_forward(const smplb_model* m, const smplb_forward_io* io, v
   if (io->kp && !io->verts && (flags & SMPLB_F_SKIN_SIMT) && !(flags & SMPLB_F_SCRATCH_VERTS))
     return fail(SMPLB_E_INVALID_ARG,
                 "smplb_forward: keypoints without a verts buffer need SMPLB_F_SCRATCH_VERTS on the SIMT skinning path");
+  if ((flags & SMPLB_F_FUSED) && (flags & (SMPLB_F_KEEP_VPOSED | SMPLB_F_BLEND_SIMT | SMPLB_F_SKIN_SIMT)))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_forward: SMPLB_F_FUSED excludes KEEP_VPOSED / BLEND_SIMT / SKIN_SIMT");
   if (!ws) return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace is required");
   if (ws_bytes < smplb_workspace_bytes(m, io->B, flags))
     return fail(SMPLB_E_INVALID_ARG, "smplb_forward: workspace too small (see smplb_workspace_bytes)");
@@ -128,11 +134,14 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.theta = io->theta;
   p.Jbar = m->Jbar;
   p.JS = m->JS;
-  p.Ximg = skin ? w.Ximg : nullptr;
+  const bool fused = skin && (flags & SMPLB_F_FUSED);
+  p.Ximg = (skin && !fused) ? w.Ximg : nullptr;
+  p.Ximg2 = fused ? w.Ximg2 : nullptr;
+  p.Aimg2 = fused ? w.Aimg2 : nullptr;
   p.joints = io->joints ? io->joints : w.joints;
   p.Rs = io->Rs;
   p.A = io->A ? io->A : w.A;
-  p.Aimg = skin ? w.Aimg : nullptr;
+  p.Aimg = (skin && !fused) ? w.Aimg : nullptr;
   p.cam_pos = io->cam_pos;
   p.cam_rot = io->cam_rot;
   p.focal = io->focal;
@@ -151,6 +160,16 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
     return SMPLB_OK;
   }
 
+  if (fused) {
+    // one kernel: v_posed = [beta|phi].D + v_template lives in TMEM and meets T = W.A there (fused_fwd.cu)
+    timing_mark(2, st);   // the "blend" interval is empty on this path: everything is counted as skinning
+    rc = launch_fused_fwd(m, B, w.Ximg2, w.Aimg2, io->verts, io->kp ? w.kpv : nullptr, st);
+    if (rc != SMPLB_OK) return rc;
+    timing_mark(3, st);
+    if (io->kp) rc = launch_keypoints_compact(m, B, w.kpv, io->kp, st);
+    timing_mark(4, st);
+    return rc;
+  }
   if (flags & SMPLB_F_BLEND_SIMT)
     rc = launch_blend_simt(m, B, w.Ximg, w.vposed, st);
   else

@@ -123,6 +123,11 @@ struct smplb_model {
   int* kpc_tile_ptr;      // [SK_NVT+1] first compact slot of every vertex tile
   int* kpc_src;           // [kpv_pitch] float index 3*lv+c inside the tile's staged verts row, -1 = pad
   int* kpc_slot;          // [nnz] compact slot of the vertex of every regressor entry
+  // fused forward (fused_fwd.cu)
+  float* Dimg2;           // [FF_NHT][FF_DTILE x 16 bit] D rows of every half tile, f16 split (ff_dimg_off)
+  float* Wimg2;           // [FF_NHT][FF_WHT x 16 bit] LBS weights, f16 split (ff_wimg_off)
+  float* vt_plain;        // [NV3] v_template in the reference order 3v+c
+  int* kpc_slot_of;       // [NV3] compact keypoint slot of (vertex, component), -1 = not a keypoint vertex
 };
 
 #define NM_BIG_ORDER 16
@@ -154,6 +159,8 @@ struct PrepParams {
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
   float* Aimg;    // [ceil(B/20)][SK_AGRP] f16/bf16 operand image of A for the skinning GEMM (aimg16_off), nullable
+  float* Ximg2;   // fused forward: [ceil(B/128)][2][FF_XHALF] f16 split image of [beta | pose feature] (ff_ximg_off), nullable
+  float* Aimg2;   // fused forward: [ceil(B/128)][16][2][FF_AGH] f16 split image of A (ff_aimg_off), nullable
   const float* cam_pos;
   const float* cam_rot;
   const float* focal;
@@ -173,6 +180,8 @@ struct Workspace {
   float* joints;   // scratch J_transformed when the caller passes none
   float* bwd;      // backward scratch (backward.cu)
   float* kpv;      // compact keypoint-vertex rows [B][kpv_pitch] (last: earlier offsets do not depend on it)
+  float* Ximg2;    // fused forward operand images (SMPLB_F_FUSED)
+  float* Aimg2;
   size_t total;
 };
 Workspace carve(void* base, int B, int flags, int kpv_pitch = 0);
@@ -279,6 +288,54 @@ __host__ __device__ inline float bf16_bits_to_float(unsigned short h) {
 // fp32 <-> fp16 bits, round to nearest even (subnormals included)
 __host__ __device__ inline unsigned short f16_rne_bits(float x) { return __half_as_ushort(__float2half_rn(x)); }
 __host__ __device__ inline float f16_bits_to_float(unsigned short h) { return __half2float(__ushort_as_half(h)); }
+// ---- operand images of the FUSED forward (fused_fwd.cu): blend GEMM + weight blend + skinning in one kernel ----
+// D-stationary, transposed: a CTA pair (cta_group::2, M = 128) owns one 128-vertex tile, 64 vertices per CTA, and keeps
+// the rows of D = [shapedirs; posedirs] of its vertices resident in shared memory for all three components; samples
+// stream through in chunks of 128 (64 per CTA: in pair mode the B operand is split between the CTAs).  With M = 128 the
+// TMEM of each CTA holds rows = its 64 vertices in lanes 0..63 for the first half of the N columns and again in lanes
+// 64..127 for the second half (profiles/r02_mma_probe.txt), so v_posed[vertex, sample] (N = 128 samples) and the blended
+// transforms T[vertex, (sample, 3x4)] (N = 96: 8 samples) meet in the same lane when the 8 samples of a T group are 4
+// of the first and 4 of the second half of the chunk.  All operands f16 main part + f16 residual (X.D ~= Xh.Dh + Xl.Dh
+// + Xh.Dl; the residual of D, ~2^-12 |D|, is a subnormal fp16 number with absolute error <= 2^-25: ~2^-18 |D|).
+// All images K-major, no swizzle: element (row, k) at (k/8) * rows*8 + (row/8)*64 + (row%8)*8 + k%8   (16-bit units)
+#define FF_VH 64                          // vertices per CTA
+#define FF_NHT (2 * SK_NVT)               // 108 half tiles
+#define FF_CH 128                         // samples per chunk (N of the blend MMAs)
+#define FF_SH 64                          // samples per CTA of the pair
+#define FF_NKS (KPAD / 16)                // 14 K16 steps
+#define FF_DPART (FF_VH * KPAD)           // elements per (component, part) block of a half tile (28 672 B)
+#define FF_DTILE (6 * FF_DPART)           // per half tile: [component 3][part 2]   (172 032 B)
+#define FF_XPART (FF_SH * 16)             // elements per part of a (chunk, half, k-step) slab (2 048 B)
+#define FF_XKS (2 * FF_XPART)             // per (chunk, half, k-step): [Xh | Xl]   (4 096 B)
+#define FF_XHALF (FF_NKS * FF_XKS)        // per (chunk, half)
+#define FF_G 8                            // samples per T group: 4 of each half of the chunk
+#define FF_NG (FF_CH / FF_G)              // 16 groups per chunk
+#define FF_AROWS 48                       // rows (4 samples x 12) per (group, half)
+#define FF_APART (FF_AROWS * SK_KPAD)     // elements per part (3 072 B)
+#define FF_AGH (2 * FF_APART)             // per (chunk, group, half): [Ah | Al]   (6 144 B)
+#define FF_WPART (FF_VH * SK_KPAD)        // elements per part of a half tile of W (4 096 B)
+#define FF_WHT (2 * FF_WPART)             // per half tile: [Wh | Wl]   (8 192 B)
+__host__ __device__ inline size_t ff_kmajor(int rows, int row, int k) {
+  return (size_t)(k / 8) * (rows * 8) + (size_t)(row / 8) * 64 + (size_t)((row & 7) * 8 + (k & 7));
+}
+__host__ __device__ inline size_t ff_dimg_off(int v, int c, int k, int part) {
+  return (size_t)(v / FF_VH) * FF_DTILE + (size_t)(c * 2 + part) * FF_DPART + ff_kmajor(FF_VH, v % FF_VH, k);
+}
+__host__ __device__ inline size_t ff_wimg_off(int v, int j, int part) {
+  return (size_t)(v / FF_VH) * FF_WHT + (size_t)part * FF_WPART + ff_kmajor(FF_VH, v % FF_VH, j);
+}
+__host__ __device__ inline size_t ff_ximg_off(int b, int k, int part) {
+  const int ch = b / FF_CH, h = (b % FF_CH) / FF_SH, s = b % FF_SH;
+  return ((size_t)(ch * 2 + h) * FF_NKS + (size_t)(k / 16)) * FF_XKS + (size_t)part * FF_XPART + ff_kmajor(FF_SH, s, k % 16);
+}
+__host__ __device__ inline size_t ff_aimg_off(int b, int j, int e, int part) {
+  const int ch = b / FF_CH, h = (b % FF_CH) / FF_SH, s = b % FF_SH;
+  return ((size_t)(ch * FF_NG + s / 4) * 2 + (size_t)h) * FF_AGH + (size_t)part * FF_APART +
+         ff_kmajor(FF_AROWS, (s % 4) * 12 + e, j);
+}
+int32_t launch_fused_fwd(const smplb_model* m, int B, const float* Ximg2, const float* Aimg2, float* verts, float* kpv,
+                         cudaStream_t st);
+
 int32_t launch_skin_simt(const smplb_model* m, int B, const float* vposed, const float* A, float* verts,
                          cudaStream_t st);
 // verts and kpv are each nullable (kpv: compact keypoint-vertex rows, see smplb_model)

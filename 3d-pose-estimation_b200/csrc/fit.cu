@@ -149,6 +149,8 @@ extern "C" int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, 
   p.Jbar = m->Jbar;
   p.JS = m->JS;
   p.Ximg = nullptr;
+  p.Ximg2 = nullptr;
+  p.Aimg2 = nullptr;
   p.joints = nullptr;
   p.Rs = nullptr;
   p.A = nullptr;

@@ -1,0 +1,410 @@
+// FUSED forward (north_star item 4; batch_smpl.py:91-95, :113-115, :120-132): blend-shape GEMM + weight blend + skinning
+// in ONE kernel -- v_posed never reaches HBM.
+//     v_posed[b,v,c] = v_template[v,c] + sum_k [beta|phi][b,k] D[k,(v,c)]          (tcgen05, accumulator in TMEM)
+//     T[b,v]         = sum_j weights[v,j] A[b,j]                                     (tcgen05, accumulator in TMEM)
+//     verts[b,v]     = T[b,v][:3,:3] v_posed[b,v] + T[b,v][:3,3]                     (epilogue, thread = vertex)
+// The unfused pair (blend_tc_kernel -> skin_tc_kernel<0>) moves v_posed through HBM once each way (10.9 GB at
+// B = 65536) and stays as the graded LBS kernel; this kernel writes only verts.
+//
+// Layout (operand images and the TMEM lane argument: common.cuh "FUSED forward"):
+//   * D-STATIONARY, transposed GEMM: a CTA pair (cluster of 2, cta_group::2, M = 128) owns a 128-vertex tile, 64
+//     vertices per CTA; each CTA keeps the D rows of its vertices resident in shared memory for x, y, z (3 x 2 parts x
+//     28 KB = 168 KB).  N = 128 samples per blend MMA (the A operand is re-read from shared memory by every MMA at
+//     <= 128 B/clk -- profiles/r02_mma_probe.txt -- so N must be large: 32 cycles per M128 N128 K16 MMA).
+//   * per 128-sample chunk: 14 K16 steps x 3 components x 3 split products = 126 blend MMAs into three 64-column
+//     accumulators (double buffered), then 16 groups of 8 samples: 6 MMAs (M128 N96 K16) for T into a 48-column
+//     accumulator (double buffered); the blend MMAs of the NEXT chunk are interleaved with the T groups of this one.
+//   * TMEM lane = vertex for both accumulators (lanes 64..127 repeat the vertices for the second half of the columns;
+//     a T group is 4 samples of each chunk half, so v_posed and T of a sample sit in the same lane).
+//   warp 0      X producer: one 4 KB bulk copy per K16 step (4-stage ring)
+//   warp 1      leader CTA: MMA issue; peer CTA: relays "my stage landed" to the leader's barriers
+//   warp 2      A-image producer (6 KB per group, 3-stage ring); D / W tile loads when the vertex tile changes
+//   warps 3-10  epilogue: tcgen05.ld T and v_posed (thread = vertex, 2 samples per warp and group), apply, transpose
+//               96 floats through smem, coalesced 384-byte row stores; keypoint vertices also go to the compact rows
+// Schedule: 54 clusters own one vertex tile each and sweep the first m chunks in step (X / A images are then shared
+// through L2); the other 20 clusters split the remaining chunks of all tiles.
+#include "tc_common.cuh"
+
+namespace smplb {
+
+using namespace tc;
+
+constexpr int FF_XST = 4;
+constexpr int FF_AST = 3;
+constexpr int FF_EPI_WARPS = 8;
+constexpr int FF_THREADS = 96 + 32 * FF_EPI_WARPS;
+constexpr uint32_t FF_D_BYTES = FF_DTILE * 2;   // 172 032
+constexpr uint32_t FF_W_BYTES = FF_WHT * 2;     // 8 192
+constexpr uint32_t FF_X_BYTES = FF_XKS * 2;     // 4 096
+constexpr uint32_t FF_A_BYTES = FF_AGH * 2;     // 6 144
+constexpr uint32_t FF_ACC_B = 192;              // TMEM columns of one blend accumulator set (3 components x 64)
+constexpr uint32_t FF_TCOL0 = 384;              // first column of the T accumulators
+constexpr uint32_t FF_ACC_T = 48;               // TMEM columns of one T accumulator (N = 96 over two lane halves)
+
+struct FfSmem {
+  unsigned char d[FF_D_BYTES];
+  unsigned char w[FF_W_BYTES];
+  unsigned char x[FF_XST][FF_X_BYTES];
+  unsigned char a[FF_AST][FF_A_BYTES];
+  float out[FF_EPI_WARPS][2][96];                 // per epilogue warp: 2 samples x 32 vertices x 3
+  uint64_t dfull, peer_dfull, dempty;
+  uint64_t xfull[FF_XST], peer_xfull[FF_XST], xempty[FF_XST];
+  uint64_t afull[FF_AST], peer_afull[FF_AST], aempty[FF_AST];
+  uint64_t bfull[2], bempty[2], tfull[2], tempty[2];
+  uint32_t tmem_base;
+};
+
+struct FfSched {
+  int n_ch;      // chunks of 128 samples
+  int n_main;    // clusters that own one vertex tile each (0 or 54)
+  int m_main;    // chunks [0, m_main) of every tile go to its main cluster
+  int n_cl;      // clusters launched
+};
+__device__ __forceinline__ int ff_n_items(const FfSched& s, int cl) {
+  if (cl < s.n_main) return s.m_main;
+  const long long t = cl - s.n_main, Tn = s.n_cl - s.n_main, L = (long long)SK_NVT * (s.n_ch - s.m_main);
+  return (int)((t + 1) * L / Tn - t * L / Tn);
+}
+__device__ __forceinline__ void ff_item(const FfSched& s, int cl, int idx, int& vt, int& ch) {
+  if (cl < s.n_main) {
+    vt = cl;
+    ch = idx;
+    return;
+  }
+  const long long t = cl - s.n_main, Tn = s.n_cl - s.n_main, tw = s.n_ch - s.m_main, L = (long long)SK_NVT * tw;
+  const long long I = t * L / Tn + idx;
+  vt = (int)(I / tw);
+  ch = s.m_main + (int)(I % tw);
+}
+
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld2(uint32_t taddr, uint32_t (&r)[2]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FF_THREADS, 1)
+fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2, const unsigned short* __restrict__ Aimg2,
+                 const unsigned short* __restrict__ Dimg2, const unsigned short* __restrict__ Wimg2,
+                 const float* __restrict__ vt_plain, float* __restrict__ verts, float* __restrict__ kpv, int kpv_pitch,
+                 const int* __restrict__ kpc_slot_of) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  FfSmem& sm = *reinterpret_cast<FfSmem*>(smem_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rk = cluster_ctarank();
+  const int cl = blockIdx.x >> 1;
+  const int n_items = ff_n_items(sched, cl);
+
+  if (threadIdx.x == 0) {
+    mbar_init(&sm.dfull, 1);
+    mbar_init(&sm.peer_dfull, 1);
+    mbar_init(&sm.dempty, 1);
+    for (int s = 0; s < FF_XST; ++s) {
+      mbar_init(&sm.xfull[s], 1);
+      mbar_init(&sm.peer_xfull[s], 1);
+      mbar_init(&sm.xempty[s], 1);
+    }
+    for (int s = 0; s < FF_AST; ++s) {
+      mbar_init(&sm.afull[s], 1);
+      mbar_init(&sm.peer_afull[s], 1);
+      mbar_init(&sm.aempty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&sm.bfull[s], 1);
+      mbar_init(&sm.bempty[s], 2 * FF_EPI_WARPS);   // epilogue warps of both CTAs
+      mbar_init(&sm.tfull[s], 1);
+      mbar_init(&sm.tempty[s], 2 * FF_EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc_pair(&sm.tmem_base, 512);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+
+  if (warp == 0) {
+    // ================= X producer (both CTAs: the 64 samples of this CTA's chunk half) =================
+    if (lane == 0) {
+      uint32_t xit = 0;
+      for (int il = 0; il < n_items; ++il) {
+        int vt, ch;
+        ff_item(sched, cl, il, vt, ch);
+        const unsigned short* src = Ximg2 + (size_t)(ch * 2 + (int)rk) * FF_XHALF;
+        for (int ks = 0; ks < FF_NKS; ++ks, ++xit) {
+          const int s = xit % FF_XST;
+          mbar_wait(&sm.xempty[s], ((xit / FF_XST) & 1) ^ 1);
+          mbar_arrive_expect_tx(&sm.xfull[s], FF_X_BYTES);
+          bulk_g2s(sm.x[s], src + (size_t)ks * FF_XKS, FF_X_BYTES, &sm.xfull[s]);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    // ================= A-image producer; D / W loads at a tile change (both CTAs) =================
+    uint32_t ait = 0, dk = 0;
+    int cur_vt = -1;
+    for (int il = 0; il < n_items; ++il) {
+      int vt, ch;
+      ff_item(sched, cl, il, vt, ch);
+      if (vt != cur_vt) {
+        cur_vt = vt;
+        const int ht = vt * 2 + (int)rk;
+        if (lane == 0) {
+          if (dk > 0) mbar_wait(&sm.dempty, (dk - 1) & 1);   // every MMA that read the old tile has completed
+          mbar_arrive_expect_tx(&sm.dfull, FF_D_BYTES + FF_W_BYTES);
+        }
+        __syncwarp();
+        if (lane < 6)
+          bulk_g2s(sm.d + (size_t)lane * (FF_DPART * 2), Dimg2 + (size_t)ht * FF_DTILE + (size_t)lane * FF_DPART,
+                   FF_DPART * 2, &sm.dfull);
+        else if (lane == 6)
+          bulk_g2s(sm.w, Wimg2 + (size_t)ht * FF_WHT, FF_W_BYTES, &sm.dfull);
+        ++dk;
+      }
+      if (lane == 0) {
+        const unsigned short* src = Aimg2 + ((size_t)ch * FF_NG * 2 + rk) * FF_AGH;
+        for (int g = 0; g < FF_NG; ++g, ++ait) {
+          const int s = ait % FF_AST;
+          mbar_wait(&sm.aempty[s], ((ait / FF_AST) & 1) ^ 1);
+          mbar_arrive_expect_tx(&sm.afull[s], FF_A_BYTES);
+          bulk_g2s(sm.a[s], src + (size_t)g * 2 * FF_AGH, FF_A_BYTES, &sm.afull[s]);
+        }
+      } else {
+        ait += FF_NG;
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ================= MMA issue (leader) / stage relay (peer): the same walk over the rings =================
+    // Whole warp runs the loops (uniform control flow); one elected lane issues the tcgen05 / arrive ops.
+    const uint32_t issue = elect_one() ? 1u : 0u;
+    const bool leader = rk == 0;
+    constexpr uint32_t idesc_b = umma_idesc(0, 128, FF_CH);        // kind::f16, f16 operands, M 128 (pair), N 128
+    constexpr uint32_t idesc_t = umma_idesc(0, 128, 2 * FF_AROWS);  // N 96
+    const uint64_t d_t = umma_desc_kmajor_noswz(0, FF_VH * 16, 128);      // D and W: 64 rows per CTA
+    const uint64_t x_t = umma_desc_kmajor_noswz(0, FF_SH * 16, 128);      // X: 64 rows per CTA
+    const uint64_t a_t = umma_desc_kmajor_noswz(0, FF_AROWS * 16, 128);   // A image: 48 rows per CTA
+    const uint32_t db = smem_u32(sm.d) >> 4, wb = smem_u32(sm.w) >> 4, xb = smem_u32(sm.x[0]) >> 4, ab = smem_u32(sm.a[0]) >> 4;
+    uint32_t xit = 0, ait = 0, tg = 0, dk = 0;
+
+    auto stage_wait = [&](uint64_t* full, uint64_t* peer_full, uint32_t ph) {
+      mbar_wait_spin(smem_u32(full), ph);
+      if (leader) mbar_wait_spin(smem_u32(peer_full), ph);
+      else if (issue) mbar_arrive_remote(peer_full, 0);
+    };
+    auto blend_kstep = [&](uint32_t bb, int ks) {
+      const uint32_t s = xit % FF_XST;
+      stage_wait(&sm.xfull[s], &sm.peer_xfull[s], (xit / FF_XST) & 1);
+      ++xit;
+      if (!leader) return;
+      tc_fence_after();
+      const uint64_t xh = x_t + (uint64_t)(xb + s * (FF_X_BYTES / 16)), xl = xh + (uint64_t)(FF_XPART * 2 / 16);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const uint32_t dcol = tmem + bb * FF_ACC_B + (uint32_t)c * (FF_CH / 2);
+        const uint64_t dh = d_t + (uint64_t)(db + (uint32_t)(c * 2) * (FF_DPART * 2 / 16) + (uint32_t)ks * (2 * FF_VH * 16 / 16));
+        const uint64_t dl = dh + (uint64_t)(FF_DPART * 2 / 16);
+        umma_f16_ss_pair(dcol, dh, xh, idesc_b, ks != 0 ? 1u : 0u, issue);   // Dh.Xh
+        umma_f16_ss_pair(dcol, dh, xl, idesc_b, 1u, issue);                  // Dh.Xl
+        umma_f16_ss_pair(dcol, dl, xh, idesc_b, 1u, issue);                  // Dl.Xh
+      }
+      umma_commit_pair(smem_u32(&sm.xempty[s]), 3, issue);
+      if (ks == FF_NKS - 1) umma_commit_pair(smem_u32(&sm.bfull[bb]), 3, issue);
+    };
+    auto t_group = [&]() {
+      const uint32_t tb = tg & 1;
+      if (leader) mbar_wait_spin(smem_u32(&sm.tempty[tb]), ((tg >> 1) & 1) ^ 1);
+      const uint32_t s = ait % FF_AST;
+      stage_wait(&sm.afull[s], &sm.peer_afull[s], (ait / FF_AST) & 1);
+      ++ait;
+      if (leader) {
+        tc_fence_after();
+        const uint32_t tcol = tmem + FF_TCOL0 + tb * FF_ACC_T;
+#pragma unroll
+        for (int ks = 0; ks < SK_KPAD / 16; ++ks) {
+          const uint64_t wh = d_t + (uint64_t)(wb + (uint32_t)ks * (2 * FF_VH * 16 / 16)), wl = wh + (uint64_t)(FF_WPART * 2 / 16);
+          const uint64_t ah = a_t + (uint64_t)(ab + s * (FF_A_BYTES / 16) + (uint32_t)ks * (2 * FF_AROWS * 16 / 16));
+          const uint64_t al = ah + (uint64_t)(FF_APART * 2 / 16);
+          umma_f16_ss_pair(tcol, wh, ah, idesc_t, ks != 0 ? 1u : 0u, issue);   // Wh.Ah
+          umma_f16_ss_pair(tcol, wl, ah, idesc_t, 1u, issue);                  // Wl.Ah
+          umma_f16_ss_pair(tcol, wh, al, idesc_t, 1u, issue);                  // Wh.Al
+        }
+        umma_commit_pair(smem_u32(&sm.aempty[s]), 3, issue);
+        umma_commit_pair(smem_u32(&sm.tfull[tb]), 3, issue);
+      }
+      ++tg;
+    };
+
+    int cur_vt = -1;
+    bool pre = false;   // the blend MMAs of the current item were already issued (interleaved with the previous item)
+    for (int il = 0; il < n_items; ++il) {
+      int vt, ch;
+      ff_item(sched, cl, il, vt, ch);
+      if (vt != cur_vt) {
+        if (cur_vt >= 0 && leader) umma_commit_pair(smem_u32(&sm.dempty), 3, issue);   // old tile no longer read
+        stage_wait(&sm.dfull, &sm.peer_dfull, dk & 1);
+        ++dk;
+        cur_vt = vt;
+        pre = false;
+      }
+      const uint32_t bb = (uint32_t)il & 1;
+      if (!pre) {
+        if (leader) mbar_wait_spin(smem_u32(&sm.bempty[bb]), (((uint32_t)il >> 1) & 1) ^ 1);
+        for (int ks = 0; ks < FF_NKS; ++ks) blend_kstep(bb, ks);
+      }
+      bool can_pre = false;
+      if (il + 1 < n_items) {
+        int vt2, ch2;
+        ff_item(sched, cl, il + 1, vt2, ch2);
+        can_pre = vt2 == vt;
+      }
+      if (can_pre && leader) mbar_wait_spin(smem_u32(&sm.bempty[bb ^ 1]), ((((uint32_t)il + 1) >> 1) & 1) ^ 1);
+      for (int g = 0; g < FF_NG; ++g) {
+        t_group();
+        if (can_pre && g < FF_NKS) blend_kstep(bb ^ 1, g);
+      }
+      pre = can_pre;
+    }
+    __syncwarp();
+  } else {
+    // ================= epilogue (warps 3..10, both CTAs) =================
+    const int ew = warp - 3;
+    const int q = warp & 3;              // TMEM lane quarter this warp may read
+    const int sub = ew >> 2;             // which 2 of the 4 samples of a (group, chunk half)
+    const int hl = q >> 1;               // chunk half held by this lane quarter
+    const int r = (q & 1) * 32 + lane;   // vertex inside the CTA's 64
+    const uint32_t lsel = (uint32_t)(q * 32) << 16;
+    float* stage = &sm.out[ew][0][0];
+    uint32_t tg = 0;
+    for (int il = 0; il < n_items; ++il) {
+      int vt, ch;
+      ff_item(sched, cl, il, vt, ch);
+      const int v = vt * SK_VT + (int)rk * FF_VH + r;
+      const bool vok = v < NV;
+      float tv[3] = {0.f, 0.f, 0.f};
+      int slot[3] = {-1, -1, -1};
+      if (vok) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          tv[c] = __ldg(vt_plain + 3 * v + c);
+          if (kpv) slot[c] = __ldg(kpc_slot_of + 3 * v + c);
+        }
+      }
+      const int v0 = vt * SK_VT + (int)rk * FF_VH + (q & 1) * 32;   // first vertex of this warp
+      const int nvf = 3 * max(0, min(32, NV - v0));                 // floats of the warp's 96 that exist
+      const uint32_t bb = (uint32_t)il & 1;
+      mbar_wait_spin(smem_u32(&sm.bfull[bb]), ((uint32_t)il >> 1) & 1);
+      tc_fence_after();
+      for (int g = 0; g < FF_NG; ++g, ++tg) {
+        const uint32_t tb = tg & 1;
+        mbar_wait_spin(smem_u32(&sm.tfull[tb]), (tg >> 1) & 1);
+        tc_fence_after();
+        // T of this thread's two samples: columns [24 sub, 24 sub + 24) of the 48 of this lane half
+        uint32_t t16[16], t8[8], px[2], py[2], pz[2];
+        const uint32_t tbase = tmem + lsel + FF_TCOL0 + tb * FF_ACC_T + (uint32_t)sub * 24;
+        if (sub == 0) {
+          tmem_ld16(tbase, t16);        // T[0..15]
+          tmem_ld8(tbase + 16, t8);     // T[16..23]
+        } else {
+          tmem_ld8(tbase, t8);          // T[0..7]
+          tmem_ld16(tbase + 8, t16);    // T[8..23]
+        }
+        const uint32_t pbase = tmem + lsel + bb * FF_ACC_B + (uint32_t)(4 * g + 2 * sub);
+        tmem_ld2(pbase, px);
+        tmem_ld2(pbase + FF_CH / 2, py);
+        tmem_ld2(pbase + 2 * (FF_CH / 2), pz);
+        tmem_ld_wait();
+        float T[24];
+#pragma unroll
+        for (int e = 0; e < 24; ++e) {
+          if (sub == 0) T[e] = __uint_as_float(e < 16 ? t16[e & 15] : t8[e & 7]);
+          else T[e] = __uint_as_float(e < 8 ? t8[e & 7] : t16[(e - 8) & 15]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_remote(&sm.tempty[tb], 0);
+        float y[2][3];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const float x0 = __uint_as_float(px[i]) + tv[0], x1 = __uint_as_float(py[i]) + tv[1], x2 = __uint_as_float(pz[i]) + tv[2];
+          const float* t = T + 12 * i;
+#pragma unroll
+          for (int rr = 0; rr < 3; ++rr)
+            y[i][rr] = fmaf(t[4 * rr], x0, fmaf(t[4 * rr + 1], x1, fmaf(t[4 * rr + 2], x2, t[4 * rr + 3])));
+        }
+        // transpose through smem: thread = vertex wrote 3 floats, rows leave as 384 contiguous bytes per sample
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int c = 0; c < 3; ++c) stage[i * 96 + 3 * lane + c] = y[i][c];
+        __syncwarp();
+        const int b0 = ch * FF_CH + hl * FF_SH + 4 * g + 2 * sub;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int b = b0 + i;
+          if (b < B) {
+            if (verts) {
+              float* dst = verts + (size_t)b * NV3 + (size_t)v0 * 3;
+#pragma unroll
+              for (int k = 0; k < 3; ++k)
+                if (lane + 32 * k < nvf) __stcs(dst + lane + 32 * k, stage[i * 96 + lane + 32 * k]);
+            }
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+              if (slot[c] >= 0) kpv[((size_t)(b / SK_S) * kpv_pitch + slot[c]) * SK_S + (b % SK_S)] = y[i][c];
+          }
+        }
+        __syncwarp();
+      }
+      // every TMEM read of this blend accumulator set has completed (the last group's tcgen05.wait::ld)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(&sm.bempty[bb], 0);
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem, 512);
+  }
+}
+
+int32_t launch_fused_fwd(const smplb_model* m, int B, const float* Ximg2, const float* Aimg2, float* verts, float* kpv,
+                         cudaStream_t st) {
+  if (B <= 0 || (!verts && !kpv)) return SMPLB_OK;
+  static KernelSetup setup;
+  const size_t smem = sizeof(FfSmem);
+  int n_sm = 0;
+  if (int32_t rc = setup.ensure(m->device, fused_fwd_kernel, smem, &n_sm)) return rc;
+  FfSched s;
+  s.n_ch = (B + FF_CH - 1) / FF_CH;
+  const int G = n_sm / 2;
+  const long long total = (long long)SK_NVT * s.n_ch;
+  if (G > SK_NVT && s.n_ch >= 8) {
+    // 54 clusters own a vertex tile each and sweep chunks [0, m) in step; the other G - 54 share the rest
+    s.n_main = SK_NVT;
+    s.m_main = (int)(total / G);
+    s.n_cl = G;
+    if (s.m_main >= s.n_ch) { s.n_main = 0; s.m_main = 0; }
+  } else {
+    s.n_main = 0;
+    s.m_main = 0;
+    s.n_cl = (int)(total < G ? total : G);
+  }
+  fused_fwd_kernel<<<2 * s.n_cl, FF_THREADS, smem, st>>>(B, s, reinterpret_cast<const unsigned short*>(Ximg2),
+                                                        reinterpret_cast<const unsigned short*>(Aimg2),
+                                                        reinterpret_cast<const unsigned short*>(m->Dimg2),
+                                                        reinterpret_cast<const unsigned short*>(m->Wimg2), m->vt_plain, verts,
+                                                        kpv, m->kpv_pitch, m->kpc_slot_of);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}
+
+}  // namespace smplb

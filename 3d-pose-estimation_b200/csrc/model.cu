@@ -232,6 +232,33 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   if (csrc.empty()) csrc.assign(8, -1);
   for (size_t e = 0; e < kvtx.size(); ++e) cslot[e] = cslot_of_v[kvtx[e]];
 
+  // ---- fused forward images (fused_fwd.cu): D rows and LBS weights per 64-vertex half tile, f16 main + f16 residual ----
+  std::vector<float> Dimg2((size_t)FF_NHT * FF_DTILE / 2, 0.f), Wimg2((size_t)FF_NHT * FF_WHT / 2, 0.f);
+  {
+    unsigned short* d2 = reinterpret_cast<unsigned short*>(Dimg2.data());
+    unsigned short* w2 = reinterpret_cast<unsigned short*>(Wimg2.data());
+    for (int v = 0; v < NV; ++v) {
+      for (int c = 0; c < 3; ++c)
+        for (int k = 0; k < KDIM; ++k) {
+          const float x = k < NB ? shapedirs[(size_t)k * NV3 + 3 * v + c] : posedirs[(size_t)(k - NB) * NV3 + 3 * v + c];
+          const unsigned short h = f16_rne_bits(x);
+          d2[ff_dimg_off(v, c, k, 0)] = h;
+          d2[ff_dimg_off(v, c, k, 1)] = f16_rne_bits(x - f16_bits_to_float(h));
+        }
+      for (int j = 0; j < NJ; ++j) {
+        const float x = weights[(size_t)v * NJ + j];
+        const unsigned short h = f16_rne_bits(x);
+        w2[ff_wimg_off(v, j, 0)] = h;
+        w2[ff_wimg_off(v, j, 1)] = f16_rne_bits(x - f16_bits_to_float(h));
+      }
+    }
+  }
+  std::vector<float> vt_plain(v_template, v_template + NV3);
+  std::vector<int> cslot_of(NV3, -1);   // (vertex, component) -> compact keypoint slot
+  for (int t = 0; t < SK_NVT; ++t)
+    for (int sl = ctile[t]; sl < ctile[t + 1]; ++sl)
+      if (csrc[sl] >= 0) cslot_of[(size_t)t * (3 * SK_VT) + csrc[sl]] = sl;
+
   int prev = 0;
   cudaGetDevice(&prev);
   SMPLB_CUDA_CHECK(cudaSetDevice(device));
@@ -264,6 +291,10 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->kpc_tile_ptr, ctile));
   chk(upload(&m->kpc_src, csrc));
   chk(upload(&m->kpc_slot, cslot));
+  chk(upload(&m->Dimg2, Dimg2));
+  chk(upload(&m->Wimg2, Wimg2));
+  chk(upload(&m->vt_plain, vt_plain));
+  chk(upload(&m->kpc_slot_of, cslot_of));
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
     smplb_model_destroy(m);
@@ -295,6 +326,10 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->kpc_tile_ptr);
   cudaFree(m->kpc_src);
   cudaFree(m->kpc_slot);
+  cudaFree(m->Dimg2);
+  cudaFree(m->Wimg2);
+  cudaFree(m->vt_plain);
+  cudaFree(m->kpc_slot_of);
   cudaSetDevice(prev);
   delete m;
   return SMPLB_OK;

@@ -62,6 +62,29 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       x16[ximg16_off(b, k, 2)] = bf16_rne_bits(v);
     }
   }
+  if (p.Ximg2) {
+    // operand image of the fused forward (ff_ximg_off): [Xh | Xl] per K16 step, sample-major inside the chunk half
+    float* x = xs[warp];
+    if (!p.Ximg) {
+      if (lane < NB) x[lane] = beta[lane];
+      if (lane < KPAD - KDIM) x[KDIM + lane] = 0.f;
+      if (act && lane >= 1) {
+        float* f = x + NB + (lane - 1) * 9;
+#pragma unroll
+        for (int e = 0; e < 9; ++e) f[e] = R[e] - ((e == 0 || e == 4 || e == 8) ? 1.0f : 0.0f);
+      }
+      __syncwarp();
+    }
+    unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg2);
+#pragma unroll
+    for (int i = 0; i < KPAD / 32; ++i) {
+      const int k = lane + 32 * i;
+      const float v = x[k];
+      const unsigned short h = f16_rne_bits(v);
+      x16[ff_ximg_off(b, k, 0)] = h;
+      x16[ff_ximg_off(b, k, 1)] = f16_rne_bits(v - f16_bits_to_float(h));
+    }
+  }
 
   // kinematic chain: G = (GR, Gt).  Root: (R_0, J_0).  Level d: G_i = G_parent * [R_i | J_i - J_parent]
   float GR[9], Gt[3];
@@ -93,6 +116,12 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
     }
   }
 
+  if (!act && p.Aimg2) {
+    // pad joints 24..31 of the fused forward's A image: one 16-byte unit per (part, component)
+    unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg2);
+    for (int u = lane - NJ; u < 24; u += 32 - NJ)
+      *reinterpret_cast<uint4*>(a16 + ff_aimg_off(b, NJ, u % 12, u / 12)) = make_uint4(0u, 0u, 0u, 0u);
+  }
   if (!act && p.Aimg) {
     // joints 24..31 of the padded K: the W columns are zero, these must be finite -> zero (workspace is not cleared).
     // Per (part, component e) the 8 pad joints are one 16-byte unit: 24 units per sample, spread over lanes 24..31.
@@ -132,6 +161,20 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
           const float hf = f16_bits_to_float(h);
           a16[aimg16_off(b, j, r * 4 + c, 0)] = h;
           a16[aimg16_off(b, j, r * 4 + c, 1)] = f16_rne_bits(row[c] - hf);
+        }
+      }
+    }
+    if (p.Aimg2) {
+      unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg2);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float tr = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
+        const float row[4] = {GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const unsigned short h = f16_rne_bits(row[c]);
+          a16[ff_aimg_off(b, j, r * 4 + c, 0)] = h;
+          a16[ff_aimg_off(b, j, r * 4 + c, 1)] = f16_rne_bits(row[c] - f16_bits_to_float(h));
         }
       }
     }

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, 'libsmplb200.so')
 
 OK = 0
 E_INVALID_ARG, E_BAD_SHAPE, E_CUDA, E_NOT_FINITE, E_UNSUPPORTED = -1, -2, -3, -4, -5
-F_BLEND_SIMT, F_KEEP_VPOSED, F_NO_SKIN, F_SKIN_SIMT, F_SCRATCH_VERTS = 1, 2, 4, 8, 16
+F_BLEND_SIMT, F_KEEP_VPOSED, F_NO_SKIN, F_SKIN_SIMT, F_SCRATCH_VERTS, F_FUSED = 1, 2, 4, 8, 16, 32
 
 NV, NV3, NJ, NB, NP, KDIM, KPAD, VP_PITCH = 6890, 20670, 24, 10, 207, 217, 224, 20736
 

@@ -57,7 +57,10 @@ enum {
   SMPLB_F_NO_SKIN = 1 << 2,      /* get_skin=False and no keypoints wanted: joints-only path   */
   SMPLB_F_SKIN_SIMT = 1 << 3,    /* skinning on CUDA cores with the compressed <=4-nonzero weights instead
                                     of the tcgen05 split-operand weight blend — verification path       */
-  SMPLB_F_SCRATCH_VERTS = 1 << 4 /* SIMT skinning path only: keypoints wanted but no verts buffer given, the workspace holds verts (the tensor-core path needs no verts for keypoints) */
+  SMPLB_F_SCRATCH_VERTS = 1 << 4, /* SIMT skinning path only: keypoints wanted but no verts buffer given, the workspace holds verts (the tensor-core path needs no verts for keypoints) */
+  SMPLB_F_FUSED = 1 << 5         /* one kernel for blend GEMM + weight blend + skinning: v_posed stays in TMEM and never
+                                    reaches HBM (north_star item 4).  Not combinable with SMPLB_F_KEEP_VPOSED (the
+                                    backward needs v_posed), SMPLB_F_BLEND_SIMT or SMPLB_F_SKIN_SIMT */
 };
 
 typedef struct smplb_model smplb_model;
