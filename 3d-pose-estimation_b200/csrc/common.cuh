@@ -159,8 +159,8 @@ struct PrepParams {
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
   float* Aimg;    // [ceil(B/20)][SK_AGRP] f16/bf16 operand image of A for the skinning GEMM (aimg16_off), nullable
-  float* Ximg2;   // fused forward: [ceil(B/128)][2][FF_XHALF] f16 split image of [beta | pose feature] (ff_ximg_off), nullable
-  float* Aimg2;   // fused forward: [ceil(B/128)][16][2][FF_AGH] f16 split image of A (ff_aimg_off), nullable
+  float* Ximg2;   // fused forward: [ceil(B/96)][2][FF_XHALF] f16 split image of [beta | pose feature] (ff_ximg_off), nullable
+  float* Aimg2;   // fused forward: [ceil(B/96)][12][2][FF_AGH] f16 split image of A (ff_aimg_off), nullable
   const float* cam_pos;
   const float* cam_rot;
   const float* focal;
@@ -291,25 +291,25 @@ __host__ __device__ inline float f16_bits_to_float(unsigned short h) { return __
 // ---- operand images of the FUSED forward (fused_fwd.cu): blend GEMM + weight blend + skinning in one kernel ----
 // D-stationary, transposed: a CTA pair (cta_group::2, M = 128) owns one 128-vertex tile, 64 vertices per CTA, and keeps
 // the rows of D = [shapedirs; posedirs] of its vertices resident in shared memory for all three components; samples
-// stream through in chunks of 128 (64 per CTA: in pair mode the B operand is split between the CTAs).  With M = 128 the
+// stream through in chunks of 96 (48 per CTA: in pair mode the B operand is split between the CTAs).  With M = 128 the
 // TMEM of each CTA holds rows = its 64 vertices in lanes 0..63 for the first half of the N columns and again in lanes
-// 64..127 for the second half (profiles/r02_mma_probe.txt), so v_posed[vertex, sample] (N = 128 samples) and the blended
+// 64..127 for the second half (profiles/r02_mma_probe.txt), so v_posed[vertex, sample] (N = 96 samples) and the blended
 // transforms T[vertex, (sample, 3x4)] (N = 96: 8 samples) meet in the same lane when the 8 samples of a T group are 4
 // of the first and 4 of the second half of the chunk.  All operands f16 main part + f16 residual (X.D ~= Xh.Dh + Xl.Dh
 // + Xh.Dl; the residual of D, ~2^-12 |D|, is a subnormal fp16 number with absolute error <= 2^-25: ~2^-18 |D|).
 // All images K-major, no swizzle: element (row, k) at (k/8) * rows*8 + (row/8)*64 + (row%8)*8 + k%8   (16-bit units)
 #define FF_VH 64                          // vertices per CTA
 #define FF_NHT (2 * SK_NVT)               // 108 half tiles
-#define FF_CH 128                         // samples per chunk (N of the blend MMAs)
-#define FF_SH 64                          // samples per CTA of the pair
+#define FF_CH 96                          // samples per chunk (N of the blend MMAs; leaves TMEM for 4 T accumulators)
+#define FF_SH 48                          // samples per CTA of the pair
 #define FF_NKS (KPAD / 16)                // 14 K16 steps
 #define FF_DPART (FF_VH * KPAD)           // elements per (component, part) block of a half tile (28 672 B)
 #define FF_DTILE (6 * FF_DPART)           // per half tile: [component 3][part 2]   (172 032 B)
-#define FF_XPART (FF_SH * 16)             // elements per part of a (chunk, half, k-step) slab (2 048 B)
-#define FF_XKS (2 * FF_XPART)             // per (chunk, half, k-step): [Xh | Xl]   (4 096 B)
+#define FF_XPART (FF_SH * 16)             // elements per part of a (chunk, half, k-step) slab (1 536 B)
+#define FF_XKS (2 * FF_XPART)             // per (chunk, half, k-step): [Xh | Xl]   (3 072 B)
 #define FF_XHALF (FF_NKS * FF_XKS)        // per (chunk, half)
 #define FF_G 8                            // samples per T group: 4 of each half of the chunk
-#define FF_NG (FF_CH / FF_G)              // 16 groups per chunk
+#define FF_NG (FF_CH / FF_G)              // 12 groups per chunk
 #define FF_AROWS 48                       // rows (4 samples x 12) per (group, half)
 #define FF_APART (FF_AROWS * SK_KPAD)     // elements per part (3 072 B)
 #define FF_AGH (2 * FF_APART)             // per (chunk, group, half): [Ah | Al]   (6 144 B)

@@ -29,28 +29,33 @@ namespace smplb {
 
 using namespace tc;
 
-constexpr int FF_XST = 4;
-constexpr int FF_AST = 3;
+constexpr int FF_XST = 5;   // X ring: 3 KB per K16 step
+constexpr int FF_AST = 5;   // A-image ring: 6 KB per group, ~450 cycles per group, ~1500 cycles of L2 latency -> >= 4 in flight
 constexpr int FF_EPI_WARPS = 8;
-constexpr int FF_THREADS = 96 + 32 * FF_EPI_WARPS;
+constexpr int FF_THREADS = 128 + 32 * FF_EPI_WARPS;   // X producer, blend issuer, A/D producer, 8 epilogue warps, T issuer
 constexpr uint32_t FF_D_BYTES = FF_DTILE * 2;   // 172 032
 constexpr uint32_t FF_W_BYTES = FF_WHT * 2;     // 8 192
-constexpr uint32_t FF_X_BYTES = FF_XKS * 2;     // 4 096
+constexpr uint32_t FF_X_BYTES = FF_XKS * 2;     // 3 072
 constexpr uint32_t FF_A_BYTES = FF_AGH * 2;     // 6 144
-constexpr uint32_t FF_ACC_B = 192;              // TMEM columns of one blend accumulator set (3 components x 64)
-constexpr uint32_t FF_TCOL0 = 384;              // first column of the T accumulators
+constexpr uint32_t FF_ACC_B = 3 * (FF_CH / 2);  // 144 TMEM columns of one blend accumulator set (3 components x 48)
+constexpr uint32_t FF_TCOL0 = 2 * FF_ACC_B;     // 288: first column of the T accumulators
 constexpr uint32_t FF_ACC_T = 48;               // TMEM columns of one T accumulator (N = 96 over two lane halves)
+constexpr int FF_TBUF = 4;                      // T accumulators in flight: the T round trip (MMA -> multicast commit ->
+                                                // tcgen05.ld in both CTAs -> remote arrive -> next MMA) takes > 1000 cycles,
+                                                // a group's tensor work ~400; with 2 accumulators the kernel ran at 1/3.6 of
+                                                // its tensor floor.  288 + 4 x 48 = 480 of the 512 columns.
 
 struct FfSmem {
   unsigned char d[FF_D_BYTES];
   unsigned char w[FF_W_BYTES];
   unsigned char x[FF_XST][FF_X_BYTES];
   unsigned char a[FF_AST][FF_A_BYTES];
-  float out[FF_EPI_WARPS][2][96];                 // per epilogue warp: 2 samples x 32 vertices x 3
-  uint64_t dfull, peer_dfull, dempty;
-  uint64_t xfull[FF_XST], peer_xfull[FF_XST], xempty[FF_XST];
-  uint64_t afull[FF_AST], peer_afull[FF_AST], aempty[FF_AST];
-  uint64_t bfull[2], bempty[2], tfull[2], tempty[2];
+  float out[FF_EPI_WARPS][96];                    // per epilogue warp: 32 vertices x 3 of one sample (four passes per group)
+  // full barriers: the leader's count the local producer AND the peer's relay (one wait per stage on the MMA thread)
+  uint64_t dfull, dempty;
+  uint64_t xfull[FF_XST], xempty[FF_XST];
+  uint64_t afull[FF_AST], aempty[FF_AST];
+  uint64_t bfull[2], bempty[2], tfull[FF_TBUF], tempty[FF_TBUF];
   uint32_t tmem_base;
 };
 
@@ -83,6 +88,12 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
                : "r"(taddr)
                : "memory");
 }
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&r)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(taddr)
+               : "memory");
+}
 __device__ __forceinline__ void tmem_ld2(uint32_t taddr, uint32_t (&r)[2]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr) : "memory");
 }
@@ -100,24 +111,24 @@ fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2,
   const int n_items = ff_n_items(sched, cl);
 
   if (threadIdx.x == 0) {
-    mbar_init(&sm.dfull, 1);
-    mbar_init(&sm.peer_dfull, 1);
-    mbar_init(&sm.dempty, 1);
+    const uint32_t nfull = rk == 0 ? 2 : 1;   // leader: own producer + the peer's relay
+    mbar_init(&sm.dfull, nfull);
+    mbar_init(&sm.dempty, 2);   // both issuing warps of the leader commit at a tile change
     for (int s = 0; s < FF_XST; ++s) {
-      mbar_init(&sm.xfull[s], 1);
-      mbar_init(&sm.peer_xfull[s], 1);
+      mbar_init(&sm.xfull[s], nfull);
       mbar_init(&sm.xempty[s], 1);
     }
     for (int s = 0; s < FF_AST; ++s) {
-      mbar_init(&sm.afull[s], 1);
-      mbar_init(&sm.peer_afull[s], 1);
+      mbar_init(&sm.afull[s], nfull);
       mbar_init(&sm.aempty[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&sm.bfull[s], 1);
       mbar_init(&sm.bempty[s], 2 * FF_EPI_WARPS);   // epilogue warps of both CTAs
+    }
+    for (int s = 0; s < FF_TBUF; ++s) {
       mbar_init(&sm.tfull[s], 1);
-      mbar_init(&sm.tempty[s], 2 * FF_EPI_WARPS);
+      mbar_init(&sm.tempty[s], FF_EPI_WARPS);       // the four warps of one epilogue set in both CTAs
     }
     fence_mbar_init();
   }
@@ -179,108 +190,103 @@ fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2,
       }
       __syncwarp();
     }
-  } else if (warp == 1) {
-    // ================= MMA issue (leader) / stage relay (peer): the same walk over the rings =================
+  } else if (warp == 1 || warp == 3 + FF_EPI_WARPS) {
+    // ================= MMA issue (leader) / stage relay (peer) =================
+    // Two issuing warps with their own rings, so that a stall of one stream does not hold up the other (with one
+    // issuer the T groups waited behind blend K steps that waited for X slabs: 4x the tensor floor):
+    //   warp 1   blend GEMM: per chunk 14 K16 steps x 9 MMAs from the X ring into blend accumulator il & 1
+    //   warp 11  weight blend: per chunk 12 groups x 6 MMAs from the A ring into T accumulator (12 il + g) % 4
     // Whole warp runs the loops (uniform control flow); one elected lane issues the tcgen05 / arrive ops.
     const uint32_t issue = elect_one() ? 1u : 0u;
     const bool leader = rk == 0;
-    constexpr uint32_t idesc_b = umma_idesc(0, 128, FF_CH);        // kind::f16, f16 operands, M 128 (pair), N 128
+    const bool blend_role = warp == 1;
+    constexpr uint32_t idesc_b = umma_idesc(0, 128, FF_CH);        // kind::f16, f16 operands, M 128 (pair), N 96
     constexpr uint32_t idesc_t = umma_idesc(0, 128, 2 * FF_AROWS);  // N 96
     const uint64_t d_t = umma_desc_kmajor_noswz(0, FF_VH * 16, 128);      // D and W: 64 rows per CTA
-    const uint64_t x_t = umma_desc_kmajor_noswz(0, FF_SH * 16, 128);      // X: 64 rows per CTA
+    const uint64_t x_t = umma_desc_kmajor_noswz(0, FF_SH * 16, 128);      // X: 48 rows per CTA
     const uint64_t a_t = umma_desc_kmajor_noswz(0, FF_AROWS * 16, 128);   // A image: 48 rows per CTA
     const uint32_t db = smem_u32(sm.d) >> 4, wb = smem_u32(sm.w) >> 4, xb = smem_u32(sm.x[0]) >> 4, ab = smem_u32(sm.a[0]) >> 4;
     uint32_t xit = 0, ait = 0, tg = 0, dk = 0;
 
-    auto stage_wait = [&](uint64_t* full, uint64_t* peer_full, uint32_t ph) {
-      mbar_wait_spin(smem_u32(full), ph);
-      if (leader) mbar_wait_spin(smem_u32(peer_full), ph);
-      else if (issue) mbar_arrive_remote(peer_full, 0);
+    auto stage_wait = [&](uint64_t* full, uint32_t ph, bool relay) {
+      mbar_wait_spin(smem_u32(full), ph);                             // leader: local data AND the peer's relay have arrived
+      if (!leader && relay && issue) mbar_arrive_remote(full, 0);     // peer: my half has landed
     };
-    auto blend_kstep = [&](uint32_t bb, int ks) {
-      const uint32_t s = xit % FF_XST;
-      stage_wait(&sm.xfull[s], &sm.peer_xfull[s], (xit / FF_XST) & 1);
-      ++xit;
-      if (!leader) return;
-      tc_fence_after();
-      const uint64_t xh = x_t + (uint64_t)(xb + s * (FF_X_BYTES / 16)), xl = xh + (uint64_t)(FF_XPART * 2 / 16);
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const uint32_t dcol = tmem + bb * FF_ACC_B + (uint32_t)c * (FF_CH / 2);
-        const uint64_t dh = d_t + (uint64_t)(db + (uint32_t)(c * 2) * (FF_DPART * 2 / 16) + (uint32_t)ks * (2 * FF_VH * 16 / 16));
-        const uint64_t dl = dh + (uint64_t)(FF_DPART * 2 / 16);
-        umma_f16_ss_pair(dcol, dh, xh, idesc_b, ks != 0 ? 1u : 0u, issue);   // Dh.Xh
-        umma_f16_ss_pair(dcol, dh, xl, idesc_b, 1u, issue);                  // Dh.Xl
-        umma_f16_ss_pair(dcol, dl, xh, idesc_b, 1u, issue);                  // Dl.Xh
-      }
-      umma_commit_pair(smem_u32(&sm.xempty[s]), 3, issue);
-      if (ks == FF_NKS - 1) umma_commit_pair(smem_u32(&sm.bfull[bb]), 3, issue);
-    };
-    auto t_group = [&]() {
-      const uint32_t tb = tg & 1;
-      if (leader) mbar_wait_spin(smem_u32(&sm.tempty[tb]), ((tg >> 1) & 1) ^ 1);
-      const uint32_t s = ait % FF_AST;
-      stage_wait(&sm.afull[s], &sm.peer_afull[s], (ait / FF_AST) & 1);
-      ++ait;
-      if (leader) {
-        tc_fence_after();
-        const uint32_t tcol = tmem + FF_TCOL0 + tb * FF_ACC_T;
-#pragma unroll
-        for (int ks = 0; ks < SK_KPAD / 16; ++ks) {
-          const uint64_t wh = d_t + (uint64_t)(wb + (uint32_t)ks * (2 * FF_VH * 16 / 16)), wl = wh + (uint64_t)(FF_WPART * 2 / 16);
-          const uint64_t ah = a_t + (uint64_t)(ab + s * (FF_A_BYTES / 16) + (uint32_t)ks * (2 * FF_AROWS * 16 / 16));
-          const uint64_t al = ah + (uint64_t)(FF_APART * 2 / 16);
-          umma_f16_ss_pair(tcol, wh, ah, idesc_t, ks != 0 ? 1u : 0u, issue);   // Wh.Ah
-          umma_f16_ss_pair(tcol, wl, ah, idesc_t, 1u, issue);                  // Wl.Ah
-          umma_f16_ss_pair(tcol, wh, al, idesc_t, 1u, issue);                  // Wh.Al
-        }
-        umma_commit_pair(smem_u32(&sm.aempty[s]), 3, issue);
-        umma_commit_pair(smem_u32(&sm.tfull[tb]), 3, issue);
-      }
-      ++tg;
-    };
-
     int cur_vt = -1;
-    bool pre = false;   // the blend MMAs of the current item were already issued (interleaved with the previous item)
     for (int il = 0; il < n_items; ++il) {
       int vt, ch;
       ff_item(sched, cl, il, vt, ch);
       if (vt != cur_vt) {
-        if (cur_vt >= 0 && leader) umma_commit_pair(smem_u32(&sm.dempty), 3, issue);   // old tile no longer read
-        stage_wait(&sm.dfull, &sm.peer_dfull, dk & 1);
+        // tile change: this issuer's MMAs on the old tile are complete -> (both issuers) the loaders may overwrite D / W
+        if (cur_vt >= 0 && leader) umma_commit_pair(smem_u32(&sm.dempty), 3, issue);
+        stage_wait(&sm.dfull, dk & 1, blend_role);   // the peer's blend warp relays the tile load once
         ++dk;
         cur_vt = vt;
-        pre = false;
       }
-      const uint32_t bb = (uint32_t)il & 1;
-      if (!pre) {
+      if (blend_role) {
+        const uint32_t bb = (uint32_t)il & 1;
         if (leader) mbar_wait_spin(smem_u32(&sm.bempty[bb]), (((uint32_t)il >> 1) & 1) ^ 1);
-        for (int ks = 0; ks < FF_NKS; ++ks) blend_kstep(bb, ks);
+#pragma unroll 1
+        for (int ks = 0; ks < FF_NKS; ++ks, ++xit) {
+          const uint32_t s = xit % FF_XST;
+          stage_wait(&sm.xfull[s], (xit / FF_XST) & 1, true);
+          if (!leader) continue;
+          tc_fence_after();
+          const uint64_t xh = x_t + (uint64_t)(xb + s * (FF_X_BYTES / 16)), xl = xh + (uint64_t)(FF_XPART * 2 / 16);
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const uint32_t dcol = tmem + bb * FF_ACC_B + (uint32_t)c * (FF_CH / 2);
+            const uint64_t dh = d_t + (uint64_t)(db + (uint32_t)(c * 2) * (FF_DPART * 2 / 16) + (uint32_t)ks * (2 * FF_VH * 16 / 16));
+            const uint64_t dl = dh + (uint64_t)(FF_DPART * 2 / 16);
+            umma_f16_ss_pair(dcol, dh, xh, idesc_b, ks != 0 ? 1u : 0u, issue);   // Dh.Xh
+            umma_f16_ss_pair(dcol, dh, xl, idesc_b, 1u, issue);                  // Dh.Xl
+            umma_f16_ss_pair(dcol, dl, xh, idesc_b, 1u, issue);                  // Dl.Xh
+          }
+          umma_commit_pair(smem_u32(&sm.xempty[s]), 3, issue);
+          if (ks == FF_NKS - 1) umma_commit_pair(smem_u32(&sm.bfull[bb]), 3, issue);
+        }
+      } else {
+#pragma unroll 1
+        for (int g = 0; g < FF_NG; ++g, ++tg, ++ait) {
+          const uint32_t tb = tg % FF_TBUF;
+          if (leader) mbar_wait_spin(smem_u32(&sm.tempty[tb]), ((tg / FF_TBUF) & 1) ^ 1);
+          const uint32_t s = ait % FF_AST;
+          stage_wait(&sm.afull[s], (ait / FF_AST) & 1, true);
+          if (!leader) continue;
+          tc_fence_after();
+          const uint32_t tcol = tmem + FF_TCOL0 + tb * FF_ACC_T;
+#pragma unroll
+          for (int ks = 0; ks < SK_KPAD / 16; ++ks) {
+            const uint64_t wh = d_t + (uint64_t)(wb + (uint32_t)ks * (2 * FF_VH * 16 / 16)), wl = wh + (uint64_t)(FF_WPART * 2 / 16);
+            const uint64_t ah = a_t + (uint64_t)(ab + s * (FF_A_BYTES / 16) + (uint32_t)ks * (2 * FF_AROWS * 16 / 16));
+            const uint64_t al = ah + (uint64_t)(FF_APART * 2 / 16);
+            umma_f16_ss_pair(tcol, wh, ah, idesc_t, ks != 0 ? 1u : 0u, issue);   // Wh.Ah
+            umma_f16_ss_pair(tcol, wl, ah, idesc_t, 1u, issue);                  // Wl.Ah
+            umma_f16_ss_pair(tcol, wh, al, idesc_t, 1u, issue);                  // Wh.Al
+          }
+          umma_commit_pair(smem_u32(&sm.aempty[s]), 3, issue);
+          umma_commit_pair(smem_u32(&sm.tfull[tb]), 3, issue);
+        }
       }
-      bool can_pre = false;
-      if (il + 1 < n_items) {
-        int vt2, ch2;
-        ff_item(sched, cl, il + 1, vt2, ch2);
-        can_pre = vt2 == vt;
-      }
-      if (can_pre && leader) mbar_wait_spin(smem_u32(&sm.bempty[bb ^ 1]), ((((uint32_t)il + 1) >> 1) & 1) ^ 1);
-      for (int g = 0; g < FF_NG; ++g) {
-        t_group();
-        if (can_pre && g < FF_NKS) blend_kstep(bb ^ 1, g);
-      }
-      pre = can_pre;
     }
     __syncwarp();
   } else {
     // ================= epilogue (warps 3..10, both CTAs) =================
+    // Two sets of four warps (one warp per TMEM lane quarter): set 0 takes the even T groups (accumulator 0), set 1 the
+    // odd ones (accumulator 1), each warp all 4 samples of its chunk half -- a group's fixed costs (barrier waits,
+    // arrivals, address set-up) are paid once per 4 samples and a warp has two group periods for one group.
     const int ew = warp - 3;
     const int q = warp & 3;              // TMEM lane quarter this warp may read
-    const int sub = ew >> 2;             // which 2 of the 4 samples of a (group, chunk half)
+    const int set = ew >> 2;             // parity of the groups this warp handles = its T accumulator
     const int hl = q >> 1;               // chunk half held by this lane quarter
     const int r = (q & 1) * 32 + lane;   // vertex inside the CTA's 64
     const uint32_t lsel = (uint32_t)(q * 32) << 16;
-    float* stage = &sm.out[ew][0][0];
-    uint32_t tg = 0;
+    const uint32_t tcol0 = tmem + lsel + FF_TCOL0 + (uint32_t)set * FF_ACC_T;   // this set uses T accumulators set and set + 2
+    float* stage = &sm.out[ew][0];
+    float* const verts_r = verts;
+    float* const kpv_r = kpv;
+    const int Bn = B;
+    uint32_t tu = 0;                     // uses of this set's T accumulators so far
     for (int il = 0; il < n_items; ++il) {
       int vt, ch;
       ff_item(sched, cl, il, vt, ch);
@@ -292,71 +298,72 @@ fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2,
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           tv[c] = __ldg(vt_plain + 3 * v + c);
-          if (kpv) slot[c] = __ldg(kpc_slot_of + 3 * v + c);
+          if (kpv_r) slot[c] = __ldg(kpc_slot_of + 3 * v + c);
         }
       }
+      const bool any_slot = (slot[0] & slot[1] & slot[2]) >= 0 || slot[0] >= 0 || slot[1] >= 0 || slot[2] >= 0;
       const int v0 = vt * SK_VT + (int)rk * FF_VH + (q & 1) * 32;   // first vertex of this warp
       const int nvf = 3 * max(0, min(32, NV - v0));                 // floats of the warp's 96 that exist
       const uint32_t bb = (uint32_t)il & 1;
+      const uint32_t pcol = tmem + lsel + bb * FF_ACC_B;
       mbar_wait_spin(smem_u32(&sm.bfull[bb]), ((uint32_t)il >> 1) & 1);
       tc_fence_after();
-      for (int g = 0; g < FF_NG; ++g, ++tg) {
-        const uint32_t tb = tg & 1;
-        mbar_wait_spin(smem_u32(&sm.tfull[tb]), (tg >> 1) & 1);
+#pragma unroll 1
+      for (int g = set; g < FF_NG; g += 2, ++tu) {
+        const uint32_t tbuf = (uint32_t)set + 2 * (tu & 1);
+        const uint32_t tcol = tcol0 + 2 * (tu & 1) * FF_ACC_T;
+        mbar_wait_spin(smem_u32(&sm.tfull[tbuf]), (tu >> 1) & 1);
         tc_fence_after();
-        // T of this thread's two samples: columns [24 sub, 24 sub + 24) of the 48 of this lane half
-        uint32_t t16[16], t8[8], px[2], py[2], pz[2];
-        const uint32_t tbase = tmem + lsel + FF_TCOL0 + tb * FF_ACC_T + (uint32_t)sub * 24;
-        if (sub == 0) {
-          tmem_ld16(tbase, t16);        // T[0..15]
-          tmem_ld8(tbase + 16, t8);     // T[16..23]
-        } else {
-          tmem_ld8(tbase, t8);          // T[0..7]
-          tmem_ld16(tbase + 8, t16);    // T[8..23]
-        }
-        const uint32_t pbase = tmem + lsel + bb * FF_ACC_B + (uint32_t)(4 * g + 2 * sub);
-        tmem_ld2(pbase, px);
-        tmem_ld2(pbase + FF_CH / 2, py);
-        tmem_ld2(pbase + 2 * (FF_CH / 2), pz);
+        uint32_t t0[16], t1[16], t2[16], px[4], py[4], pz[4];
+        tmem_ld16(tcol, t0);
+        tmem_ld16(tcol + 16, t1);
+        tmem_ld16(tcol + 32, t2);
+        tmem_ld4(pcol + 4 * g, px);
+        tmem_ld4(pcol + 4 * g + FF_CH / 2, py);
+        tmem_ld4(pcol + 4 * g + 2 * (FF_CH / 2), pz);
         tmem_ld_wait();
-        float T[24];
-#pragma unroll
-        for (int e = 0; e < 24; ++e) {
-          if (sub == 0) T[e] = __uint_as_float(e < 16 ? t16[e & 15] : t8[e & 7]);
-          else T[e] = __uint_as_float(e < 8 ? t8[e & 7] : t16[(e - 8) & 15]);
-        }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive_remote(&sm.tempty[tb], 0);
-        float y[2][3];
+        if (lane == 0) mbar_arrive_remote(&sm.tempty[tbuf], 0);
+        const int b0 = ch * FF_CH + hl * FF_SH + 4 * g;
+        float y[4][3];
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 4; ++i) {
           const float x0 = __uint_as_float(px[i]) + tv[0], x1 = __uint_as_float(py[i]) + tv[1], x2 = __uint_as_float(pz[i]) + tv[2];
-          const float* t = T + 12 * i;
+          float t[12];
+#pragma unroll
+          for (int e = 0; e < 12; ++e) {
+            const int idx = 12 * i + e;
+            t[e] = __uint_as_float(idx < 16 ? t0[idx & 15] : (idx < 32 ? t1[idx & 15] : t2[idx & 15]));
+          }
 #pragma unroll
           for (int rr = 0; rr < 3; ++rr)
             y[i][rr] = fmaf(t[4 * rr], x0, fmaf(t[4 * rr + 1], x1, fmaf(t[4 * rr + 2], x2, t[4 * rr + 3])));
         }
         // transpose through smem: thread = vertex wrote 3 floats, rows leave as 384 contiguous bytes per sample
+        // (one sample per pass: the staging buffer is kept small, shared memory goes to the operand rings)
 #pragma unroll
-        for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < 4; ++i) {
 #pragma unroll
-          for (int c = 0; c < 3; ++c) stage[i * 96 + 3 * lane + c] = y[i][c];
-        __syncwarp();
-        const int b0 = ch * FF_CH + hl * FF_SH + 4 * g + 2 * sub;
+          for (int c = 0; c < 3; ++c) stage[3 * lane + c] = y[i][c];
+          __syncwarp();
+          if (verts_r && b0 + i < Bn) {
+            float* dst = verts_r + (size_t)(b0 + i) * NV3 + (size_t)v0 * 3 + lane;
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int b = b0 + i;
-          if (b < B) {
-            if (verts) {
-              float* dst = verts + (size_t)b * NV3 + (size_t)v0 * 3;
+            for (int k = 0; k < 3; ++k)
+              if (lane + 32 * k < nvf) __stcs(dst + 32 * k, stage[lane + 32 * k]);
+          }
+          __syncwarp();
+        }
+        if (any_slot) {
 #pragma unroll
-              for (int k = 0; k < 3; ++k)
-                if (lane + 32 * k < nvf) __stcs(dst + lane + 32 * k, stage[i * 96 + lane + 32 * k]);
+          for (int i = 0; i < 4; ++i) {
+            const int b = b0 + i;
+            if (b < Bn) {
+#pragma unroll
+              for (int c = 0; c < 3; ++c)
+                if (slot[c] >= 0) kpv_r[((size_t)(b / SK_S) * kpv_pitch + slot[c]) * SK_S + (b % SK_S)] = y[i][c];
             }
-#pragma unroll
-            for (int c = 0; c < 3; ++c)
-              if (slot[c] >= 0) kpv[((size_t)(b / SK_S) * kpv_pitch + slot[c]) * SK_S + (b % SK_S)] = y[i][c];
           }
         }
         __syncwarp();

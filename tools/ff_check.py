@@ -33,9 +33,16 @@ if os.environ.get('FF_TIME'):
         for _ in range(3):
             m.forward(d['beta'], d['theta'], d['cam_pos'], d['cam_rot'], d['focal'], flags=fl, out=out)
         torch.cuda.synchronize()
+        import ctypes as C
+        L = _lib.lib()
+        L.smplb_timing_begin(10)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(10):
             m.forward(d['beta'], d['theta'], d['cam_pos'], d['cam_rot'], d['focal'], flags=fl, out=out)
         e1.record(); torch.cuda.synchronize()
-        print('B=%d %s forward: %.3f ms' % (B, name, e0.elapsed_time(e1) / 10), flush=True)
+        kms = (C.c_float * 40)(); nc = C.c_int32(0)
+        L.smplb_timing_end(kms, C.byref(nc))
+        kt = np.array(list(kms)).reshape(-1, 4)[:nc.value].mean(axis=0)
+        print('B=%d %s forward: %.3f ms  [prep %.3f | blend %.3f | skin/fused %.3f | kp %.3f]' % (
+            B, name, e0.elapsed_time(e1) / 10, kt[0], kt[1], kt[2], kt[3]), flush=True)
