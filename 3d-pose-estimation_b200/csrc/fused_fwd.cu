@@ -9,18 +9,23 @@
 // Layout (operand images and the TMEM lane argument: common.cuh "FUSED forward"):
 //   * D-STATIONARY, transposed GEMM: a CTA pair (cluster of 2, cta_group::2, M = 128) owns a 128-vertex tile, 64
 //     vertices per CTA; each CTA keeps the D rows of its vertices resident in shared memory for x, y, z (3 x 2 parts x
-//     28 KB = 168 KB).  N = 128 samples per blend MMA (the A operand is re-read from shared memory by every MMA at
-//     <= 128 B/clk -- profiles/r02_mma_probe.txt -- so N must be large: 32 cycles per M128 N128 K16 MMA).
-//   * per 128-sample chunk: 14 K16 steps x 3 components x 3 split products = 126 blend MMAs into three 64-column
-//     accumulators (double buffered), then 16 groups of 8 samples: 6 MMAs (M128 N96 K16) for T into a 48-column
-//     accumulator (double buffered); the blend MMAs of the NEXT chunk are interleaved with the T groups of this one.
+//     28 KB = 168 KB).  N = 96 samples per blend MMA (the A operand is re-read from shared memory by every MMA at
+//     <= 128 B/clk -- profiles/r02_mma_probe.txt -- so N must be large: ~24 cycles per M128 N96 K16 MMA).
+//   * per 96-sample chunk: 14 K16 steps x 3 components x 3 split products = 126 blend MMAs into three 48-column
+//     accumulators (double buffered), then 12 groups of 8 samples: 6 MMAs (M128 N96 K16) for T into a 48-column
+//     accumulator (4 in flight); blend and weight-blend MMAs are issued by two warps with their own operand rings.
+//   STATUS (profiles/r02_fused_forward.md): parity-green, 3.7 - 4.4 ms at B = 65536 against 3.5 ms for the unfused pair,
+//   so smplb_forward uses it only on request (SMPLB_F_FUSED).  With 168 KB of D resident only 52 KB are left for the X
+//   and A-image rings, whose round trip (bulk copy from L2 + peer relay + MMA completion + multicast commit) was
+//   measured at 1800 - 2200 cycles: X ring alone 1.68 ms, A ring alone 1.17 ms with every MMA, TMEM load and store removed.
 //   * TMEM lane = vertex for both accumulators (lanes 64..127 repeat the vertices for the second half of the columns;
 //     a T group is 4 samples of each chunk half, so v_posed and T of a sample sit in the same lane).
-//   warp 0      X producer: one 4 KB bulk copy per K16 step (4-stage ring)
-//   warp 1      leader CTA: MMA issue; peer CTA: relays "my stage landed" to the leader's barriers
-//   warp 2      A-image producer (6 KB per group, 3-stage ring); D / W tile loads when the vertex tile changes
-//   warps 3-10  epilogue: tcgen05.ld T and v_posed (thread = vertex, 2 samples per warp and group), apply, transpose
-//               96 floats through smem, coalesced 384-byte row stores; keypoint vertices also go to the compact rows
+//   warp 0      X producer: one 3 KB bulk copy per K16 step (5-stage ring)
+//   warp 1      leader CTA: blend MMA issue; peer CTA: relays "my stage landed" to the leader's barriers
+//   warp 2      A-image producer (6 KB per group, 5-stage ring); D / W tile loads when the vertex tile changes
+//   warps 3-10  epilogue: tcgen05.ld T and v_posed (thread = vertex, 4 samples per warp and group, two sets of warps
+//               alternate over the groups), apply, 12-byte-stride stores; keypoint vertices also go to the compact rows
+//   warp 11     leader CTA: weight-blend MMA issue; peer CTA: relay of the A ring
 // Schedule: 54 clusters own one vertex tile each and sweep the first m chunks in step (X / A images are then shared
 // through L2); the other 20 clusters split the remaining chunks of all tiles.
 #include "tc_common.cuh"
@@ -50,7 +55,6 @@ struct FfSmem {
   unsigned char w[FF_W_BYTES];
   unsigned char x[FF_XST][FF_X_BYTES];
   unsigned char a[FF_AST][FF_A_BYTES];
-  float out[FF_EPI_WARPS][96];                    // per epilogue warp: 32 vertices x 3 of one sample (four passes per group)
   // full barriers: the leader's count the local producer AND the peer's relay (one wait per stage on the MMA thread)
   uint64_t dfull, dempty;
   uint64_t xfull[FF_XST], xempty[FF_XST];
@@ -282,7 +286,6 @@ fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2,
     const int r = (q & 1) * 32 + lane;   // vertex inside the CTA's 64
     const uint32_t lsel = (uint32_t)(q * 32) << 16;
     const uint32_t tcol0 = tmem + lsel + FF_TCOL0 + (uint32_t)set * FF_ACC_T;   // this set uses T accumulators set and set + 2
-    float* stage = &sm.out[ew][0];
     float* const verts_r = verts;
     float* const kpv_r = kpv;
     const int Bn = B;
@@ -340,20 +343,18 @@ fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2,
           for (int rr = 0; rr < 3; ++rr)
             y[i][rr] = fmaf(t[4 * rr], x0, fmaf(t[4 * rr + 1], x1, fmaf(t[4 * rr + 2], x2, t[4 * rr + 3])));
         }
-        // transpose through smem: thread = vertex wrote 3 floats, rows leave as 384 contiguous bytes per sample
-        // (one sample per pass: the staging buffer is kept small, shared memory goes to the operand rings)
+        // straight from registers: 12-byte lane stride, the three stores of a sample fill the same 384 bytes (the L2 merges
+        // them into whole sectors); a transposition through smem (as in the unfused kernel) cost more epilogue latency
+        // than it saved: 4.49 -> 3.65 ms
+        if (verts_r && vok) {
+          float* dst = verts_r + (size_t)b0 * NV3 + (size_t)v * 3;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+          for (int i = 0; i < 4; ++i) {
+            if (b0 + i < Bn) {
 #pragma unroll
-          for (int c = 0; c < 3; ++c) stage[3 * lane + c] = y[i][c];
-          __syncwarp();
-          if (verts_r && b0 + i < Bn) {
-            float* dst = verts_r + (size_t)(b0 + i) * NV3 + (size_t)v0 * 3 + lane;
-#pragma unroll
-            for (int k = 0; k < 3; ++k)
-              if (lane + 32 * k < nvf) __stcs(dst + 32 * k, stage[lane + 32 * k]);
+              for (int c = 0; c < 3; ++c) __stcs(dst + (size_t)i * NV3 + c, y[i][c]);
+            }
           }
-          __syncwarp();
         }
         if (any_slot) {
 #pragma unroll
@@ -366,7 +367,6 @@ fused_fwd_kernel(int B, FfSched sched, const unsigned short* __restrict__ Ximg2,
             }
           }
         }
-        __syncwarp();
       }
       // every TMEM read of this blend accumulator set has completed (the last group's tcgen05.wait::ld)
       tc_fence_before();
