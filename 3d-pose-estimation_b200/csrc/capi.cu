@@ -16,6 +16,7 @@ Workspace carve(void* base, int B, int flags, int kpv_pitch) {
     return (float*)p;
   };
   const size_t b = (size_t)(B > 0 ? B : 0);
+  w.status = (int*)take(256);   // input-range flags of the last forward call (smplb_forward_status)
   w.Ximg = take(((b + BL_BM - 1) / BL_BM) * BL_XTILE * sizeof(float));
   w.A = take(b * NJ * 12 * sizeof(float));
   w.joints = take(b * NJ * 3 * sizeof(float));
@@ -149,6 +150,8 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.px = io->px;
   p.cfg = io->cfg;
   p.tree = m->tree;
+  p.status = w.status;
+  SMPLB_CUDA_CHECK(cudaMemsetAsync(w.status, 0, sizeof(int), st));
   timing_mark(0, st);
   rc = launch_pose_prep(p, st);
   if (rc != SMPLB_OK) return rc;
@@ -190,6 +193,18 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   if (io->kp) rc = compact ? launch_keypoints_compact(m, B, w.kpv, io->kp, st) : launch_keypoints(m, B, verts, io->kp, st);
   timing_mark(4, st);
   return rc;
+}
+
+extern "C" int32_t smplb_forward_status(const void* workspace, void* stream) {
+  if (!workspace) return fail(SMPLB_E_INVALID_ARG, "smplb_forward_status: null workspace");
+  int flags = 0;
+  SMPLB_CUDA_CHECK(cudaMemcpyAsync(&flags, workspace, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  SMPLB_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+  if (flags & 1)
+    return fail(SMPLB_E_NOT_FINITE, "smplb_forward: a beta entry is not finite or exceeds 65504 in magnitude (the fp16 main "
+                                    "part of the split-operand GEMM cannot carry it); the outputs of that call are invalid");
+  if (flags & 2) return fail(SMPLB_E_NOT_FINITE, "smplb_forward: a theta entry is not finite; the outputs of that call are invalid");
+  return SMPLB_OK;
 }
 
 extern "C" int32_t smplb_forward_host(const smplb_model* m, const smplb_forward_io* h,

@@ -168,10 +168,12 @@ struct PrepParams {
   float* px;
   smplb_camcfg cfg;
   Tree tree;
+  int* status;    // nullable: input-range flags (see Workspace)
 };
 
 // Carving of the caller-owned workspace (capi.cu)
 struct Workspace {
+  int* status;     // [1] bit 0: |beta| > 65504 or not finite, bit 1: theta not finite (set by pose_prep, smplb_forward_status)
   float* Ximg;
   float* A;
   float* Aimg;

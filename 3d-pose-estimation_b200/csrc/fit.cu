@@ -151,6 +151,7 @@ extern "C" int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, 
   p.Ximg = nullptr;
   p.Ximg2 = nullptr;
   p.Aimg2 = nullptr;
+  p.status = nullptr;
   p.joints = nullptr;
   p.Rs = nullptr;
   p.A = nullptr;

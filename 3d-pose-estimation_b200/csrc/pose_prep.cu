@@ -31,6 +31,15 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
   float beta[NB];
 #pragma unroll
   for (int k = 0; k < NB; ++k) beta[k] = __ldg(p.beta + (size_t)b * NB + k);
+  if (p.status) {
+    // the fp16 main parts of the split-operand GEMMs cannot carry |beta| > 65504 (theta only enters through rotations)
+    bool bad_b = false;
+#pragma unroll
+    for (int k = 0; k < NB; ++k) bad_b |= !(fabsf(beta[k]) <= 65504.0f);
+    const bool bad_t = !(fabsf(tx) <= 3.0e38f) || !(fabsf(ty) <= 3.0e38f) || !(fabsf(tz) <= 3.0e38f);
+    const int f = (bad_b ? 1 : 0) | ((act && bad_t) ? 2 : 0);
+    if (f && (lane == 0 || (f & 2))) atomicOr(p.status, f);
+  }
   float J[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {

@@ -73,6 +73,7 @@ SYMBOLS = {
     'smplb_workspace_bytes': (C.c_size_t, [C.c_void_p, C.c_int32, C.c_int32]),
     'smplb_forward': (C.c_int32, [C.c_void_p, C.POINTER(ForwardIO), C.c_void_p, C.c_size_t,
                                   C.c_int32, C.c_void_p]),
+    'smplb_forward_status': (C.c_int32, [C.c_void_p, C.c_void_p]),
     'smplb_forward_host': (C.c_int32, [C.c_void_p, C.POINTER(ForwardIO), C.POINTER(ForwardIO),
                                        C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p]),
     'smplb_rodrigues': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),

@@ -95,8 +95,9 @@ class Model:
 
     def forward(self, beta, theta, cam_pos=None, cam_rot=None, focal=None, want_verts=True,
                 want_kp=True, want_Rs=True, want_A=False, want_uv=True, flags=0, cam_cfg=None,
-                out=None, ws=None):
-        """One smplb_forward call.  Returns a dict of CUDA tensors."""
+                out=None, ws=None, check_inputs=False):
+        """One smplb_forward call.  Returns a dict of CUDA tensors.  check_inputs: also run smplb_forward_status
+        (synchronises; raises SmplbError(E_NOT_FINITE) for a non-finite input or |beta| > 65504)."""
         dev = self.device
         beta = _dev_f32(beta, dev)
         theta = _dev_f32(theta, dev)
@@ -141,6 +142,8 @@ class Model:
         with torch.cuda.device(dev):
             check(_lib.lib().smplb_forward(self._h, C.byref(io), _ptr(ws), ws.numel(), flags,
                                            _stream(dev)))
+            if check_inputs:
+                check(_lib.lib().smplb_forward_status(_ptr(ws), _stream(dev)))
         out['_keep'] = (beta, theta, cam_pos, cam_rot, focal)
         return out
 

@@ -132,6 +132,12 @@ size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags);
 int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* io, void* workspace,
                       size_t workspace_bytes, int32_t flags, void* stream);
 
+/* Input-range check of the LAST smplb_forward call that used `workspace` (stream-ordered after it; synchronises the
+ * stream): SMPLB_E_NOT_FINITE when a beta entry was not finite or beyond the fp16 range (|beta| > 65504: the fp16 main
+ * part of the split-operand GEMMs cannot carry it -- the vertices of that call are invalid), or a theta entry was not
+ * finite; SMPLB_OK otherwise.  The forward itself never synchronises, so the check is a separate, optional call. */
+int32_t smplb_forward_status(const void* workspace, void* stream);
+
 /* Same call with HOST buffers (pinned or pageable): H2D of beta/theta/camera, the kernels, D2H of
  * every non-NULL output, then a stream synchronise.  `io` holds HOST pointers here; `dev_io`
  * holds caller-owned DEVICE staging buffers of the same shapes.  This is the end-to-end entry

@@ -74,14 +74,18 @@ def batch_global_rigid_transformation(Rs, Js, parent):
     return new_J, results - init_bone
 
 
-def smpl_forward(m, beta, theta, tile_W=True):
-    """batch_smpl.py:71-143."""
+def smpl_forward(m, beta, theta, tile_W=True, want_verts=True):
+    """batch_smpl.py:71-143.  want_verts=False stops after J_transformed (the joint-only losses of pose_model_3d.py:194-238
+    never touch the vertices; saves the checker the blend GEMM at BASELINE batch sizes)."""
     N = beta.shape[0]
     nv = m.size[0]
     dt = beta.dtype
     v_shaped = torch.matmul(beta, m.shapedirs).reshape(-1, nv, 3) + m.v_template
     J = torch.stack([torch.matmul(v_shaped[:, :, c], m.J_regressor) for c in range(3)], dim=2)
     Rs = batch_rodrigues(theta.reshape(-1, 3)).reshape(-1, 24, 3, 3)
+    if not want_verts:
+        J_transformed, A = batch_global_rigid_transformation(Rs, J, m.parents)
+        return {'J_transformed': J_transformed, 'Rs': Rs, 'A': A}
     pose_feature = (Rs[:, 1:] - torch.eye(3, dtype=dt)).reshape(-1, 207)
     v_posed = torch.matmul(pose_feature, m.posedirs).reshape(-1, nv, 3) + v_shaped
     J_transformed, A = batch_global_rigid_transformation(Rs, J, m.parents)

@@ -186,3 +186,37 @@ def test_mesh_fit_first_steps_match_oracle(gpu_model, synth_dd):
     assert maxrel(np.array(losses), np.array(want)) <= 1e-4
     assert maxrel(f.theta.cpu().numpy(), theta) <= 1e-4
     assert losses[-1] < losses[0]
+
+
+def test_baseline_config3_B4096_first_steps(gpu_model, synth_dd):
+    """BASELINE.json configs[2] at exactly B = 4096: the first 3 Adam steps of the re-projection fit against the float64
+    oracle trajectory (autograd gradients + TF1 Adam), oracle evaluated in chunks (samples are independent; only the
+    mean couples them)."""
+    B, steps, lr, chunk = 4096, 3, 1e-2, 512
+    m64 = rt.load_model(synth_dd, dtype=torch.float64)
+    inp = syn.make_inputs(B, seed=4096, dtype=np.float32)
+    tgt = syn.make_inputs(B, seed=4097, dtype=np.float32)
+    gt_px = gpu_model.forward(inp['beta'], tgt['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=4)['px'].cpu().numpy()
+    f = Fitter(gpu_model, inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], gt_px, focal=inp['focal'], lr=lr)
+    losses = [float(f.step()[0]) for _ in range(steps)]
+    theta = inp['theta'].astype(np.float64)
+    mt, vt = 0 * theta, 0 * theta
+    want = []
+    n_total = B * 48
+    for t in range(1, steps + 1):
+        g = np.zeros_like(theta)
+        tot = 0.0
+        for b0 in range(0, B, chunk):
+            sl = slice(b0, b0 + chunk)
+            th = _t64(theta[sl], True)
+            o = rt.smpl_forward(m64, _t64(inp['beta'][sl]), th, tile_W=False, want_verts=False)
+            _, px = rt.project_joints_px(o['J_transformed'], *[_t64(inp[k][sl]) for k in ('cam_pos', 'cam_rot', 'focal')])
+            part = ((px - _t64(gt_px[sl])) ** 2).sum() * (rt.CFG.ss / n_total)
+            part.backward()
+            g[sl] = th.grad.numpy()
+            tot += float(part.detach())
+        want.append(tot)
+        theta, mt, vt = rn.adam_tf1(theta, g, mt, vt, t, lr=lr)
+    assert maxrel(np.array(losses), np.array(want)) <= 1e-4
+    assert maxrel(f.theta.cpu().numpy(), theta) <= 1e-4
+    assert maxrel(f.theta.cpu().numpy() - inp['theta'], theta - inp['theta']) <= 1e-3

@@ -15,7 +15,8 @@ import smplb200
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
 GOLD = os.path.join(ROOT, 'tests', 'golden')
-BLENDS = [_lib.F_BLEND_SIMT | _lib.F_SKIN_SIMT, 0]   # CUDA-core verification kernels, tcgen05 kernels (f16 main product + bf16 corrections)
+# CUDA-core verification kernels, tcgen05 kernels (f16 main product + f16/bf16 corrections), fused single-kernel forward
+BLENDS = [_lib.F_BLEND_SIMT | _lib.F_SKIN_SIMT, 0, _lib.F_FUSED]
 
 
 def _check(out, o, px=None, tol=TOL):
@@ -264,3 +265,95 @@ def test_blend_split_precision(gpu_model, oracle64):
     out = gpu_model.forward(beta, theta, flags=0)
     o = rn.smpl_forward(oracle64, beta.astype(np.float64), theta.astype(np.float64), tile_W=False)
     assert maxrel(out['verts'].cpu().numpy(), o['verts']) <= 2e-6
+
+
+def _oracle_chunked(oracle64, inp, chunk=256):
+    """float64 oracle over a large batch in chunks (memory)."""
+    outs = []
+    for b0 in range(0, inp['beta'].shape[0], chunk):
+        f64 = {k: v[b0:b0 + chunk].astype(np.float64) for k, v in inp.items()}
+        o = rn.smpl_forward(oracle64, f64['beta'], f64['theta'], tile_W=False)
+        _, px = rn.project_joints_px(o['J_transformed'], f64['cam_pos'], f64['cam_rot'], f64['focal'])
+        outs.append((o['verts'], o['J_transformed'], o['joints'], px))
+    return [np.concatenate(x) for x in zip(*outs)]
+
+
+@pytest.mark.parametrize('flags', [0, _lib.F_FUSED])
+def test_baseline_config2_B1024_matches_oracle(gpu_model, oracle64, flags):
+    """BASELINE.json configs[1]: batched SMPL forward + perspective projection at exactly B = 1024, every sample against
+    the float64 oracle (the largest oracle-checked batch was 300)."""
+    B = 1024
+    inp = syn.make_inputs(B, seed=4242, dtype=np.float32)
+    out = gpu_model.forward(inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=flags,
+                            check_inputs=True)
+    verts, joints, kp, px = _oracle_chunked(oracle64, inp)
+    assert maxrel(out['verts'].cpu().numpy(), verts) <= TOL
+    assert maxrel(out['joints'].cpu().numpy(), joints) <= TOL
+    assert maxrel(out['kp'].cpu().numpy(), kp) <= TOL
+    assert maxrel(out['px'].cpu().numpy(), px) <= TOL
+
+
+def test_fused_forward_ragged_and_keypoints_only(gpu_model, oracle64):
+    """SMPLB_F_FUSED: batches that end inside a 96-sample chunk / a 4-sample T group, and the get_skin=False use
+    (keypoints without a verts buffer: the compact keypoint rows come from the fused epilogue)."""
+    for B in (1, 5, 97, 191, 200):
+        inp = syn.make_inputs(B, seed=77 + B, dtype=np.float32)
+        f64 = {k: v.astype(np.float64) for k, v in inp.items()}
+        o = rn.smpl_forward(oracle64, f64['beta'], f64['theta'], tile_W=False)
+        out = gpu_model.forward(inp['beta'], inp['theta'], flags=_lib.F_FUSED, out={})
+        assert maxrel(out['verts'].cpu().numpy(), o['verts']) <= TOL
+        assert maxrel(out['kp'].cpu().numpy(), o['joints']) <= TOL
+        out2 = gpu_model.forward(inp['beta'], inp['theta'], want_verts=False, flags=_lib.F_FUSED, out={})
+        assert 'verts' not in out2 or out2.get('verts') is None
+        assert maxrel(out2['kp'].cpu().numpy(), o['joints']) <= TOL
+    with pytest.raises(smplb200.SmplbError):      # the backward needs v_posed: not with the fused forward
+        gpu_model.forward(inp['beta'], inp['theta'], flags=_lib.F_FUSED | _lib.F_KEEP_VPOSED, out={})
+
+
+def test_input_range_check(gpu_model):
+    """|beta| beyond the fp16 range cannot be carried by the split-operand GEMMs: smplb_forward_status reports
+    SMPLB_E_NOT_FINITE instead of silently returning inf; in-range inputs pass."""
+    inp = syn.make_inputs(8, seed=3, dtype=np.float32)
+    gpu_model.forward(inp['beta'], inp['theta'], check_inputs=True)
+    bad = inp['beta'].copy()
+    bad[5, 2] = 1.0e5
+    with pytest.raises(smplb200.SmplbError) as e:
+        gpu_model.forward(bad, inp['theta'], check_inputs=True)
+    assert e.value.code == _lib.E_NOT_FINITE
+    th = inp['theta'].copy()
+    th[1, 7] = np.nan
+    with pytest.raises(smplb200.SmplbError) as e:
+        gpu_model.forward(inp['beta'], th, check_inputs=True)
+    assert e.value.code == _lib.E_NOT_FINITE
+    gpu_model.forward(inp['beta'], inp['theta'], check_inputs=True)      # the flag is cleared by the next call
+
+
+def test_tolerance_report(gpu_model, oracle64, oracle32):
+    """SURVEY 8c asks for three numbers side by side: the max-norm error (the acceptance criterion), the share of
+    elements inside |a-b| <= 1e-5 |b| + 1e-5 max|b|, and the error of the float32 restatement of the reference itself
+    (the floor).  Written to gpurun_out/tolerance_report.json (committed copy: profiles/r02_tolerance_report.json)."""
+    import json
+    B = 256
+    inp = syn.make_inputs(B, seed=99, dtype=np.float32)
+    f64 = {k: v.astype(np.float64) for k, v in inp.items()}
+    o64 = rn.smpl_forward(oracle64, f64['beta'], f64['theta'], tile_W=False)
+    _, px64 = rn.project_joints_px(o64['J_transformed'], f64['cam_pos'], f64['cam_rot'], f64['focal'])
+    o32 = rn.smpl_forward(oracle32, inp['beta'], inp['theta'], tile_W=False)
+    _, px32 = rn.project_joints_px(o32['J_transformed'], inp['cam_pos'], inp['cam_rot'], inp['focal'])
+    rep = {}
+    for name, fl in (('tcgen05 unfused', 0), ('tcgen05 fused', _lib.F_FUSED), ('CUDA-core verification', BLENDS[0])):
+        out = gpu_model.forward(inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], flags=fl, out={})
+        row = {}
+        for key, got, want, floor in (('verts', out['verts'], o64['verts'], o32['verts']),
+                                      ('J_transformed', out['joints'], o64['J_transformed'], o32['J_transformed']),
+                                      ('keypoints', out['kp'], o64['joints'], o32['joints']),
+                                      ('px', out['px'], px64, px32)):
+            a = got.cpu().numpy().astype(np.float64)
+            mixed = np.abs(a - want) <= 1e-5 * np.abs(want) + 1e-5 * np.abs(want).max()
+            row[key] = {'max_norm': maxrel(a, want), 'inside_rtol_atol': float(mixed.mean()),
+                        'fp32_restatement_max_norm': maxrel(floor, want)}
+            assert row[key]['max_norm'] <= TOL and row[key]['inside_rtol_atol'] == 1.0
+        rep[name] = row
+    os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
+    with open(os.path.join(ROOT, 'gpurun_out', 'tolerance_report.json'), 'w') as f:
+        json.dump({'B': B, 'criterion': 'max|a-b|/max|b| <= 1e-5; also |a-b| <= 1e-5|b| + 1e-5 max|b| per element', 'paths': rep}, f, indent=1)
