@@ -73,7 +73,8 @@ class Model:
                                    hp(self.weights), hp(self.joint_regressor), self.NK,
                                    hp(self.parents)))
         self._ws = None
-        self._ws_key = None
+        self._last = None          # (workspace data_ptr, B, flags) of the last forward: what a backward may rely on
+        self.n_forward_calls = 0   # smplb_forward launches made through this handle (tests count them)
 
     def close(self):
         if getattr(self, '_h', None) is not None and self._h.value:
@@ -142,14 +143,26 @@ class Model:
         with torch.cuda.device(dev):
             check(_lib.lib().smplb_forward(self._h, C.byref(io), _ptr(ws), ws.numel(), flags,
                                            _stream(dev)))
+            self.n_forward_calls += 1
+            self._last = (ws.data_ptr(), B, flags)
             if check_inputs:
                 check(_lib.lib().smplb_forward_status(_ptr(ws), _stream(dev)))
         out['_keep'] = (beta, theta, cam_pos, cam_rot, focal)
         return out
 
+    def new_workspace(self, B, flags):
+        """A workspace of its own for one forward (+ backward) call: several forward calls can then stay alive until
+        their backward runs (the reference's training step calls SMPL twice before differentiating,
+        pose_model_3d.py:177-192)."""
+        need = _lib.lib().smplb_workspace_bytes(self._h, B, flags)
+        return torch.empty(max(need, 256), dtype=torch.uint8, device=self.device)
+
     def backward(self, beta, theta, g_verts=None, g_joints=None, g_kp=None, g_px=None,
-                 cam_pos=None, cam_rot=None, focal=None, flags=0, cam_cfg=None):
-        """smplb_backward: needs the workspace of the matching forward(flags|F_KEEP_VPOSED)."""
+                 cam_pos=None, cam_rot=None, focal=None, flags=0, cam_cfg=None, ws=None):
+        """smplb_backward.  Vertex gradients (g_verts / g_kp) need the workspace of the matching
+        forward(flags | F_KEEP_VPOSED): pass it as `ws`, or leave ws=None to use the handle's cached workspace, which
+        is only accepted when the LAST forward through this handle filled it with the same batch and flags (a stale
+        or foreign workspace would silently give wrong gradients)."""
         dev = self.device
         beta = _dev_f32(beta, dev)
         theta = _dev_f32(theta, dev)
@@ -174,7 +187,15 @@ class Model:
                         _ptr(g_beta), _ptr(g_theta))
         if g_verts is not None or g_kp is not None:   # vertex path: needs the forward's workspace
             flags |= _lib.F_KEEP_VPOSED
-            ws, need = self.workspace(B, flags)
+            if ws is None:
+                ws = self._ws
+                if ws is None or self._last != (ws.data_ptr(), B, flags):
+                    raise RuntimeError(
+                        'Model.backward: the cached workspace does not hold the forward of this call (last forward: %r, '
+                        'wanted B=%d flags=%d incl. F_KEEP_VPOSED); run forward(flags | F_KEEP_VPOSED) right before, or '
+                        'give each call its own workspace (new_workspace / ws=)' % (self._last, B, flags))
+            if ws.numel() < _lib.lib().smplb_workspace_bytes(self._h, B, flags):
+                raise RuntimeError('Model.backward: workspace too small for B=%d flags=%d' % (B, flags))
             wsp, wsn = _ptr(ws), ws.numel()
         else:
             wsp, wsn = None, 0

@@ -16,8 +16,11 @@ class _SMPLFunction(torch.autograd.Function):
     def forward(ctx, beta, theta, model, flags):
         need_grad = beta.requires_grad or theta.requires_grad
         f = flags | (_lib.F_KEEP_VPOSED if need_grad else 0)
-        out = model.forward(beta, theta, want_verts=True, want_kp=True, want_Rs=True, flags=f)
-        ctx.model, ctx.flags = model, f
+        # every differentiable call keeps its own workspace (v_posed, A image) until its backward has run: the
+        # reference's training step calls SMPL twice before it differentiates (pose_model_3d.py:177-192)
+        ws = model.new_workspace(beta.shape[0], f) if need_grad else None
+        out = model.forward(beta, theta, want_verts=True, want_kp=True, want_Rs=True, flags=f, ws=ws, out={})
+        ctx.model, ctx.flags, ctx.ws = model, f, ws
         ctx.save_for_backward(out['_keep'][0], out['_keep'][1])
         ctx.mark_non_differentiable(out['Rs'])
         return out['verts'], out['kp'], out['Rs'], out['joints']
@@ -25,11 +28,9 @@ class _SMPLFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_verts, g_kp, g_Rs, g_joints):
         beta, theta = ctx.saved_tensors
-        # the workspace still holds this call's v_posed / A only if no other forward ran since;
-        # re-run the forward to make the backward self-contained (cheap relative to autograd use).
-        ctx.model.forward(beta, theta, want_verts=False, want_kp=False, want_Rs=False, flags=ctx.flags)
         g_beta, g_theta = ctx.model.backward(beta, theta, g_verts=g_verts, g_joints=g_joints,
-                                             g_kp=g_kp, flags=ctx.flags)
+                                             g_kp=g_kp, flags=ctx.flags, ws=ctx.ws)
+        ctx.ws = None      # release the call's workspace
         return g_beta, g_theta, None, None
 
 

@@ -166,3 +166,51 @@ def test_dropin_smpl_autograd(synth_dd, tmodel64, tmp_path):
     rt.loss3d(og['verts'], o['verts'], og['J_transformed'], o['J_transformed']).backward()
     assert maxrel(theta.grad.cpu().numpy(), t64.grad.numpy()) <= GTOL
     assert maxrel(beta.grad.cpu().numpy(), b64.grad.numpy()) <= GTOL
+
+
+def test_dropin_two_calls_then_one_backward(synth_dd, tmodel64, tmp_path):
+    """The reference's training step builds TWO SMPL calls before it differentiates (pose_model_3d.py:177-192). Both
+    calls keep their own workspace, so one backward through both needs no hidden extra forward: exactly two
+    smplb_forward launches, gradients of both calls vs the float64 autograd twin."""
+    from tf_smpl.batch_smpl import SMPL
+    path = str(tmp_path / 'm.pkl')
+    syn.write_pkl(path, synth_dd)
+    smpl = SMPL(path)
+    B = 5
+    a, b = syn.make_inputs(B, seed=11, dtype=np.float32), syn.make_inputs(B, seed=12, dtype=np.float32)
+    th1 = torch.tensor(a['theta'], device='cuda', requires_grad=True)
+    th2 = torch.tensor(b['theta'], device='cuda', requires_grad=True)
+    be = torch.tensor(a['beta'], device='cuda', requires_grad=True)
+    n0 = smpl._model.n_forward_calls
+    v1, _, _ = smpl(be, th1, get_skin=True)
+    j1 = smpl.J_transformed
+    v2, _, _ = smpl(be, th2, get_skin=True)          # second call: must not clobber what the first one kept
+    j2 = smpl.J_transformed
+    loss = 1.0 * torch.mean((v1 - v2) ** 2) + 2.0 * torch.mean((j1 - j2) ** 2)
+    loss.backward()
+    assert smpl._model.n_forward_calls - n0 == 2      # no re-run of the forward inside backward
+    b64, t1, t2 = _t64(a['beta'], True), _t64(a['theta'], True), _t64(b['theta'], True)
+    o1 = rt.smpl_forward(tmodel64, b64, t1, tile_W=False)
+    o2 = rt.smpl_forward(tmodel64, b64, t2, tile_W=False)
+    rt.loss3d(o2['verts'], o1['verts'], o2['J_transformed'], o1['J_transformed']).backward()
+    assert maxrel(th1.grad.cpu().numpy(), t1.grad.numpy()) <= GTOL
+    assert maxrel(th2.grad.cpu().numpy(), t2.grad.numpy()) <= GTOL
+    assert maxrel(be.grad.cpu().numpy(), b64.grad.numpy()) <= GTOL
+
+
+def test_backward_rejects_a_stale_workspace(gpu_model):
+    """Model.backward without an explicit workspace only accepts the cached one when the last forward filled it for
+    the same batch with F_KEEP_VPOSED (it used to reallocate silently and read garbage)."""
+    from smplb200 import _lib
+    inp = syn.make_inputs(4, seed=1, dtype=np.float32)
+    gv = np.ones((4, 6890, 3), np.float32)
+    gpu_model.forward(inp['beta'], inp['theta'])                       # no F_KEEP_VPOSED
+    with pytest.raises(RuntimeError):
+        gpu_model.backward(inp['beta'], inp['theta'], g_verts=gv)
+    gpu_model.forward(inp['beta'], inp['theta'], flags=_lib.F_KEEP_VPOSED)
+    gpu_model.forward(inp['beta'][:2], inp['theta'][:2], flags=_lib.F_KEEP_VPOSED)   # another batch in between
+    with pytest.raises(RuntimeError):
+        gpu_model.backward(inp['beta'], inp['theta'], g_verts=gv)
+    gpu_model.forward(inp['beta'], inp['theta'], flags=_lib.F_KEEP_VPOSED)
+    gb, gt = gpu_model.backward(inp['beta'], inp['theta'], g_verts=gv)
+    assert torch.isfinite(gt).all()
