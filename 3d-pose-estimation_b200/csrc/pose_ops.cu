@@ -262,3 +262,57 @@ extern "C" int32_t smplb_mse_grad(int64_t n, const float* pred, const float* tar
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
+
+// ---- allocation-free variant of smplb_cam_losses (no counterpart in the reference; added
+// for callers that cannot allocate device memory: CUDA graph capture, tight serving loops) ----------------
+// The per-block partial sums live in a file-scope device array instead of a caller-provided scratch buffer.  Every GPU
+// that loads the library holds the array (SMPLB_CAM_LOSSES_STATIC_MAX_B / 128 blocks x 3 floats + 16 B = 6 160 B) until
+// exit.  All calls on one device share it: calls that overlap on the GPU (different streams) race.
+#define SMPLB_CAM_STATIC_FLOATS ((SMPLB_CAM_LOSSES_STATIC_MAX_B / 128) * 3 + 4)
+static __device__ __align__(256) float g_cam_losses_scratch[SMPLB_CAM_STATIC_FLOATS];
+
+extern "C" int32_t smplb_cam_losses_static(int32_t B, const float* gt_joints3d, const float* gt_joints2d,
+                                           const float* cam_pos, const float* cam_rot, const float* cam_f,
+                                           const float* f_raw, const smplb_camcfg* cfg, float angle_scale,
+                                           float* loss_out, float* g_cam_pos, float* g_cam_rot, float* g_cam_f,
+                                           float* g_f_raw, void* stream) {
+  if (B < 0) return fail(SMPLB_E_BAD_SHAPE, "smplb_cam_losses_static: negative batch");
+  if (B > SMPLB_CAM_LOSSES_STATIC_MAX_B)
+    return fail(SMPLB_E_UNSUPPORTED, "smplb_cam_losses_static: B exceeds SMPLB_CAM_LOSSES_STATIC_MAX_B (" +
+                                         std::to_string(SMPLB_CAM_LOSSES_STATIC_MAX_B) +
+                                         "): the built-in scratch array is fixed; use smplb_cam_losses with a caller-owned scratch");
+  if (!cfg || !loss_out) return fail(SMPLB_E_INVALID_ARG, "smplb_cam_losses_static: null cfg or loss_out");
+  if (B == 0) return SMPLB_OK;
+  if (!gt_joints3d || !gt_joints2d || !cam_pos || !cam_rot || !cam_f)
+    return fail(SMPLB_E_INVALID_ARG, "smplb_cam_losses_static: null pointer");
+  if ((g_cam_pos == nullptr) != (g_cam_rot == nullptr))
+    return fail(SMPLB_E_INVALID_ARG, "smplb_cam_losses_static: g_cam_pos and g_cam_rot go together");
+  // In host code the array's name is only a stand-in: the device address is looked up once per device, with that
+  // device current (cudaGetSymbolAddress answers for the current device), and cached.
+  static std::mutex mu;
+  static float* addr[64] = {};
+  int dev = -1;
+  SMPLB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(SMPLB_E_UNSUPPORTED, "smplb_cam_losses_static: device index beyond 63");
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[dev]) {
+      void* p = nullptr;
+      SMPLB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_cam_losses_scratch));
+      addr[dev] = (float*)p;
+    }
+    scratch = addr[dev];
+  }
+  const int nb = (B + 127) / 128;
+  const float w_angle = angle_scale / (float)((long long)B * 24), w_neg = 1.0f / (float)((long long)B * 3),
+              w_rot = 10.0f / (float)B;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the previous call's partial sums: clear the part this call uses (stream-ordered, no allocation)
+  SMPLB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, (size_t)nb * 3 * sizeof(float), st));
+  cam_losses_kernel<<<nb, 128, 0, st>>>(B, gt_joints3d, gt_joints2d, cam_pos, cam_rot, cam_f, f_raw, *cfg, w_angle, w_neg,
+                                       w_rot, scratch, g_cam_pos, g_cam_rot, g_cam_f, g_f_raw);
+  cam_losses_finish_kernel<<<1, 32, 0, st>>>(nb, scratch, w_angle, w_neg, w_rot, loss_out);
+  SMPLB_CUDA_CHECK(cudaGetLastError());
+  return SMPLB_OK;
+}

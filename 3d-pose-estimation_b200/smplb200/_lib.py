@@ -111,6 +111,9 @@ SYMBOLS = {
     'smplb_cam_losses': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.POINTER(CamCfg), C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'smplb_cam_losses_static': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.POINTER(CamCfg), C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_mse_scratch_bytes': (C.c_size_t, []),
     'smplb_mse_grad': (C.c_int32, [C.c_int64, C.c_void_p, C.c_void_p, C.c_float, C.c_int64, C.c_void_p, C.c_void_p,
                                    C.c_int32, C.c_void_p, C.c_void_p]),

@@ -309,6 +309,19 @@ int32_t smplb_cam_losses(int32_t B, const float* gt_joints3d, const float* gt_jo
                          float angle_scale, float* loss_out, float* g_cam_pos, float* g_cam_rot, float* g_cam_f,
                          float* g_f_raw, void* scratch, void* stream);
 
+/* Allocation-free variant of smplb_cam_losses.  No counterpart in the reference: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same inputs, outputs and arithmetic as smplb_cam_losses, but the per-block
+ * partial sums live in a fixed device array inside the library (6 160 bytes, held by every GPU that loads the
+ * library until exit) instead of a caller-provided scratch buffer; the call allocates nothing.
+ * B > SMPLB_CAM_LOSSES_STATIC_MAX_B is rejected with SMPLB_E_UNSUPPORTED.  All calls on a device share the array:
+ * calls that may overlap on the GPU (different streams, concurrent graphs) race -- serialise them. */
+#define SMPLB_CAM_LOSSES_STATIC_MAX_B 65536
+int32_t smplb_cam_losses_static(int32_t B, const float* gt_joints3d, const float* gt_joints2d, const float* cam_pos,
+                                const float* cam_rot, const float* cam_f, const float* f_raw, const smplb_camcfg* cfg,
+                                float angle_scale, float* loss_out, float* g_cam_pos, float* g_cam_rot, float* g_cam_f,
+                                float* g_f_raw, void* stream);
+
 /* 3D losses of deps/pose_3d/pose_model_3d.py:183-192 (tf.losses.mean_squared_error with a scalar weight):
  * loss_out[0] (+)= weight * sum((pred - target)^2) / n_total, and, when g_out is given, its gradient w.r.t. pred,
  * g_out[i] = 2 * weight / n_total * (pred[i] - target[i]).  n_total = element count of the global mean (n, or the
