@@ -353,7 +353,9 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
       gy = s.g_vtot;
     }
     timing_mark_bwd(0, st);
-    rc = launch_skin_bwd_gA(m, B, gy, w.vposed, s.g_A, st);                 // g_A  = sum_v w (g_y (x) [v_posed;1])
+    // g_A = sum_v w (g_y (x) [v_posed;1]): tcgen05 reduction; SMPLB_F_SKIN_SIMT selects the CUDA-core verification kernel
+    rc = (flags & SMPLB_F_SKIN_SIMT) ? launch_skin_bwd_gA(m, B, gy, w.vposed, s.g_A, st)
+                                     : launch_skin_bwd_gA_tc(m, B, gy, w.vposed, s.g_A, st);
     if (rc != SMPLB_OK) return rc;
     timing_mark_bwd(1, st);
     rc = launch_skin_bwd_vposed(m, B, gy, w.Aimg, s.g_img, st);             // g_vp = T^T g_y  (operand image)

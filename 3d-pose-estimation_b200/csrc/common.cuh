@@ -123,6 +123,7 @@ struct smplb_model {
   int* kpc_tile_ptr;      // [SK_NVT+1] first compact slot of every vertex tile
   int* kpc_src;           // [kpv_pitch] float index 3*lv+c inside the tile's staged verts row, -1 = pad
   int* kpc_slot;          // [nnz] compact slot of the vertex of every regressor entry
+  float* Wimg3;           // bf16 split K-major image of the LBS weights for the tensor-core g_A reduction (skin_bwd_tc.cu)
   // fused forward (fused_fwd.cu)
   float* Dimg2;           // [FF_NHT][FF_DTILE x 16 bit] D rows of every half tile, f16 split (ff_dimg_off)
   float* Wimg2;           // [FF_NHT][FF_WHT x 16 bit] LBS weights, f16 split (ff_wimg_off)
@@ -347,6 +348,10 @@ int32_t launch_skin_bwd_vposed(const smplb_model* m, int B, const float* g_verts
                                cudaStream_t st);
 int32_t launch_skin_bwd_gA(const smplb_model* m, int B, const float* g_verts, const float* vposed, float* g_A,
                            cudaStream_t st);
+void build_wimg3(const float* weights, unsigned short* out);   // skin_bwd_tc.cu (host)
+size_t wimg3_elems();
+int32_t launch_skin_bwd_gA_tc(const smplb_model* m, int B, const float* g_verts, const float* vposed, float* g_A,
+                              cudaStream_t st);
 int32_t launch_gverts_total(const smplb_model* m, int B, const float* g_verts, const float* g_kp, float* out,
                             cudaStream_t st);
 // g_X partial sums: [n_slices][B][KPAD]; returns the slice count through *n_slices

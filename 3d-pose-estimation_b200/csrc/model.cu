@@ -253,6 +253,8 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
       }
     }
   }
+  std::vector<unsigned short> Wimg3(wimg3_elems(), 0);
+  build_wimg3(weights, Wimg3.data());
   std::vector<float> vt_plain(v_template, v_template + NV3);
   std::vector<int> cslot_of(NV3, -1);   // (vertex, component) -> compact keypoint slot
   for (int t = 0; t < SK_NVT; ++t)
@@ -291,6 +293,11 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->kpc_tile_ptr, ctile));
   chk(upload(&m->kpc_src, csrc));
   chk(upload(&m->kpc_slot, cslot));
+  {
+    unsigned short* d = nullptr;
+    chk(upload(&d, Wimg3));
+    m->Wimg3 = reinterpret_cast<float*>(d);
+  }
   chk(upload(&m->Dimg2, Dimg2));
   chk(upload(&m->Wimg2, Wimg2));
   chk(upload(&m->vt_plain, vt_plain));
@@ -326,6 +333,7 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->kpc_tile_ptr);
   cudaFree(m->kpc_src);
   cudaFree(m->kpc_slot);
+  cudaFree(m->Wimg3);
   cudaFree(m->Dimg2);
   cudaFree(m->Wimg2);
   cudaFree(m->vt_plain);

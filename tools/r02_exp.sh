@@ -1,2 +1,7 @@
 #!/bin/bash
-for d in 63 127 191 255; do echo "DBG=$d"; SMPLB_DBG=$d FF_TIME=65536 python tools/ff_check.py 8 2>&1 | grep "fused forward"; done
+for d in 0 1 2 3; do
+SMPLB_DBG=$d python bench.py --mode sweep --sweep-min 65536 --steps 10 --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.read())
+r=d['rows'][-1]; print('DBG=$d', {k: round(v,3) for k,v in r.get('kernel_ms_bwd_rank0',{}).items()})"
+done
