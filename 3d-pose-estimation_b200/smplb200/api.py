@@ -189,7 +189,9 @@ class Model:
             flags |= _lib.F_KEEP_VPOSED
             if ws is None:
                 ws = self._ws
-                if ws is None or self._last != (ws.data_ptr(), B, flags):
+                layout = _lib.F_KEEP_VPOSED | _lib.F_NO_SKIN | _lib.F_SCRATCH_VERTS | _lib.F_FUSED   # what shapes the workspace
+                if ws is None or self._last is None or self._last[:2] != (ws.data_ptr(), B) or \
+                        (self._last[2] & layout) != (flags & layout):
                     raise RuntimeError(
                         'Model.backward: the cached workspace does not hold the forward of this call (last forward: %r, '
                         'wanted B=%d flags=%d incl. F_KEEP_VPOSED); run forward(flags | F_KEEP_VPOSED) right before, or '
