@@ -3,7 +3,8 @@
 Host-side I/O (scipy.io), mirroring the annotation half of read_maps_poses_images_surreal
 (deps/pose_3d/data_helpers.py:43-89): `pose [72,T]`, `shape [10,T]`, `joints2D [2,24,T]`, `zrot [T,1]` -> arrays with
 time first, the horizontal flip of the 2D ground truth (:66-67), the validity mask and the every-2nd-frame
-subsampling (:80-87).  The heat-map / JPEG half of that function feeds the CNN encoder and is out of scope.
+subsampling (:80-87).  The heat-map / JPEG half of that function (`read_maps_frames_surreal`) is the CNN encoder's
+input: it is read for completeness of the reader but nothing here processes it (the encoder is out of scope).
 `gt_batch` then runs what the reference's graph does with these annotations before the losses
 (pose_model_3d.py:371-372 rotate_global_pose, :177-181 SMPL) on the kernels."""
 import numpy as np
@@ -27,6 +28,41 @@ def read_maps_mask_surreal(maps_file):
         if name == 'heat_mat':
             w = int(shape[1])
     return mask, w
+
+
+# left/right swap of the 19 heat-map channels for the mirrored SURREAL images (data_helpers.py:53)
+SURREAL_REORDER = [0, 1, 5, 6, 7, 2, 3, 4, 11, 12, 13, 8, 9, 10, 15, 14, 17, 16, 18]
+
+
+def read_maps_frames_surreal(maps_file, frames_path, n_joints=14, mask=None, skip=2):
+    """The heat-map / frame half of read_maps_poses_images_surreal (data_helpers.py:44-57,70-87): heat maps
+    [T,H,W,n_joints] (time first, mirrored horizontally, left/right channels swapped) concatenated with the RGB frames
+    `f*.jpg` of `frames_path` (sorted; each min-max normalised to [0,1] like cv2.normalize(NORM_MINMAX); mirrored), then
+    the same `x[mask]` / every-`skip`-th-frame selection as the annotations.  This is the CNN encoder's input -- host
+    I/O only, decoded with OpenCV when it is installed, else PIL."""
+    import glob
+    import os
+    import scipy.io
+    heat = np.transpose(scipy.io.loadmat(maps_file, variable_names=['heat_mat'])['heat_mat'], (3, 0, 1, 2))   # :46
+    heat = np.flip(heat, axis=2)[:, :, :, SURREAL_REORDER][:, :, :, :n_joints]                                  # :50-56
+    fp = frames_path.decode('utf-8') if isinstance(frames_path, bytes) else frames_path
+    files = sorted(glob.glob(os.path.join(fp, 'f*.jpg')))                                                      # :71
+    try:
+        import cv2
+        frames = [cv2.cvtColor(cv2.imread(f), cv2.COLOR_BGR2RGB) for f in files]
+    except ImportError:
+        from PIL import Image
+        frames = [np.array(Image.open(f).convert('RGB')) for f in files]
+    frames = np.array(frames, dtype=np.float32)                                                                 # :73
+    norm = []
+    for fr in frames:                                                                                           # :74-75
+        lo, hi = fr.min(), fr.max()
+        norm.append((fr - lo) / max(float(hi - lo), 1e-12))
+    frames = np.flip(norm, axis=2)                                                                              # :77
+    concat = np.concatenate([heat, frames], axis=3)                                                             # :79
+    if mask is not None:
+        concat = concat[np.asarray(mask)]                                                                       # :81
+    return np.ascontiguousarray(concat[::skip], dtype=np.float32)                                               # :85
 
 
 def read_info_surreal(info_file, img_size_x=320, mask=None, skip=2):

@@ -685,3 +685,87 @@ def enable_eager_execution(*a, **k):
 
 keras = types.ModuleType('tensorflow.keras')
 test = types.SimpleNamespace(TestCase=object, main=lambda: None)
+
+
+# ---- tf.train.Example parsing (pose_3d/data_helpers.py:92-119 read_tfrecord_h36m) -----------------------------------
+# TensorFlow documents tf.parse_single_example(serialized, {key: FixedLenFeature(shape, dtype)}) as: decode the
+# tf.train.Example protobuf, return every requested feature reshaped to `shape`.  The decoding here is done by the
+# OFFICIAL protobuf runtime on the published schema (tensorflow/core/example/{example,feature}.proto), built as dynamic
+# messages -- deliberately not by the product's own wire-format parser (smplb200/h36m.py), which this pins.
+class FixedLenFeature:
+    def __init__(self, shape, dtype, default_value=None):
+        self.shape, self.dtype, self.default_value = list(shape), dtype, default_value
+
+
+def example_proto_classes():
+    """(Example, Features, Feature) message classes of the public tf.train.Example schema."""
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+    fd = descriptor_pb2.FileDescriptorProto(name='smplb_tf_example.proto', package='tensorflow', syntax='proto3')
+    T = descriptor_pb2.FieldDescriptorProto
+
+    def msg(name):
+        m = fd.message_type.add()
+        m.name = name
+        return m
+
+    def field(m, name, number, ftype, label=T.LABEL_OPTIONAL, type_name=None, oneof=None):
+        f = m.field.add()
+        f.name, f.number, f.type, f.label = name, number, ftype, label
+        if type_name:
+            f.type_name = type_name
+        if oneof is not None:
+            f.oneof_index = oneof
+        return f
+
+    field(msg('BytesList'), 'value', 1, T.TYPE_BYTES, T.LABEL_REPEATED)
+    field(msg('FloatList'), 'value', 1, T.TYPE_FLOAT, T.LABEL_REPEATED)      # proto3: packed
+    field(msg('Int64List'), 'value', 1, T.TYPE_INT64, T.LABEL_REPEATED)
+    ft = msg('Feature')
+    ft.oneof_decl.add().name = 'kind'
+    field(ft, 'bytes_list', 1, T.TYPE_MESSAGE, type_name='.tensorflow.BytesList', oneof=0)
+    field(ft, 'float_list', 2, T.TYPE_MESSAGE, type_name='.tensorflow.FloatList', oneof=0)
+    field(ft, 'int64_list', 3, T.TYPE_MESSAGE, type_name='.tensorflow.Int64List', oneof=0)
+    fs = msg('Features')
+    entry = fs.nested_type.add()
+    entry.name = 'FeatureEntry'
+    entry.options.map_entry = True
+    field(entry, 'key', 1, T.TYPE_STRING)
+    field(entry, 'value', 2, T.TYPE_MESSAGE, type_name='.tensorflow.Feature')
+    field(fs, 'feature', 1, T.TYPE_MESSAGE, T.LABEL_REPEATED, type_name='.tensorflow.Features.FeatureEntry')
+    field(msg('Example'), 'features', 1, T.TYPE_MESSAGE, type_name='.tensorflow.Features')
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(fd)
+    get = lambda n: message_factory.GetMessageClass(pool.FindMessageTypeByName('tensorflow.' + n))
+    return get('Example'), get('Features'), get('Feature')
+
+
+def parse_single_example(serialized, features, name=None, example_names=None):
+    Example, _, _ = example_proto_classes()
+    ex = Example()
+    ex.ParseFromString(bytes(serialized))
+    out = {}
+    for key, spec in features.items():
+        if key not in ex.features.feature:
+            raise ValueError('feature %r missing from the Example' % key)
+        f = ex.features.feature[key]
+        kind = f.WhichOneof('kind')
+        vals = list(getattr(f, kind).value)
+        n = int(np.prod(spec.shape)) if spec.shape else 1
+        if len(vals) != n:
+            raise ValueError('feature %r: %d values, FixedLenFeature wants %d' % (key, len(vals), n))
+        if spec.dtype == string:
+            out[key] = vals[0] if not spec.shape else np.array(vals, dtype=object)
+        elif kind == 'int64_list':
+            out[key] = Tensor(torch.tensor(vals, dtype=torch.int64).reshape(spec.shape))
+        else:
+            out[key] = Tensor(torch.tensor(vals, dtype=torch.float32).reshape(spec.shape))
+    return out
+
+
+def _decode_jpeg(contents, channels=0, **kw):
+    import io
+    from PIL import Image
+    return Tensor(torch.from_numpy(np.array(Image.open(io.BytesIO(bytes(contents))))))
+
+
+image = types.SimpleNamespace(decode_jpeg=_decode_jpeg)

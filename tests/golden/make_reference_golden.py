@@ -253,7 +253,7 @@ def make_surreal(pkl):
     info = os.path.join(rr.REF, 'data', 'images', '01_11_c0001_info.mat')
     T = scipy.io.loadmat(info)['pose'].shape[1]
     r = np.random.default_rng(77)
-    H, W = 24, 32
+    H, W = 6, 8        # small: the whole concat output is stored
     mask = (r.uniform(size=(T, 1)) < 0.8).astype(np.uint8)
     diffs = r.uniform(0, 300, size=(T, 1))
     diffs[r.integers(0, T, 7)] = np.nan
@@ -264,12 +264,71 @@ def make_surreal(pkl):
     os.mkdir(frames)
     for t in range(T):
         Image.fromarray(r.integers(0, 255, (H, W, 3), dtype=np.uint8)).save(os.path.join(frames, 'f%04d.jpg' % t))
+    jpeg = [open(os.path.join(frames, 'f%04d.jpg' % t), 'rb').read() for t in range(T)]
+    heat_mat = scipy.io.loadmat(maps)['heat_mat']
     with np.errstate(invalid='ignore'):
         concat, poses, shapes, joints2d, zrot = ns.data_helpers.read_maps_poses_images_surreal(
             maps, info, frames.encode('utf-8'))
     print('surreal', concat.shape, poses.shape, joints2d.dtype, zrot.shape)
     np.savez_compressed(os.path.join(OUT, 'reference_surreal.npz'), mask=mask, diffs=diffs, img_size_x=W,
-                        poses=poses, shapes=shapes, joints2d=joints2d, zrot=zrot)
+                        poses=poses, shapes=shapes, joints2d=joints2d, zrot=zrot, concat=concat, heat_mat=heat_mat,
+                        jpeg_blob=np.frombuffer(b''.join(jpeg), dtype=np.uint8),
+                        jpeg_len=np.array([len(j) for j in jpeg], dtype=np.int64))
+
+
+def make_h36m(pkl):
+    """pose_3d/data_helpers.py:92-131: the reference's read_tfrecord_h36m / read_maps_h36m / concat_img_heatmaps_h36m run
+    on a synthetic HMR-style TFRecord.  The Examples are serialised by the official protobuf runtime (dynamic messages
+    on the public tf.train.Example schema, oracle/tfshim), which also serves tf.parse_single_example for the reference
+    code; the record framing (length + masked CRC-32C) is written by smplb200.h36m.write_tfrecord."""
+    import io
+    from PIL import Image
+    cv2 = types.ModuleType('cv2')
+    ns = rr.load(float64=False, cv2=cv2)
+    tf = ns.tf
+    Example, _, _ = tf.example_proto_classes()
+    from smplb200 import h36m
+    r = np.random.default_rng(36)
+    N, H, W = 6, 10, 12
+    recs, fields = [], []
+    for i in range(N):
+        buf = io.BytesIO()
+        Image.fromarray(r.integers(0, 255, (H, W, 3), dtype=np.uint8)).save(buf, format='JPEG')
+        f = {'image/center': r.integers(0, 300, 2), 'image/encoded': [buf.getvalue()],
+             'image/filename': [b'S1_Directions_%d.jpg' % i], 'image/format': [b'JPEG'], 'image/height': [H],
+             'image/visibility': r.integers(0, 2, 14), 'image/width': [W],
+             'image/x': r.uniform(0, W, 14).astype(np.float32), 'image/y': r.uniform(0, H, 14).astype(np.float32),
+             'meta/crop_pt': r.integers(-50, 50, 2), 'meta/has_3d': [1],
+             'meta/scale_factors': r.uniform(0.5, 2, 2).astype(np.float32),
+             'mosh/gt3d': r.normal(size=42).astype(np.float32), 'mosh/pose': r.normal(0, 0.4, 72).astype(np.float32),
+             'mosh/shape': r.normal(size=10).astype(np.float32)}
+        ex = Example()
+        for k, v in f.items():
+            ft = ex.features.feature[k]
+            if isinstance(v[0], (bytes, bytearray)):
+                ft.bytes_list.value.extend(v)
+            elif np.asarray(v).dtype.kind == 'f':
+                ft.float_list.value.extend([float(x) for x in v])
+            else:
+                ft.int64_list.value.extend([int(x) for x in v])
+        recs.append(ex.SerializeToString())
+        fields.append(f)
+    tmp = tempfile.mkdtemp()
+    path = os.path.join(tmp, 'h36m.tfrecord')
+    h36m.write_tfrecord(path, recs)
+    imgs, poses, shapes, j2d = [], [], [], []
+    for rec in recs:
+        img, p, s, j = ns.data_helpers.read_tfrecord_h36m(rec)          # the reference function, unmodified
+        imgs.append(tf._raw(img).numpy()); poses.append(tf._raw(p).numpy()); shapes.append(tf._raw(s).numpy())
+        j2d.append(tf._raw(j).numpy())
+    import scipy.io
+    maps = os.path.join(tmp, 'maps.mat')
+    scipy.io.savemat(maps, dict(heat_mat=r.uniform(size=(H, W, 19, N)).astype(np.float32)))
+    heat = ns.data_helpers.read_maps_h36m(maps)
+    print('h36m', np.stack(poses).shape, np.stack(j2d).shape, heat.shape, np.stack(imgs).shape)
+    np.savez_compressed(os.path.join(OUT, 'reference_h36m.npz'), tfrecord=np.frombuffer(open(path, 'rb').read(), dtype=np.uint8),
+                        poses=np.stack(poses), shapes=np.stack(shapes), joints2d=np.stack(j2d), imgs=np.stack(imgs),
+                        heat_mat=scipy.io.loadmat(maps)['heat_mat'], heatmaps=heat)
 
 
 def main():
@@ -278,9 +337,9 @@ def main():
     pkl = os.path.join(tempfile.mkdtemp(), 'synthetic_smpl_seed0.pkl')
     with open(pkl, 'wb') as f:
         pickle.dump(syn.make_synthetic_smpl(0), f)
-    which = sys.argv[1:] or ['smpl', 'losses', 'utils', 'surreal']
+    which = sys.argv[1:] or ['smpl', 'losses', 'utils', 'surreal', 'h36m']
     for w in which:
-        {'smpl': make_smpl, 'losses': make_losses, 'utils': make_utils, 'surreal': make_surreal}[w](pkl)
+        {'smpl': make_smpl, 'losses': make_losses, 'utils': make_utils, 'surreal': make_surreal, 'h36m': make_h36m}[w](pkl)
 
 
 if __name__ == '__main__':
