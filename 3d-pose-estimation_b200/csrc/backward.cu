@@ -27,14 +27,20 @@ struct JointBwdParams {
   float* g_theta;
   smplb_camcfg cfg;
   Tree tree;
+  // fused fitting step (fit.cu): when gt_px is given the kernel forms the re-projection residual itself --
+  // g_px = px_coef * (px - gt_px), px written to px_out, sum of squared residuals of the block to partial[blockIdx]
+  // (fixed order) -- so pose_prep and reproj_grad need not run (this kernel recomputes the forward chain anyway)
+  const float* gt_px;      // [B,24,2] nullable
+  float px_coef;
+  float* px_out;           // [B,24,2] nullable
+  float* g_px_out;         // [B,24,2] nullable
+  double* partial;         // [gridDim.x]
 };
 
 constexpr int JB_WARPS = 4;
 
-__global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwdParams p) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * JB_WARPS + warp;
-  if (b >= p.B) return;
+// one sample per warp, lane = joint
+__device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const int b, const int lane, double* sq_out) {
   const int j = lane < NJ ? lane : 0;
   const bool act = lane < NJ;
   const unsigned FULL = 0xffffffffu;
@@ -89,9 +95,11 @@ __global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwd
     const float* g = p.g_joints + ((size_t)b * NJ + j) * 3;
     gJt[0] = g[0]; gJt[1] = g[1]; gJt[2] = g[2];
   }
-  if (act && p.g_px) {
+  const bool fused_px = p.gt_px != nullptr;
+  float sq = 0.f;
+  if (act && (p.g_px || fused_px)) {
     // px = uv / ss * H + off (pose_model_3d.py:229-231); camera held constant (:218-221)
-    const float2 gp = reinterpret_cast<const float2*>(p.g_px)[(size_t)b * NJ + j];
+    float2 gp = p.g_px ? reinterpret_cast<const float2*>(p.g_px)[(size_t)b * NJ + j] : make_float2(0.f, 0.f);
     const float sc = p.cfg.img_h / p.cfg.ss;
     const float* cp = p.cam_pos + (size_t)b * 3;
     const float* cr = p.cam_rot + (size_t)b * 3;
@@ -99,9 +107,26 @@ __global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwd
     float Rc[9], q[3], u, v, gq[3];
     rodrigues_cam(__ldg(cr), __ldg(cr + 1), __ldg(cr + 2), Rc);
     project_point(Rc, Gt[0], Gt[1], Gt[2], __ldg(cp), __ldg(cp + 1), __ldg(cp + 2), f, u, v, q);
+    if (fused_px) {
+      // the re-projection residual of the fitting step, formed here (pose_model_3d.py:229-235)
+      float pxx, pxy;
+      to_pixels(u, v, p.cfg, pxx, pxy);
+      const float2 gt = reinterpret_cast<const float2*>(p.gt_px)[(size_t)b * NJ + j];
+      const float dx = pxx - gt.x, dy = pxy - gt.y;
+      gp = make_float2(p.px_coef * dx, p.px_coef * dy);
+      sq = dx * dx + dy * dy;
+      if (p.px_out) reinterpret_cast<float2*>(p.px_out)[(size_t)b * NJ + j] = make_float2(pxx, pxy);
+      if (p.g_px_out) reinterpret_cast<float2*>(p.g_px_out)[(size_t)b * NJ + j] = gp;
+    }
     project_bwd_q(q, f, gp.x * sc, gp.y * sc, gq);
 #pragma unroll
     for (int r = 0; r < 3; ++r) gJt[r] += Rc[r * 3] * gq[0] + Rc[r * 3 + 1] * gq[1] + Rc[r * 3 + 2] * gq[2];
+  }
+
+  if (fused_px) {
+    double sd = (double)sq;   // fixed-order warp tree -> the block's partial sum
+    for (int o = 16; o > 0; o >>= 1) sd += __shfl_xor_sync(FULL, sd, o);
+    if (lane == 0) *sq_out = sd;
   }
 
   // ---- A -> G adjoint: A.R = G.R, A.t = G.t - G.R J (batch_lbs.py:138-142) ----
@@ -221,6 +246,26 @@ __global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwd
   }
 }
 
+__global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwdParams p) {
+  __shared__ double sq_sum[JB_WARPS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * JB_WARPS + warp;
+  if (p.gt_px) {
+    // fused fitting step: every warp of the block takes part in the loss partial sum (no early exit)
+    if (lane == 0) sq_sum[warp] = 0.0;
+    __syncthreads();
+  }
+  if (b < p.B) joint_bwd_sample(p, b, lane, sq_sum + warp);
+  if (p.gt_px) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double sacc = 0.0;
+      for (int w = 0; w < JB_WARPS; ++w) sacc += sq_sum[w];
+      p.partial[blockIdx.x] = sacc;
+    }
+  }
+}
+
 // project() adjoint (project.py:7-48) wrt points and camera position / rotation.  Thread per camera
 // group: loops over its P points so the per-camera sums have a fixed order.
 __global__ void project_bwd_kernel(int N, int P, const float* __restrict__ pts, const float* __restrict__ cpos,
@@ -293,9 +338,13 @@ static BwdScratch carve_bwd(void* base, int B) {
 
 size_t backward_scratch_bytes(int B) { return carve_bwd(nullptr, B).total; }
 
-int32_t launch_joint_bwd_px(const smplb_model* m, int B, const float* beta, const float* theta, const float* g_px,
-                            const float* cam_pos, const float* cam_rot, const float* focal, const smplb_camcfg& cfg,
-                            float* g_beta, float* g_theta, cudaStream_t st) {
+// The fused fitting step on the 2D re-projection loss (fit.cu): forward chain + projection + residual + backward chain in
+// ONE per-sample kernel.  px / g_px are written for the caller; partial[i] = sum of squared pixel residuals of block i.
+int fit_fused_blocks(int B) { return (B + JB_WARPS - 1) / JB_WARPS; }
+int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const float* theta, const float* gt_px,
+                         float px_coef, const float* cam_pos, const float* cam_rot, const float* focal,
+                         const smplb_camcfg& cfg, float* px, float* g_px, double* partial, float* g_beta, float* g_theta,
+                         cudaStream_t st) {
   JointBwdParams p;
   p.B = B;
   p.beta = beta;
@@ -303,7 +352,7 @@ int32_t launch_joint_bwd_px(const smplb_model* m, int B, const float* beta, cons
   p.Jbar = m->Jbar;
   p.JS = m->JS;
   p.g_joints = nullptr;
-  p.g_px = g_px;
+  p.g_px = nullptr;
   p.cam_pos = cam_pos;
   p.cam_rot = cam_rot;
   p.focal = focal;
@@ -314,7 +363,12 @@ int32_t launch_joint_bwd_px(const smplb_model* m, int B, const float* beta, cons
   p.g_theta = g_theta;
   p.cfg = cfg;
   p.tree = m->tree;
-  joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
+  p.gt_px = gt_px;
+  p.px_coef = px_coef;
+  p.px_out = px;
+  p.g_px_out = g_px;
+  p.partial = partial;
+  joint_bwd_kernel<<<fit_fused_blocks(B), JB_WARPS * 32, 0, st>>>(p);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
@@ -385,6 +439,7 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   p.g_theta = io->g_theta;
   p.cfg = io->cfg;
   p.tree = m->tree;
+  p.gt_px = nullptr; p.px_coef = 0.f; p.px_out = nullptr; p.g_px_out = nullptr; p.partial = nullptr;
   joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   if (vertex_path) timing_mark_bwd(4, st);

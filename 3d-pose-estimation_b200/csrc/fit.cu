@@ -1,8 +1,10 @@
 // One step of iterative SMPL fitting on the 2D re-projection loss (BASELINE config 3; loss block
 // pose_model_3d.py:194-238, optimiser :393-401) with per-sample pose (and optionally shape) as the Adam
 // variables.  Joint-only path: no vertices are touched.
-//   pose_prep (forward + projection) -> reproj_grad (dL/dpx, loss partial sums) -> loss_finish (mean, cap gate)
-//   -> joint_bwd (hand-written adjoint) -> Adam (TF1 formula, gradient gated by the cap like tf.minimum)
+//   fit_fused (joint_bwd_kernel with the residual formed inside: forward chain + projection + dL/dpx + loss partial sums +
+//   hand-written adjoint, one warp per sample) -> loss_finish (mean, cap gate, Adam's lr_t) -> Adam (TF1 formula,
+//   gradient gated by the cap like tf.minimum).  Round 1 ran pose_prep -> reproj_grad -> loss_finish -> joint_bwd -> Adam:
+//   joint_bwd recomputes the forward chain anyway, so the two extra kernels (and their launches) were pure overhead.
 // All launches are stream-ordered and allocation-free, so a caller can capture the step in a CUDA graph: with
 // smplb_fit_io.step_dev the step counter lives on the device (loss_finish increments it and derives Adam's lr_t from
 // it), so every replay of the captured step advances the bias correction like an eager step does.
@@ -10,9 +12,11 @@
 
 namespace smplb {
 
-int32_t launch_joint_bwd_px(const smplb_model* m, int B, const float* beta, const float* theta, const float* g_px,
-                            const float* cam_pos, const float* cam_rot, const float* focal, const smplb_camcfg& cfg,
-                            float* g_beta, float* g_theta, cudaStream_t st);
+int fit_fused_blocks(int B);
+int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const float* theta, const float* gt_px,
+                         float px_coef, const float* cam_pos, const float* cam_rot, const float* focal,
+                         const smplb_camcfg& cfg, float* px, float* g_px, double* partial, float* g_beta, float* g_theta,
+                         cudaStream_t st);
 
 constexpr int RG_THREADS = 256;
 
@@ -120,7 +124,8 @@ extern "C" int32_t smplb_adam_step_dev(int64_t n, float* x, const float* g, floa
 
 extern "C" size_t smplb_fit_scratch_bytes(int32_t B) {
   const size_t n = (size_t)(B > 0 ? B : 0) * NJ * 2;
-  return ((n + RG_THREADS - 1) / RG_THREADS) * sizeof(double) + 256;
+  const size_t a = (n + RG_THREADS - 1) / RG_THREADS, b = (size_t)fit_fused_blocks(B > 0 ? B : 0);
+  return (a > b ? a : b) * sizeof(double) + 256;
 }
 
 extern "C" int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, void* stream) {
@@ -142,41 +147,17 @@ extern "C" int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, 
                                      "fit sharded batches uncapped or gate on the all-reduced loss in the caller)");
   cudaStream_t st = (cudaStream_t)stream;
   const int B = io->B;
-  PrepParams p;
-  p.B = B;
-  p.beta = io->beta;
-  p.theta = io->theta;
-  p.Jbar = m->Jbar;
-  p.JS = m->JS;
-  p.Ximg = nullptr;
-  p.Ximg2 = nullptr;
-  p.Aimg2 = nullptr;
-  p.status = nullptr;
-  p.joints = nullptr;
-  p.Rs = nullptr;
-  p.A = nullptr;
-  p.Aimg = nullptr;
-  p.cam_pos = io->cam_pos;
-  p.cam_rot = io->cam_rot;
-  p.focal = io->focal;
-  p.uv = nullptr;
-  p.px = io->px;
-  p.cfg = io->cfg.cam;
-  p.tree = m->tree;
-  int32_t rc = launch_pose_prep(p, st);
-  if (rc != SMPLB_OK) return rc;
-  const int n = B * NJ * 2;
-  const int nblocks = (n + RG_THREADS - 1) / RG_THREADS;
+  const int nblocks = fit_fused_blocks(B);
   double* partial = (double*)io->scratch;
   const double inv_n = 1.0 / (double)io->n_total;
-  reproj_grad_kernel<<<nblocks, RG_THREADS, 0, st>>>(n, io->px, io->gt_px, (float)(2.0 * io->cfg.reproj_scale * inv_n),
-                                                    io->g_px, partial);
+  // g_px = 2 * scale / n_total * (px - gt)   (d/dpx of scale * mean((gt - px)^2), pose_model_3d.py:233-235)
+  int32_t rc = launch_fit_fused(m, B, io->beta, io->theta, io->gt_px, (float)(2.0 * io->cfg.reproj_scale * inv_n),
+                                io->cam_pos, io->cam_rot, io->focal, io->cfg.cam, io->px, io->g_px, partial, io->g_beta,
+                                io->g_theta, st);
+  if (rc != SMPLB_OK) return rc;
   loss_finish_kernel<<<1, 256, 0, st>>>(nblocks, partial, io->cfg.reproj_scale, inv_n, io->cfg.reproj_cap, io->loss,
                                         io->step_dev, io->step, io->lr, io->beta1, io->beta2);
   SMPLB_CUDA_CHECK(cudaGetLastError());
-  rc = launch_joint_bwd_px(m, B, io->beta, io->theta, io->g_px, io->cam_pos, io->cam_rot, io->focal, io->cfg.cam,
-                           io->g_beta, io->g_theta, st);
-  if (rc != SMPLB_OK) return rc;
   const int64_t nt = (int64_t)B * NJ * 3;
   adam_gated_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(nt, io->theta, io->g_theta, io->m_theta, io->v_theta,
                                                                   io->loss + 2, io->loss + 3, io->beta1, io->beta2, io->eps);
