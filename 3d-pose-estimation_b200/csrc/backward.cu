@@ -26,7 +26,8 @@ struct JointBwdParams {
   float* g_beta;
   float* g_theta;
   smplb_camcfg cfg;
-  Tree tree;
+  const int4* tree_tab;   // smplb_model::tree_tab: per lane {order, sub, up0, up1 | up2, up3, up4, -}
+  int n_rounds;
   // fused fitting step (fit.cu): when gt_px is given the kernel forms the re-projection residual itself --
   // g_px = px_coef * (px - gt_px), px written to px_out, sum of squared residuals of the block to partial[blockIdx]
   // (fixed order) -- so pose_prep and reproj_grad need not run (this kernel recomputes the forward chain anyway)
@@ -39,11 +40,24 @@ struct JointBwdParams {
 
 constexpr int JB_WARPS = 4;
 
-// one sample per warp, lane = joint
+// One sample per warp.  Lane l holds joint order[l], the joints in depth-first PRE-order (Tree::order), so the subtree of
+// a joint is the contiguous lane range [l, l + sub[l]).  That turns both chains into log-depth warp operations:
+//   forward   G_i = L_root ... L_i with L_m = (R_m, J_m - J_parent(m)) by pointer jumping: round r composes every joint
+//             with its 2^r-th ancestor (Tree::up[r]); ceil(log2(depth+1)) = 4 rounds for SMPL instead of 8 levels
+//   backward  with the own gradients gGR_k, gGt_k of every joint (dL/dG_k when G_k is held independent), the chain rule
+//             through G_k.R = G_i.R rel_k, G_k.t = G_i.R l_k + G_i.t for every descendant k of i collapses to
+//               dL/dG_i.R = [ sum_k (gGR_k G_k.R^T + gGt_k G_k.t^T)  -  (sum_k gGt_k) G_i.t^T ] G_i.R ,  dL/dG_i.t = sum_k gGt_k
+//             (k over the subtree of i, i included): 12 subtree sums per joint = range sums over contiguous lanes (a
+//             doubling table of 5 rounds), instead of 8 levels of 45 shuffles
+// Everything is fixed-order, so results are run-to-run identical.
 __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const int b, const int lane, double* sq_out) {
-  const int j = lane < NJ ? lane : 0;
-  const bool act = lane < NJ;
   const unsigned FULL = 0xffffffffu;
+  const bool act = lane < NJ;
+  const int4 tt0 = __ldg(p.tree_tab + lane * 2), tt1 = __ldg(p.tree_tab + lane * 2 + 1);
+  const int j = tt0.x;          // joint of this lane (0 for idle lanes)
+  const int sub = tt0.y;        // subtree size, itself included (1 for idle lanes)
+  const int up[5] = {tt0.z, tt0.w, tt1.x, tt1.y, tt1.z};   // lane of the 2^r-th ancestor, -1 past the root
+  const int par = up[0] >= 0 ? up[0] : 0;
 
   // ---- recompute the forward quantities of this joint (pose_prep.cu) ----
   const float* th = p.theta + (size_t)b * (NJ * 3) + j * 3;
@@ -65,26 +79,32 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
 #pragma unroll
   for (int e = 0; e < 9; ++e) GR[e] = R[e];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) Gt[c] = J[c];
-  const int par = p.tree.parent[j];
-  const int dep = act ? p.tree.depth[j] : -1;
-  for (int d = 1; d <= p.tree.max_depth; ++d) {
-    float pR[9], pt[3], pJ[3];
+  for (int c = 0; c < 3; ++c) {
+    const float pj = __shfl_sync(FULL, J[c], par);
+    Gt[c] = up[0] >= 0 ? J[c] - pj : J[c];
+  }
 #pragma unroll
-    for (int e = 0; e < 9; ++e) pR[e] = __shfl_sync(FULL, GR[e], par);
+  for (int r = 0; r < 5; ++r) {
+    if (r < p.n_rounds) {
+      const int a = up[r] >= 0 ? up[r] : 0;
+      float aR[9], at[3];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      pt[c] = __shfl_sync(FULL, Gt[c], par);
-      pJ[c] = __shfl_sync(FULL, J[c], par);
-    }
-    if (dep == d) {
-      const float r0 = J[0] - pJ[0], r1 = J[1] - pJ[1], r2 = J[2] - pJ[2];
+      for (int e = 0; e < 9; ++e) aR[e] = __shfl_sync(FULL, GR[e], a);
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
+      for (int c = 0; c < 3; ++c) at[c] = __shfl_sync(FULL, Gt[c], a);
+      if (up[r] >= 0) {
+        float nR[9], nt[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c)
-          GR[r * 3 + c] = pR[r * 3 + 0] * R[c] + pR[r * 3 + 1] * R[3 + c] + pR[r * 3 + 2] * R[6 + c];
-        Gt[r] = pR[r * 3 + 0] * r0 + pR[r * 3 + 1] * r1 + pR[r * 3 + 2] * r2 + pt[r];
+        for (int rr = 0; rr < 3; ++rr) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            nR[rr * 3 + c] = aR[rr * 3 + 0] * GR[c] + aR[rr * 3 + 1] * GR[3 + c] + aR[rr * 3 + 2] * GR[6 + c];
+          nt[rr] = aR[rr * 3 + 0] * Gt[0] + aR[rr * 3 + 1] * Gt[1] + aR[rr * 3 + 2] * Gt[2] + at[rr];
+        }
+#pragma unroll
+        for (int e = 0; e < 9; ++e) GR[e] = nR[e];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) Gt[c] = nt[c];
       }
     }
   }
@@ -129,8 +149,10 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
     if (lane == 0) *sq_out = sd;
   }
 
-  // ---- A -> G adjoint: A.R = G.R, A.t = G.t - G.R J (batch_lbs.py:138-142) ----
-  float gGR[9], gGt[3], gJ[3];
+  // ---- own gradients: A.R = G.R, A.t = G.t - G.R J (batch_lbs.py:138-142), plus the posed-joint gradient on G.t ----
+  float gJ[3];
+  float S[12];   // the summands of the subtree sums: gGR_own G.R^T + gGt_own G.t^T (9) | gGt_own (3)
+  float Fown[3], Qown[9];   // Qown = gGR_own G.R^T: the joint's own share of dL/dG_i.R G_i.R^T
   {
     float gAR[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, gAt[3] = {0.f, 0.f, 0.f};
     if (act && p.g_A) {
@@ -141,68 +163,83 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
         gAR[r * 3] = v.x; gAR[r * 3 + 1] = v.y; gAR[r * 3 + 2] = v.z; gAt[r] = v.w;
       }
     }
+    float gGR[9];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
 #pragma unroll
       for (int c = 0; c < 3; ++c) gGR[r * 3 + c] = gAR[r * 3 + c] - gAt[r] * J[c];
-      gGt[r] = gAt[r] + gJt[r];
+      Fown[r] = act ? gAt[r] + gJt[r] : 0.f;
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) gJ[c] = -(GR[c] * gAt[0] + GR[3 + c] * gAt[1] + GR[6 + c] * gAt[2]);
-  }
-
-  // ---- reverse kinematic chain, deepest level first; parents gather their children's contributions ----
-  float gR[9];
 #pragma unroll
-  for (int e = 0; e < 9; ++e) gR[e] = 0.f;
-  const int c0 = act ? p.tree.child[j][0] : -1, c1 = act ? p.tree.child[j][1] : -1, c2 = act ? p.tree.child[j][2] : -1;
-  for (int d = p.tree.max_depth; d >= 1; --d) {
-    float pR[9], pJ[3];
-#pragma unroll
-    for (int e = 0; e < 9; ++e) pR[e] = __shfl_sync(FULL, GR[e], par);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) pJ[c] = __shfl_sync(FULL, J[c], par);
-    float con[15];   // contribution to the parent: gGR (9), gGt (3), gJ (3)
-#pragma unroll
-    for (int e = 0; e < 15; ++e) con[e] = 0.f;
-    if (dep == d) {
-      // G_i.R = G_p.R R_i ; G_i.t = G_p.R (J_i - J_p) + G_p.t
-      const float dj[3] = {J[0] - pJ[0], J[1] - pJ[1], J[2] - pJ[2]};
-#pragma unroll
-      for (int r = 0; r < 3; ++r)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          gR[r * 3 + c] = pR[r] * gGR[c] + pR[3 + r] * gGR[3 + c] + pR[6 + r] * gGR[6 + c];   // G_p.R^T gGR
-          con[r * 3 + c] = gGR[r * 3] * R[c * 3] + gGR[r * 3 + 1] * R[c * 3 + 1] + gGR[r * 3 + 2] * R[c * 3 + 2] +
-                           gGt[r] * dj[c];                                                      // gGR R^T + gGt dj^T
-        }
+    for (int r = 0; r < 3; ++r) {
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        con[9 + c] = gGt[c];
-        const float dv = pR[c] * gGt[0] + pR[3 + c] * gGt[1] + pR[6 + c] * gGt[2];             // G_p.R^T gGt
-        gJ[c] += dv;
-        con[12 + c] = -dv;
+        const float v = gGR[r * 3] * GR[c * 3] + gGR[r * 3 + 1] * GR[c * 3 + 1] + gGR[r * 3 + 2] * GR[c * 3 + 2];
+        Qown[r * 3 + c] = v;
+        S[r * 3 + c] = act ? v + Fown[r] * Gt[c] : 0.f;
       }
-    }
-#pragma unroll
-    for (int e = 0; e < 15; ++e) {
-      const float v0 = __shfl_sync(FULL, con[e], c0 >= 0 ? c0 : 0);
-      const float v1 = __shfl_sync(FULL, con[e], c1 >= 0 ? c1 : 0);
-      const float v2 = __shfl_sync(FULL, con[e], c2 >= 0 ? c2 : 0);
-      float add = 0.f;
-      if (c0 >= 0) add += v0;
-      if (c1 >= 0) add += v1;
-      if (c2 >= 0) add += v2;
-      if (e < 9) gGR[e] += add;
-      else if (e < 12) gGt[e - 9] += add;
-      else gJ[e - 12] += add;
+      S[9 + r] = Fown[r];
     }
   }
-  if (dep == 0) {   // root: G_0 = (R_0, J_0)
+
+  // ---- sums over the STRICT descendants = lanes [l + 1, l + sub): doubling table W_r[l] = S[l] + ... + S[l + 2^r - 1] built
+  // in place; the range is cut into power-of-two blocks by the bits of its length.  No subtraction of prefixes: a leaf gets
+  // an exact zero (as TF's autodiff does -- Adam would turn rounding noise on a zero gradient into steps of size lr) and
+  // nothing cancels.
+  float D[12];
 #pragma unroll
-    for (int e = 0; e < 9; ++e) gR[e] = gGR[e];
+  for (int e = 0; e < 12; ++e) D[e] = 0.f;
+  {
+    const int n = sub - 1;
+    int pos = lane + 1;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) gJ[c] += gGt[c];
+    for (int r = 0; r < 5; ++r) {
+      const bool take = (n >> r) & 1;
+#pragma unroll
+      for (int e = 0; e < 12; ++e) {
+        const float blk = __shfl_sync(FULL, S[e], pos & 31);
+        if (take) D[e] += blk;
+      }
+      if (take) pos += 1 << r;
+      if (r < 4) {
+#pragma unroll
+        for (int e = 0; e < 12; ++e) S[e] += __shfl_down_sync(FULL, S[e], 1 << r);
+      }
+    }
+  }
+
+  // ---- dL/dG_i -> dL/dR_i and dL/dJ: G_i.R = G_p.R R_i ; G_i.t = G_p.R (J_i - J_p) + G_p.t (root: G_p = identity) ----
+  float gR[9];
+  {
+    float pR[9];
+#pragma unroll
+    for (int e = 0; e < 9; ++e) {
+      const float v = __shfl_sync(FULL, GR[e], par);
+      pR[e] = up[0] >= 0 ? v : ((e == 0 || e == 4 || e == 8) ? 1.f : 0.f);
+    }
+    float M[9], T[9];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        M[r * 3 + c] = Qown[r * 3 + c] + (D[r * 3 + c] - D[9 + r] * Gt[c]);
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        T[r * 3 + c] = M[r * 3] * GR[c] + M[r * 3 + 1] * GR[3 + c] + M[r * 3 + 2] * GR[6 + c];   // dL/dG_i.R
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) gR[r * 3 + c] = pR[r] * T[c] + pR[3 + r] * T[3 + c] + pR[6 + r] * T[6 + c];   // G_p.R^T .
+    // J_i enters G_i.t through G_p.R, and every child's G_c.t through -G_i.R
+    const float gt0 = Fown[0] + D[9], gt1 = Fown[1] + D[10], gt2 = Fown[2] + D[11];   // dL/dG_i.t
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      gJ[c] += (pR[c] * gt0 + pR[3 + c] * gt1 + pR[6 + c] * gt2) -
+               (GR[c] * D[9] + GR[3 + c] * D[10] + GR[6 + c] * D[11]);
   }
 
   // ---- pose feature adjoint (batch_smpl.py:109-110): phi = vec(R_1..23 - I) ----
@@ -246,7 +283,7 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
   }
 }
 
-__global__ void __launch_bounds__(JB_WARPS * 32) joint_bwd_kernel(const JointBwdParams p) {
+__global__ void __launch_bounds__(JB_WARPS * 32, 7) joint_bwd_kernel(const JointBwdParams p) {
   __shared__ double sq_sum[JB_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * JB_WARPS + warp;
@@ -362,7 +399,8 @@ int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const f
   p.g_beta = g_beta;
   p.g_theta = g_theta;
   p.cfg = cfg;
-  p.tree = m->tree;
+  p.tree_tab = m->tree_tab;
+  p.n_rounds = m->tree.n_rounds;
   p.gt_px = gt_px;
   p.px_coef = px_coef;
   p.px_out = px;
@@ -438,7 +476,8 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   p.g_beta = io->g_beta;
   p.g_theta = io->g_theta;
   p.cfg = io->cfg;
-  p.tree = m->tree;
+  p.tree_tab = m->tree_tab;
+  p.n_rounds = m->tree.n_rounds;
   p.gt_px = nullptr; p.px_coef = 0.f; p.px_out = nullptr; p.g_px_out = nullptr; p.partial = nullptr;
   joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
   SMPLB_CUDA_CHECK(cudaGetLastError());

@@ -81,8 +81,15 @@ struct KernelSetup {
 struct Tree {
   int parent[NJ];
   int depth[NJ];
-  int child[NJ][3];   // -1 padded (SMPL: at most 3 children per joint); used by the backward chain
+  int child[NJ][3];   // -1 padded (SMPL: at most 3 children per joint)
   int max_depth;
+  // depth-first pre-order view, used by the per-sample adjoint kernel (backward.cu): lane l holds joint order[l], its
+  // subtree is the lane range [l, l + sub[l]), up[r][l] is the lane of its 2^r-th ancestor (-1 past the root)
+  int order[NJ];
+  int rank[NJ];
+  int sub[NJ];
+  int up[5][NJ];
+  int n_rounds;       // ceil(log2(max_depth + 1)): pointer-jumping rounds of the forward chain
 };
 int32_t build_tree(const int32_t* parents, Tree* out, const char* who);
 
@@ -93,6 +100,7 @@ struct smplb_model {
   int device;
   int NK;
   smplb::Tree tree;
+  int4* tree_tab;   // device: [32 lanes][2] = {order, sub, up0, up1 | up2, up3, up4, 0} (idle lanes: 0, 1, -1 ...)
   // reference-layout constants
   float* v_template_pad;  // [VPP]   v_template flattened (3v+c), zero padded
   // blend-shape basis D = [shapedirs; posedirs] : K=217 rows, padded to KPAD x VPP

@@ -57,6 +57,36 @@ int32_t build_tree(const int32_t* parents, Tree* t, const char* who) {
     if (c == 3) return fail(SMPLB_E_UNSUPPORTED, std::string(who) + ": more than 3 children per joint");
     t->child[p][c] = i;
   }
+  // depth-first pre-order (children in index order)
+  {
+    int stack[NJ], sp = 0, n = 0;
+    stack[sp++] = 0;
+    while (sp > 0) {
+      const int i = stack[--sp];
+      t->rank[i] = n;
+      t->order[n++] = i;
+      for (int c = 2; c >= 0; --c)
+        if (t->child[i][c] >= 0) stack[sp++] = t->child[i][c];
+    }
+    int size[NJ];
+    for (int i = NJ - 1; i >= 0; --i) {
+      size[i] = 1;
+      for (int c = 0; c < 3; ++c)
+        if (t->child[i][c] >= 0) size[i] += size[t->child[i][c]];
+    }
+    for (int l = 0; l < NJ; ++l) {
+      const int i = t->order[l];
+      t->sub[l] = size[i];
+      t->up[0][l] = i == 0 ? -1 : t->rank[t->parent[i]];
+    }
+    for (int r = 1; r < 5; ++r)
+      for (int l = 0; l < NJ; ++l) {
+        const int a = t->up[r - 1][l];
+        t->up[r][l] = a < 0 ? -1 : t->up[r - 1][a];
+      }
+    t->n_rounds = 0;
+    while ((1 << t->n_rounds) < t->max_depth + 1) ++t->n_rounds;
+  }
   return SMPLB_OK;
 }
 
@@ -302,6 +332,15 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->Wimg2, Wimg2));
   chk(upload(&m->vt_plain, vt_plain));
   chk(upload(&m->kpc_slot_of, cslot_of));
+  {
+    std::vector<int4> tab(64);
+    for (int l = 0; l < 32; ++l) {
+      const bool a = l < NJ;
+      tab[l * 2] = make_int4(a ? tree.order[l] : 0, a ? tree.sub[l] : 1, a ? tree.up[0][l] : -1, a ? tree.up[1][l] : -1);
+      tab[l * 2 + 1] = make_int4(a ? tree.up[2][l] : -1, a ? tree.up[3][l] : -1, a ? tree.up[4][l] : -1, 0);
+    }
+    chk(upload(&m->tree_tab, tab));
+  }
   cudaSetDevice(prev);
   if (e != cudaSuccess) {
     smplb_model_destroy(m);
@@ -321,6 +360,7 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->Dimg);
   cudaFree(m->Jbar);
   cudaFree(m->JS);
+  cudaFree(m->tree_tab);
   cudaFree(m->skin_idx);
   cudaFree(m->skin_w);
   cudaFree(m->kp_ptr);
