@@ -36,7 +36,30 @@ struct JointBwdParams {
   float* px_out;           // [B,24,2] nullable
   float* g_px_out;         // [B,24,2] nullable
   double* partial;         // [gridDim.x]
+  // ... and, when the loss cap is off (the gate is 1 whatever the loss turns out to be), the TF1 Adam update of this
+  // sample's theta (and beta) straight from the registers that hold the gradient: adam_m_theta != nullptr
+  float* adam_theta;       // [B,72] updated in place (every lane has read its own theta before)
+  float* adam_m_theta;
+  float* adam_v_theta;
+  float* adam_beta;        // [B,10] nullable
+  float* adam_m_beta;
+  float* adam_v_beta;
+  const int* step_dev;     // t = *step_dev + 1 (incremented by loss_finish_kernel AFTER this kernel), else step_host
+  int step_host;
+  float lr, b1, b2, eps;
 };
+
+__device__ __forceinline__ float adam_lr_t_dev(float lr, float b1, float b2, int t) {
+  return lr * sqrtf(1.0f - powf(b2, (float)t)) / (1.0f - powf(b1, (float)t));
+}
+__device__ __forceinline__ void adam_update(float* x, float* m, float* v, float g, float lr_t, float b1, float b2,
+                                            float eps) {
+  const float mi = b1 * *m + (1.0f - b1) * g;
+  const float vi = b2 * *v + (1.0f - b2) * g * g;
+  *m = mi;
+  *v = vi;
+  *x = *x - lr_t * mi / (sqrtf(vi) + eps);
+}
 
 constexpr int JB_WARPS = 4;
 
@@ -58,6 +81,8 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
   const int sub = tt0.y;        // subtree size, itself included (1 for idle lanes)
   const int up[5] = {tt0.z, tt0.w, tt1.x, tt1.y, tt1.z};   // lane of the 2^r-th ancestor, -1 past the root
   const int par = up[0] >= 0 ? up[0] : 0;
+  float lr_t = 0.f;
+  if (p.adam_m_theta) lr_t = adam_lr_t_dev(p.lr, p.b1, p.b2, p.step_dev ? __ldg(p.step_dev) + 1 : p.step_host);
 
   // ---- recompute the forward quantities of this joint (pose_prep.cu) ----
   const float* th = p.theta + (size_t)b * (NJ * 3) + j * 3;
@@ -257,6 +282,12 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
     rodrigues_smpl_bwd(tx, ty, tz, gR, gth);
     float* o = p.g_theta + (size_t)b * (NJ * 3) + j * 3;
     o[0] = gth[0]; o[1] = gth[1]; o[2] = gth[2];
+    if (p.adam_m_theta) {
+      const size_t at = (size_t)b * (NJ * 3) + j * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        adam_update(p.adam_theta + at + c, p.adam_m_theta + at + c, p.adam_v_theta + at + c, gth[c], lr_t, p.b1, p.b2, p.eps);
+    }
   }
 
   // ---- J = Jbar + JS beta adjoint (+ shape-blend columns of g_X) -> g_beta ----
@@ -280,6 +311,10 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
     if (p.g_X)
       for (int sl = 0; sl < p.n_slices; ++sl) v += __ldg(p.g_X + ((size_t)sl * p.B + b) * KPAD + lane);
     p.g_beta[(size_t)b * NB + lane] = v;
+    if (p.adam_m_beta) {
+      const size_t at = (size_t)b * NB + lane;
+      adam_update(p.adam_beta + at, p.adam_m_beta + at, p.adam_v_beta + at, v, lr_t, p.b1, p.b2, p.eps);
+    }
   }
 }
 
@@ -381,8 +416,16 @@ int fit_fused_blocks(int B) { return (B + JB_WARPS - 1) / JB_WARPS; }
 int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const float* theta, const float* gt_px,
                          float px_coef, const float* cam_pos, const float* cam_rot, const float* focal,
                          const smplb_camcfg& cfg, float* px, float* g_px, double* partial, float* g_beta, float* g_theta,
-                         cudaStream_t st) {
+                         const FitAdam* adam, cudaStream_t st) {
   JointBwdParams p;
+  p.adam_m_theta = nullptr;
+  p.adam_m_beta = nullptr;
+  if (adam) {
+    p.adam_theta = adam->theta; p.adam_m_theta = adam->m_theta; p.adam_v_theta = adam->v_theta;
+    p.adam_beta = adam->beta; p.adam_m_beta = adam->m_beta; p.adam_v_beta = adam->v_beta;
+    p.step_dev = adam->step_dev; p.step_host = adam->step_host;
+    p.lr = adam->lr; p.b1 = adam->b1; p.b2 = adam->b2; p.eps = adam->eps;
+  }
   p.B = B;
   p.beta = beta;
   p.theta = theta;
@@ -479,6 +522,7 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   p.tree_tab = m->tree_tab;
   p.n_rounds = m->tree.n_rounds;
   p.gt_px = nullptr; p.px_coef = 0.f; p.px_out = nullptr; p.g_px_out = nullptr; p.partial = nullptr;
+  p.adam_m_theta = nullptr; p.adam_m_beta = nullptr;
   joint_bwd_kernel<<<(B + JB_WARPS - 1) / JB_WARPS, JB_WARPS * 32, 0, st>>>(p);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   if (vertex_path) timing_mark_bwd(4, st);

@@ -93,6 +93,15 @@ struct Tree {
 };
 int32_t build_tree(const int32_t* parents, Tree* out, const char* who);
 
+// Adam state handed to the fused fitting kernel (backward.cu) when the update can run inside it (fit.cu)
+struct FitAdam {
+  float *theta, *m_theta, *v_theta;
+  float *beta, *m_beta, *v_beta;   // m_beta == nullptr: beta is not fitted
+  const int* step_dev;
+  int step_host;
+  float lr, b1, b2, eps;
+};
+
 }  // namespace smplb
 
 // Device-resident model constants (SMPL.__init__, batch_smpl.py:17-69) plus derived tables.

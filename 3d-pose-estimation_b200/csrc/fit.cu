@@ -16,7 +16,7 @@ int fit_fused_blocks(int B);
 int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const float* theta, const float* gt_px,
                          float px_coef, const float* cam_pos, const float* cam_rot, const float* focal,
                          const smplb_camcfg& cfg, float* px, float* g_px, double* partial, float* g_beta, float* g_theta,
-                         cudaStream_t st);
+                         const FitAdam* adam, cudaStream_t st);
 
 constexpr int RG_THREADS = 256;
 
@@ -151,20 +151,30 @@ extern "C" int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, 
   double* partial = (double*)io->scratch;
   const double inv_n = 1.0 / (double)io->n_total;
   // g_px = 2 * scale / n_total * (px - gt)   (d/dpx of scale * mean((gt - px)^2), pose_model_3d.py:233-235)
+  // With the cap off the gate is 1 whatever the loss is, so Adam runs inside the fused kernel on the gradient it holds in
+  // registers (2 launches per step); with the cap on, the update has to wait for the global loss (3 - 4 launches).
+  const bool adam_inside = !(io->cfg.reproj_cap > 0.f);
+  FitAdam ad;
+  ad.theta = io->theta; ad.m_theta = io->m_theta; ad.v_theta = io->v_theta;
+  ad.beta = io->beta; ad.m_beta = io->m_beta; ad.v_beta = io->v_beta;
+  ad.step_dev = io->step_dev; ad.step_host = io->step;
+  ad.lr = io->lr; ad.b1 = io->beta1; ad.b2 = io->beta2; ad.eps = io->eps;
   int32_t rc = launch_fit_fused(m, B, io->beta, io->theta, io->gt_px, (float)(2.0 * io->cfg.reproj_scale * inv_n),
                                 io->cam_pos, io->cam_rot, io->focal, io->cfg.cam, io->px, io->g_px, partial, io->g_beta,
-                                io->g_theta, st);
+                                io->g_theta, adam_inside ? &ad : nullptr, st);
   if (rc != SMPLB_OK) return rc;
   loss_finish_kernel<<<1, 256, 0, st>>>(nblocks, partial, io->cfg.reproj_scale, inv_n, io->cfg.reproj_cap, io->loss,
                                         io->step_dev, io->step, io->lr, io->beta1, io->beta2);
   SMPLB_CUDA_CHECK(cudaGetLastError());
-  const int64_t nt = (int64_t)B * NJ * 3;
-  adam_gated_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(nt, io->theta, io->g_theta, io->m_theta, io->v_theta,
-                                                                  io->loss + 2, io->loss + 3, io->beta1, io->beta2, io->eps);
-  if (io->m_beta) {
-    const int64_t nb = (int64_t)B * NB;
-    adam_gated_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, st>>>(nb, io->beta, io->g_beta, io->m_beta, io->v_beta,
+  if (!adam_inside) {
+    const int64_t nt = (int64_t)B * NJ * 3;
+    adam_gated_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(nt, io->theta, io->g_theta, io->m_theta, io->v_theta,
                                                                     io->loss + 2, io->loss + 3, io->beta1, io->beta2, io->eps);
+    if (io->m_beta) {
+      const int64_t nb = (int64_t)B * NB;
+      adam_gated_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, st>>>(nb, io->beta, io->g_beta, io->m_beta, io->v_beta,
+                                                                      io->loss + 2, io->loss + 3, io->beta1, io->beta2, io->eps);
+    }
   }
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;

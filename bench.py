@@ -284,7 +284,7 @@ def run_fit(args, rank, local_rank, world, dist):
                                        '2D re-projection loss', B)), 'cuda_graph': graph is not None,
                        'collective': ('NCCL all-reduce of the [%d,4] loss log once every %d step(s)' % (k, k)) if world > 1 else 'none',
                        'adam_step_counter': 'device (advances on graph replays)'},
-            'gpu_launches': (15 if mesh else 3) * steps, 'loss_first': first, 'loss_last': float(log[k - 1, 0]),
+            'gpu_launches': (15 if mesh else 2) * steps, 'loss_first': first, 'loss_last': float(log[k - 1, 0]),
             'adam_steps_done': int(f.step_dev)}),
             flush=True)
     if graph is not None:
