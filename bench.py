@@ -164,6 +164,39 @@ def cpu_reference_rate(B_chunk, min_seconds, max_chunks, seed=1000):
     return n * B_chunk / el, cores, n * B_chunk, el, step
 
 
+def cpu_tight_rate(min_seconds, B_chunk=2048, seed=1000):
+    """the tight C + OpenMP version of the same workload (oracle/smpl_omp.c; blend as one tiled matrix
+    with 8 samples in the vector lanes, sparse skinning), all host threads.  A fairer CPU number than the TF op sequence;
+    reported beside it, never the thing shipped."""
+    import numpy as np
+    from oracle import ref_numpy as rn          # timed CPU baseline only
+    from oracle import smpl_omp
+    from smplb200 import synthetic as syn
+    tm = smpl_omp.TightModel(rn.load_model(syn.make_synthetic_smpl(0), dtype=np.float32))
+    inp = syn.make_inputs(B_chunk, seed=seed)
+    a = (inp['beta'], inp['theta'], inp['cam_pos'], inp['cam_rot'], inp['focal'], rn.CFG.ss, 320.0, 240.0)
+    o = tm.forward(*a)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        o = tm.forward(*a, out=o)
+        n += 1
+        el = time.perf_counter() - t0
+        if el >= min_seconds:
+            break
+    return {'value': n * B_chunk / el, 'unit': UNIT, 'cores': int(o['threads']), 'kind': 'port (tight C + OpenMP, AVX2)',
+            'sample': '%d samples (%d-sample chunks, %.1f s) of the same workload: verts, joints, key points, px' % (
+                n * B_chunk, B_chunk, el)}
+
+
+def tensorflow_probe():
+    """the reference on real TensorFlow, if the box has it."""
+    try:
+        import tensorflow as tf                  # noqa: F401
+        return 'importable (%s) -- not wired: the reference needs TF1 graph mode' % getattr(tf, '__version__', '?')
+    except Exception as e:                       # ImportError on this image
+        return 'not importable on this box (%s)' % type(e).__name__
+
+
 def workload_config(args, world):
     """config block shared by both arms (the driver compares them)."""
     if args.scaling == 'strong':
@@ -865,7 +898,9 @@ def run_forward(args, rank, local_rank, world, dist):
             line['cpu_baseline'] = {
                 'value': rate, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                 'sample': '%d samples (%d-sample chunks, %.1f s) of the same workload; torch-CPU fp32 port of '
-                          'the reference TF op sequence incl. tile(W)' % (ns, args.ref_chunk, el)}
+                          'the reference TF op sequence incl. tile(W)' % (ns, args.ref_chunk, el),
+                'tight': cpu_tight_rate(min(args.cpu_seconds, 5.0)),
+                'tensorflow': tensorflow_probe()}
         print(json.dumps(line), flush=True)
     if graph is not None:
         graph.reset()
