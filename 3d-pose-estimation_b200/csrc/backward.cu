@@ -15,6 +15,7 @@ struct JointBwdParams {
   const float* theta;
   const float* Jbar;
   const float* JS;
+  const float* JSt;        // smplb_model::JSt (joint-minor copy of Jbar / JS)
   const float* g_joints;   // [B,24,3] nullable
   const float* g_px;       // [B,24,2] nullable
   const float* cam_pos;
@@ -95,9 +96,9 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
   float J[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    float acc = __ldg(p.Jbar + j * 3 + c);
+    float acc = __ldg(p.JSt + (3 * NB + c) * 32 + j);
 #pragma unroll
-    for (int k = 0; k < NB; ++k) acc = fmaf(__ldg(p.JS + (j * 3 + c) * NB + k), beta[k], acc);
+    for (int k = 0; k < NB; ++k) acc = fmaf(__ldg(p.JSt + (c * NB + k) * 32 + j), beta[k], acc);
     J[c] = acc;
   }
   float GR[9], Gt[3];
@@ -297,7 +298,7 @@ __device__ __forceinline__ void joint_bwd_sample(const JointBwdParams& p, const 
     float v = 0.f;
     if (act) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v = fmaf(__ldg(p.JS + (j * 3 + c) * NB + k), gJ[c], v);
+      for (int c = 0; c < 3; ++c) v = fmaf(__ldg(p.JSt + (c * NB + k) * 32 + j), gJ[c], v);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
@@ -431,6 +432,7 @@ int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const f
   p.theta = theta;
   p.Jbar = m->Jbar;
   p.JS = m->JS;
+  p.JSt = m->JSt;
   p.g_joints = nullptr;
   p.g_px = nullptr;
   p.cam_pos = cam_pos;
@@ -508,6 +510,7 @@ extern "C" int32_t smplb_backward(const smplb_model* m, const smplb_backward_io*
   p.theta = io->theta;
   p.Jbar = m->Jbar;
   p.JS = m->JS;
+  p.JSt = m->JSt;
   p.g_joints = io->g_joints;
   p.g_px = io->g_px;
   p.cam_pos = io->cam_pos;

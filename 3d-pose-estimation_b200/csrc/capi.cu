@@ -135,6 +135,7 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.theta = io->theta;
   p.Jbar = m->Jbar;
   p.JS = m->JS;
+  p.JSt = m->JSt;
   const bool fused = skin && (flags & SMPLB_F_FUSED);
   p.Ximg = (skin && !fused) ? w.Ximg : nullptr;
   p.Ximg2 = fused ? w.Ximg2 : nullptr;
@@ -149,7 +150,8 @@ extern "C" int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* i
   p.uv = io->uv;
   p.px = io->px;
   p.cfg = io->cfg;
-  p.tree = m->tree;
+  p.tree_tab = m->tree_tab;
+  p.n_rounds = m->tree.n_rounds;
   p.status = w.status;
   SMPLB_CUDA_CHECK(cudaMemsetAsync(w.status, 0, sizeof(int), st));
   timing_mark(0, st);

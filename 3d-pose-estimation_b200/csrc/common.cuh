@@ -89,6 +89,7 @@ struct Tree {
   int rank[NJ];
   int sub[NJ];
   int up[5][NJ];
+  int upj[5][NJ];     // the same in joint order: upj[r][j] = 2^r-th ancestor joint of joint j, -1 past the root
   int n_rounds;       // ceil(log2(max_depth + 1)): pointer-jumping rounds of the forward chain
 };
 int32_t build_tree(const int32_t* parents, Tree* out, const char* who);
@@ -109,7 +110,8 @@ struct smplb_model {
   int device;
   int NK;
   smplb::Tree tree;
-  int4* tree_tab;   // device: [32 lanes][2] = {order, sub, up0, up1 | up2, up3, up4, 0} (idle lanes: 0, 1, -1 ...)
+  int4* tree_tab;   // device: [32 lanes][2] = {order, sub, up0, up1 | up2, up3, up4, 0} (idle lanes: 0, 1, -1 ...), then the
+                    // same table with lane = joint (pose_prep.cu): {j, 1, upj0, upj1 | upj2, upj3, upj4, 0}
   // reference-layout constants
   float* v_template_pad;  // [VPP]   v_template flattened (3v+c), zero padded
   // blend-shape basis D = [shapedirs; posedirs] : K=217 rows, padded to KPAD x VPP
@@ -118,6 +120,8 @@ struct smplb_model {
   // folded joint regression: J = Jbar + JS * beta  (batch_smpl.py:91-101)
   float* Jbar;            // [24*3]
   float* JS;              // [24*3*10]
+  float* JSt;             // [33][32] joint-minor copy: row c*10+k = JS[.][c][k], rows 30..32 = Jbar[.][c]; lanes that hold
+                          // joints read one 128-byte line per row (the per-sample kernels)
   // compressed LBS weights (<= 4 non-zeros per vertex), sorted by joint index (SIMT skinning path);
   // has_compressed == 0 when some vertex has more than 4 non-zero weights (dense models: TC path only)
   uint32_t* skin_idx;     // [NV] 4 x u8 joint ids
@@ -172,6 +176,7 @@ struct PrepParams {
   const float* theta;
   const float* Jbar;
   const float* JS;
+  const float* JSt;   // smplb_model::JSt
   float* Ximg;    // [ceil(B/128)][BL_XTILE] f16/bf16 operand image of [beta | pose feature] (ximg16_off), nullable
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
@@ -185,7 +190,9 @@ struct PrepParams {
   float* uv;
   float* px;
   smplb_camcfg cfg;
-  Tree tree;
+  const int4* tree_tab;   // smplb_model::tree_tab
+  int n_rounds;           // Tree::n_rounds
+  int staged;             // set by launch_pose_prep: per-joint outputs leave through shared memory (16-byte stores)
   int* status;    // nullable: input-range flags (see Workspace)
 };
 

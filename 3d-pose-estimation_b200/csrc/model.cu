@@ -84,6 +84,12 @@ int32_t build_tree(const int32_t* parents, Tree* t, const char* who) {
         const int a = t->up[r - 1][l];
         t->up[r][l] = a < 0 ? -1 : t->up[r - 1][a];
       }
+    for (int j = 0; j < NJ; ++j) t->upj[0][j] = j == 0 ? -1 : t->parent[j];
+    for (int r = 1; r < 5; ++r)
+      for (int j = 0; j < NJ; ++j) {
+        const int a = t->upj[r - 1][j];
+        t->upj[r][j] = a < 0 ? -1 : t->upj[r - 1][a];
+      }
     t->n_rounds = 0;
     while ((1 << t->n_rounds) < t->max_depth + 1) ++t->n_rounds;
   }
@@ -310,6 +316,15 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->Dimg, Dimg));
   chk(upload(&m->Jbar, Jbar));
   chk(upload(&m->JS, JS));
+  {
+    std::vector<float> JSt(33 * 32, 0.f);
+    for (int j = 0; j < NJ; ++j)
+      for (int c = 0; c < 3; ++c) {
+        for (int k = 0; k < NB; ++k) JSt[(c * NB + k) * 32 + j] = JS[(j * 3 + c) * NB + k];
+        JSt[(3 * NB + c) * 32 + j] = Jbar[j * 3 + c];
+      }
+    chk(upload(&m->JSt, JSt));
+  }
   chk(upload(&m->skin_idx, sidx));
   chk(upload(&m->skin_w, sw));
   chk(upload(&m->kp_ptr, kptr));
@@ -333,11 +348,13 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   chk(upload(&m->vt_plain, vt_plain));
   chk(upload(&m->kpc_slot_of, cslot_of));
   {
-    std::vector<int4> tab(64);
+    std::vector<int4> tab(128);
     for (int l = 0; l < 32; ++l) {
       const bool a = l < NJ;
       tab[l * 2] = make_int4(a ? tree.order[l] : 0, a ? tree.sub[l] : 1, a ? tree.up[0][l] : -1, a ? tree.up[1][l] : -1);
       tab[l * 2 + 1] = make_int4(a ? tree.up[2][l] : -1, a ? tree.up[3][l] : -1, a ? tree.up[4][l] : -1, 0);
+      tab[64 + l * 2] = make_int4(a ? l : 0, 1, a ? tree.upj[0][l] : -1, a ? tree.upj[1][l] : -1);
+      tab[64 + l * 2 + 1] = make_int4(a ? tree.upj[2][l] : -1, a ? tree.upj[3][l] : -1, a ? tree.upj[4][l] : -1, 0);
     }
     chk(upload(&m->tree_tab, tab));
   }
@@ -360,6 +377,7 @@ extern "C" int32_t smplb_model_destroy(smplb_model* m) {
   cudaFree(m->Dimg);
   cudaFree(m->Jbar);
   cudaFree(m->JS);
+  cudaFree(m->JSt);
   cudaFree(m->tree_tab);
   cudaFree(m->skin_idx);
   cudaFree(m->skin_w);

@@ -2,7 +2,7 @@
 //   Rodrigues x24 (batch_lbs.py:38-57)  ->  207-d pose feature (batch_smpl.py:107-110) written as the
 //   TF32 hi/lo split A-operand of the blend GEMM, beta in columns 0..9;
 //   folded joint regression J = Jbar + JS beta (batch_smpl.py:91-101);
-//   kinematic chain by depth level with warp shuffles (batch_lbs.py:84-144);
+//   kinematic chain by pointer jumping with warp shuffles (batch_lbs.py:84-144);
 //   J_transformed, relative skinning transforms A[B,24,3,4];
 //   optional perspective projection of the 24 posed joints + pixel rescale
 //   (project.py:7-48, pose_model_3d.py:202-231).
@@ -12,15 +12,38 @@
 
 namespace smplb {
 
-constexpr int PREP_WARPS = 4;
+constexpr int PREP_WARPS = 8;          // samples per block: 8 x 16 bytes = one full line of the X operand image per k-chunk
+constexpr int PREP_XPITCH = KPAD + 4;  // X rows in shared memory (pitch 228: the 8 samples' float4 reads hit distinct banks)
+constexpr int PREP_STAGE = 2 * 4 * 12 * 8 / 2;   // floats per warp: the A operand image of one sample (1536 B) >= A (1152 B)
+static_assert(PREP_STAGE >= NJ * 12, "staging buffer holds the largest per-joint output");
+static_assert(BL_BM % PREP_WARPS == 0 && KPAD % 8 == 0, "a block's samples share one X tile");
+
+// Per-joint outputs of one sample ([24][n] floats, n * 96 bytes per sample) leave through shared memory: every lane
+// writes its joint's n floats, then the warp stores the sample's block with 16-byte coalesced stores -- lane = joint
+// stores straight to global memory touch 24 sectors per instruction (9 instructions for Rs: 243 sector writes for 27
+// sectors of data), and the store path, not the arithmetic, was what the kernel waited on.
+template <int N>
+__device__ __forceinline__ void store_staged(float* stage, float* dst, const float (&v)[N], int lane, bool act) {
+  __syncwarp();
+  if (act) {
+#pragma unroll
+    for (int e = 0; e < N; ++e) stage[lane * N + e] = v[e];
+  }
+  __syncwarp();
+  constexpr int NQ = NJ * N / 4;   // 16-byte units of the block
+  for (int q = lane; q < NQ; q += 32)
+    reinterpret_cast<float4*>(dst)[q] = reinterpret_cast<const float4*>(stage)[q];
+}
 
 __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepParams p) {
-  __shared__ float xs[PREP_WARPS][KPAD];
+  __shared__ __align__(16) float xrow[PREP_WARPS][PREP_XPITCH];   // [beta | pose feature | 0] of the block's samples
+  __shared__ __align__(16) float xs[PREP_WARPS][PREP_STAGE];      // per-warp staging of the outputs
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * PREP_WARPS + warp;
-  if (b >= p.B) return;
+  const int b0 = blockIdx.x * PREP_WARPS;
+  const bool valid = b0 + warp < p.B;
+  const int b = valid ? b0 + warp : p.B - 1;   // warps past the batch redo the last sample and store nothing
   const int j = lane < NJ ? lane : 0;  // lanes 24..31 shadow joint 0, never store
-  const bool act = lane < NJ;
+  const bool act = lane < NJ && valid;
 
   const float* th = p.theta + (size_t)b * (NJ * 3) + j * 3;
   const float tx = th[0], ty = th[1], tz = th[2];
@@ -37,53 +60,56 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
 #pragma unroll
     for (int k = 0; k < NB; ++k) bad_b |= !(fabsf(beta[k]) <= 65504.0f);
     const bool bad_t = !(fabsf(tx) <= 3.0e38f) || !(fabsf(ty) <= 3.0e38f) || !(fabsf(tz) <= 3.0e38f);
-    const int f = (bad_b ? 1 : 0) | ((act && bad_t) ? 2 : 0);
-    if (f && (lane == 0 || (f & 2))) atomicOr(p.status, f);
+    const int f = (bad_b ? 1 : 0) | ((lane < NJ && bad_t) ? 2 : 0);
+    if (valid && f && (lane == 0 || (f & 2))) atomicOr(p.status, f);
   }
   float J[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    float acc = __ldg(p.Jbar + j * 3 + c);
+    float acc = __ldg(p.JSt + (3 * NB + c) * 32 + j);
 #pragma unroll
-    for (int k = 0; k < NB; ++k) acc = fmaf(__ldg(p.JS + (j * 3 + c) * NB + k), beta[k], acc);
+    for (int k = 0; k < NB; ++k) acc = fmaf(__ldg(p.JSt + (c * NB + k) * 32 + j), beta[k], acc);
     J[c] = acc;
   }
 
   // GEMM A-operand row: [beta(10) | vec(R_1..23 - I)(207) | 0(7)]
-  if (p.Ximg) {
-    float* x = xs[warp];
+  {
+    float* x = xrow[warp];
     if (lane < NB) x[lane] = beta[lane];
     if (lane < KPAD - KDIM) x[KDIM + lane] = 0.f;
-    if (act && lane >= 1) {
+    if (lane >= 1 && lane < NJ) {
       float* f = x + NB + (lane - 1) * 9;
 #pragma unroll
       for (int e = 0; e < 9; ++e) f[e] = R[e] - ((e == 0 || e == 4 || e == 8) ? 1.0f : 0.0f);
     }
-    __syncwarp();
+  }
+  __syncthreads();
+  if (p.Ximg) {
+    // 16-bit split image (ximg16_off): for one k-chunk of 8 the samples of a tile are 16 bytes apart, so thread
+    // (chunk q, sample s) of the block converts 8 values and the 8 samples of a chunk leave as one 128-byte line per part
+    const int s8 = threadIdx.x & 7, q = threadIdx.x >> 3;
+    if (q < KPAD / 8 && b0 + s8 < p.B) {
+      const float4 v0 = *reinterpret_cast<const float4*>(&xrow[s8][q * 8]);
+      const float4 v1 = *reinterpret_cast<const float4*>(&xrow[s8][q * 8 + 4]);
+      const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+      uint32_t h[4], l[4], bf[4];
 #pragma unroll
-    for (int i = 0; i < KPAD / 32; ++i) {
-      const int k = lane + 32 * i;
-      const float v = x[k];
+      for (int i = 0; i < 4; ++i) {
+        const unsigned short ha = f16_rne_bits(v[2 * i]), hb = f16_rne_bits(v[2 * i + 1]);
+        h[i] = (uint32_t)ha | ((uint32_t)hb << 16);
+        l[i] = (uint32_t)f16_rne_bits(v[2 * i] - f16_bits_to_float(ha)) |
+               ((uint32_t)f16_rne_bits(v[2 * i + 1] - f16_bits_to_float(hb)) << 16);
+        bf[i] = (uint32_t)bf16_rne_bits(v[2 * i]) | ((uint32_t)bf16_rne_bits(v[2 * i + 1]) << 16);
+      }
       unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg);
-      const unsigned short h = f16_rne_bits(v);
-      x16[ximg16_off(b, k, 0)] = h;
-      x16[ximg16_off(b, k, 1)] = f16_rne_bits(v - f16_bits_to_float(h));
-      x16[ximg16_off(b, k, 2)] = bf16_rne_bits(v);
+      *reinterpret_cast<uint4*>(x16 + ximg16_off(b0 + s8, q * 8, 0)) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(x16 + ximg16_off(b0 + s8, q * 8, 1)) = make_uint4(l[0], l[1], l[2], l[3]);
+      *reinterpret_cast<uint4*>(x16 + ximg16_off(b0 + s8, q * 8, 2)) = make_uint4(bf[0], bf[1], bf[2], bf[3]);
     }
   }
-  if (p.Ximg2) {
+  if (p.Ximg2 && valid) {
     // operand image of the fused forward (ff_ximg_off): [Xh | Xl] per K16 step, sample-major inside the chunk half
-    float* x = xs[warp];
-    if (!p.Ximg) {
-      if (lane < NB) x[lane] = beta[lane];
-      if (lane < KPAD - KDIM) x[KDIM + lane] = 0.f;
-      if (act && lane >= 1) {
-        float* f = x + NB + (lane - 1) * 9;
-#pragma unroll
-        for (int e = 0; e < 9; ++e) f[e] = R[e] - ((e == 0 || e == 4 || e == 8) ? 1.0f : 0.0f);
-      }
-      __syncwarp();
-    }
+    const float* x = xrow[warp];
     unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg2);
 #pragma unroll
     for (int i = 0; i < KPAD / 32; ++i) {
@@ -94,33 +120,46 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       x16[ff_ximg_off(b, k, 1)] = f16_rne_bits(v - f16_bits_to_float(h));
     }
   }
+  if (!valid) return;   // no block-wide barrier below
 
-  // kinematic chain: G = (GR, Gt).  Root: (R_0, J_0).  Level d: G_i = G_parent * [R_i | J_i - J_parent]
+  // kinematic chain G_i = L_root ... L_i with L_m = (R_m, J_m - J_parent(m)) (batch_lbs.py:122-136) by pointer jumping:
+  // round r composes every joint with its 2^r-th ancestor -- ceil(log2(depth + 1)) = 4 rounds for SMPL instead of one
+  // pass per tree level (8)
   float GR[9], Gt[3];
+  {
+    const int4 t0 = __ldg(p.tree_tab + 64 + lane * 2), t1 = __ldg(p.tree_tab + 64 + lane * 2 + 1);
+    const int up[5] = {t0.z, t0.w, t1.x, t1.y, t1.z};
+    const int par = up[0] >= 0 ? up[0] : 0;
 #pragma unroll
-  for (int e = 0; e < 9; ++e) GR[e] = R[e];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) Gt[c] = J[c];
-  const int par = p.tree.parent[j];
-  const int dep = act ? p.tree.depth[j] : -1;
-  for (int d = 1; d <= p.tree.max_depth; ++d) {
-    float pR[9], pt[3], pJ[3];
-#pragma unroll
-    for (int e = 0; e < 9; ++e) pR[e] = __shfl_sync(0xffffffffu, GR[e], par);
+    for (int e = 0; e < 9; ++e) GR[e] = R[e];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      pt[c] = __shfl_sync(0xffffffffu, Gt[c], par);
-      pJ[c] = __shfl_sync(0xffffffffu, J[c], par);
+      const float pj = __shfl_sync(0xffffffffu, J[c], par);
+      Gt[c] = up[0] >= 0 ? J[c] - pj : J[c];
     }
-    if (dep == d) {
-      const float r0 = J[0] - pJ[0], r1 = J[1] - pJ[1], r2 = J[2] - pJ[2];
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
+    for (int r = 0; r < 5; ++r) {
+      if (r < p.n_rounds) {
+        const int a = up[r] >= 0 ? up[r] : 0;
+        float aR[9], at[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c)
-          GR[r * 3 + c] = pR[r * 3 + 0] * R[0 * 3 + c] + pR[r * 3 + 1] * R[1 * 3 + c] +
-                          pR[r * 3 + 2] * R[2 * 3 + c];
-        Gt[r] = pR[r * 3 + 0] * r0 + pR[r * 3 + 1] * r1 + pR[r * 3 + 2] * r2 + pt[r];
+        for (int e = 0; e < 9; ++e) aR[e] = __shfl_sync(0xffffffffu, GR[e], a);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) at[c] = __shfl_sync(0xffffffffu, Gt[c], a);
+        if (up[r] >= 0) {
+          float nR[9], nt[3];
+#pragma unroll
+          for (int rr = 0; rr < 3; ++rr) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+              nR[rr * 3 + c] = aR[rr * 3 + 0] * GR[c] + aR[rr * 3 + 1] * GR[3 + c] + aR[rr * 3 + 2] * GR[6 + c];
+            nt[rr] = aR[rr * 3 + 0] * Gt[0] + aR[rr * 3 + 1] * Gt[1] + aR[rr * 3 + 2] * Gt[2] + at[rr];
+          }
+#pragma unroll
+          for (int e = 0; e < 9; ++e) GR[e] = nR[e];
+#pragma unroll
+          for (int c = 0; c < 3; ++c) Gt[c] = nt[c];
+        }
       }
     }
   }
@@ -131,46 +170,50 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
     for (int u = lane - NJ; u < 24; u += 32 - NJ)
       *reinterpret_cast<uint4*>(a16 + ff_aimg_off(b, NJ, u % 12, u / 12)) = make_uint4(0u, 0u, 0u, 0u);
   }
-  if (!act && p.Aimg) {
-    // joints 24..31 of the padded K: the W columns are zero, these must be finite -> zero (workspace is not cleared).
-    // Per (part, component e) the 8 pad joints are one 16-byte unit: 24 units per sample, spread over lanes 24..31.
+  if (p.Aimg) {
+    // skinning-GEMM B operand (aimg16_off): per part and chunk of 8 joints one sample owns 12 x 16 = 192 contiguous
+    // bytes.  Every lane (joints 24..31 of the padded K are zero: the W columns are zero, the image must be finite)
+    // puts its 2 x 12 halves into the staged [part][chunk][e][8] block; the warp then stores 96 16-byte units.
+    unsigned short* st16 = reinterpret_cast<unsigned short*>(xs[warp]);
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const float tr = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
+      const float row[4] = {GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const float val = lane < NJ ? row[c] : 0.f;
+        const unsigned short h = f16_rne_bits(val);
+        st16[(((lane >> 3)) * 12 + r * 4 + c) * 8 + (lane & 7)] = h;
+        st16[((4 + (lane >> 3)) * 12 + r * 4 + c) * 8 + (lane & 7)] = f16_rne_bits(val - f16_bits_to_float(h));
+      }
+    }
+    __syncwarp();
     unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg);
-    for (int u = lane - NJ; u < 24; u += 32 - NJ)
-      *reinterpret_cast<uint4*>(a16 + aimg16_off(b, NJ, u % 12, u / 12)) = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int u = lane + 32 * i, part = u / 48, chunk = (u % 48) / 12, e = u % 12;
+      *reinterpret_cast<uint4*>(a16 + aimg16_off(b, chunk * 8, e, part)) = reinterpret_cast<const uint4*>(st16)[u];
+    }
   }
+  float uvv[2] = {0.f, 0.f}, pxv[2] = {0.f, 0.f};
   if (act) {
-    if (p.joints) {
+    if (p.joints && !p.staged) {
       float* o = p.joints + ((size_t)b * NJ + j) * 3;
       o[0] = Gt[0]; o[1] = Gt[1]; o[2] = Gt[2];
     }
-    if (p.Rs) {
+    if (p.Rs && !p.staged) {
       float* o = p.Rs + ((size_t)b * NJ + j) * 9;
 #pragma unroll
       for (int e = 0; e < 9; ++e) o[e] = R[e];
     }
-    if (p.A) {
+    if (p.A && !p.staged) {
       // A = G - [0 | G.R J] (batch_lbs.py:138-142): rows [R | t - R J]
       float4* o = reinterpret_cast<float4*>(p.A + ((size_t)b * NJ + j) * 12);
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
         const float tr = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
         o[r] = make_float4(GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr);
-      }
-    }
-    if (p.Aimg) {
-      // skinning-GEMM B operand: component e of joint j of sample b in the 16-bit split format (common.cuh)
-      unsigned short* a16 = reinterpret_cast<unsigned short*>(p.Aimg);
-#pragma unroll
-      for (int r = 0; r < 3; ++r) {
-        const float tr = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
-        const float row[4] = {GR[r * 3 + 0], GR[r * 3 + 1], GR[r * 3 + 2], tr};
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const unsigned short h = f16_rne_bits(row[c]);
-          const float hf = f16_bits_to_float(h);
-          a16[aimg16_off(b, j, r * 4 + c, 0)] = h;
-          a16[aimg16_off(b, j, r * 4 + c, 1)] = f16_rne_bits(row[c] - hf);
-        }
       }
     }
     if (p.Aimg2) {
@@ -194,20 +237,40 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       float Rc[9], q[3], u, v;
       rodrigues_cam(__ldg(cr), __ldg(cr + 1), __ldg(cr + 2), Rc);
       project_point(Rc, Gt[0], Gt[1], Gt[2], __ldg(cp), __ldg(cp + 1), __ldg(cp + 2), f, u, v, q);
-      if (p.uv) reinterpret_cast<float2*>(p.uv)[(size_t)b * NJ + j] = make_float2(u, v);
-      if (p.px) {
-        float x, y;
-        to_pixels(u, v, p.cfg, x, y);
-        reinterpret_cast<float2*>(p.px)[(size_t)b * NJ + j] = make_float2(x, y);
+      uvv[0] = u; uvv[1] = v;
+      to_pixels(u, v, p.cfg, pxv[0], pxv[1]);
+      if (!p.staged) {
+        if (p.uv) reinterpret_cast<float2*>(p.uv)[(size_t)b * NJ + j] = make_float2(u, v);
+        if (p.px) reinterpret_cast<float2*>(p.px)[(size_t)b * NJ + j] = make_float2(pxv[0], pxv[1]);
       }
     }
+  }
+  if (p.staged) {   // uniform over the warp
+    float* stage = xs[warp];
+    if (p.joints) store_staged(stage, p.joints + (size_t)b * NJ * 3, Gt, lane, act);
+    if (p.Rs) store_staged(stage, p.Rs + (size_t)b * NJ * 9, R, lane, act);
+    if (p.A) {
+      // A = G - [0 | G.R J] (batch_lbs.py:138-142): rows [R | t - R J]
+      float a[12];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        a[r * 4 + 0] = GR[r * 3 + 0]; a[r * 4 + 1] = GR[r * 3 + 1]; a[r * 4 + 2] = GR[r * 3 + 2];
+        a[r * 4 + 3] = Gt[r] - (GR[r * 3 + 0] * J[0] + GR[r * 3 + 1] * J[1] + GR[r * 3 + 2] * J[2]);
+      }
+      store_staged(stage, p.A + (size_t)b * NJ * 12, a, lane, act);
+    }
+    if (p.cam_pos && p.uv) store_staged(stage, p.uv + (size_t)b * NJ * 2, uvv, lane, act);
+    if (p.cam_pos && p.px) store_staged(stage, p.px + (size_t)b * NJ * 2, pxv, lane, act);
   }
 }
 
 int32_t launch_pose_prep(const PrepParams& p, cudaStream_t st) {
   if (p.B <= 0) return SMPLB_OK;
   const int grid = (p.B + PREP_WARPS - 1) / PREP_WARPS;
-  pose_prep_kernel<<<grid, PREP_WARPS * 32, 0, st>>>(p);
+  PrepParams q = p;
+  // the staged 16-byte stores need 16-byte aligned outputs (every per-sample block is a multiple of 96 bytes)
+  q.staged = (((uintptr_t)p.joints | (uintptr_t)p.Rs | (uintptr_t)p.A | (uintptr_t)p.uv | (uintptr_t)p.px) & 15) == 0;
+  pose_prep_kernel<<<grid, PREP_WARPS * 32, 0, st>>>(q);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }
