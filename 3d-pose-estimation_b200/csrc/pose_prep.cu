@@ -1,6 +1,6 @@
 // K1 pose_prep: one warp per sample, lane = joint.
 //   Rodrigues x24 (batch_lbs.py:38-57)  ->  207-d pose feature (batch_smpl.py:107-110) written as the
-//   TF32 hi/lo split A-operand of the blend GEMM, beta in columns 0..9;
+//   f16 / f16-residual / bf16 split A-operand image of the blend GEMM (ximg16_off), beta in columns 0..9;
 //   folded joint regression J = Jbar + JS beta (batch_smpl.py:91-101);
 //   kinematic chain by pointer jumping with warp shuffles (batch_lbs.py:84-144);
 //   J_transformed, relative skinning transforms A[B,24,3,4];

@@ -61,6 +61,15 @@ class FitIO(C.Structure):
                 ('step_dev', C.c_void_p)]
 
 
+class PhongIO(C.Structure):
+    _fields_ = [('B', C.c_int32), ('H', C.c_int32), ('W', C.c_int32), ('C', C.c_int32), ('L', C.c_int32),
+                ('off_normal', C.c_int32), ('off_position', C.c_int32), ('off_diffuse', C.c_int32),
+                ('off_specular', C.c_int32), ('off_shininess', C.c_int32), ('normalize_normals', C.c_int32),
+                ('attr', C.c_void_p), ('alphas', C.c_void_p), ('shininess', C.c_void_p),
+                ('light_positions', C.c_void_p), ('light_intensities', C.c_void_p), ('camera', C.c_void_p),
+                ('ambient', C.c_void_p)]
+
+
 # name -> (restype, argtypes); every symbol include/smplb200.h declares
 SYMBOLS = {
     'smplb_last_error': (C.c_char_p, []),
@@ -105,6 +114,10 @@ SYMBOLS = {
     'smplb_render_diffuse': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'smplb_phong_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    'smplb_phong_shade': (C.c_int32, [C.POINTER(PhongIO), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'smplb_phong_shade_backward': (C.c_int32, [C.POINTER(PhongIO), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_size_t, C.c_void_p]),
     'smplb_add_axis_angle': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_rotate_global_pose': (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_cam_losses_scratch_bytes': (C.c_size_t, [C.c_int32]),

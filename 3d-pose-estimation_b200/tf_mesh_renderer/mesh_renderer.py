@@ -4,51 +4,42 @@ mesh_renderer(...) keeps the reference signature (mesh_renderer.py:197-213).  Tw
  * no specular terms and no gradient wanted (the way pose_3d renders, utils.py:45-50): ONE fused pass in
    csrc/raster.cu (`smplb_render_diffuse`: clip transform, rasterisation, perspective-correct interpolation and
    diffuse Phong shading; only RGBA reaches HBM);
- * otherwise the reference's graph restated on torch tensors around the rasteriser kernels (differentiable wrt
-   vertices, normals and colours like the TF graph: rasterize_triangles drop-in + phong_shader below).
+ * otherwise rasterize_triangles (kernel rasteriser + its gradient kernel; the attribute interpolation around it is the
+   reference's element-wise graph on torch tensors) followed by the shading kernels of csrc/shade.cu: specular term,
+   forward and adjoint (differentiable wrt vertices, normals and colours like the TF graph).
 """
 import torch
 
+from smplb200 import shade
 from smplb200.raster import Mesh
 
 from . import camera_utils
 from . import rasterize_triangles as rt
 
 
-def _l2n(x, dim):
-    return x / torch.sqrt(torch.clamp((x * x).sum(dim, keepdim=True), min=1e-12))
-
-
 def phong_shader(normals, alphas, pixel_positions, light_positions, light_intensities, diffuse_colors=None,
                  camera_position=None, specular_colors=None, shininess_coefficients=None, ambient_color=None):
-    """mesh_renderer.py:23-162 ([B,H,W,*] buffers -> lit RGBA [B,H,W,4], rows reversed)."""
+    """mesh_renderer.py:23-162 ([B,H,W,*] buffers -> lit RGBA [B,H,W,4], rows reversed) on the shading kernels of
+    csrc/shade.cu (forward and adjoint).  The separate buffers of the reference signature are packed into the
+    interleaved attribute image the kernels read; mesh_renderer below hands over its attribute image as it is."""
     B, H, W = normals.shape[:3]
-    L = light_positions.shape[1]
-    normals = normals.reshape(B, -1, 3)
-    alphas = alphas.reshape(B, -1, 1)
-    diffuse_colors = diffuse_colors.reshape(B, -1, 3)
-    out = torch.zeros((B, H * W, 3), dtype=normals.dtype, device=normals.device)
-    if ambient_color is not None:
-        out = out + ambient_color.unsqueeze(1) * diffuse_colors
-    pos = pixel_positions.reshape(B, -1, 3)
-    to_l = _l2n(light_positions.unsqueeze(2) - pos.unsqueeze(1), 3)
-    ndl = torch.clamp((normals.unsqueeze(1) * to_l).sum(3), 0.0, 1.0)
-    out = out + (diffuse_colors.unsqueeze(1) * ndl.unsqueeze(3) * light_intensities.unsqueeze(2)).sum(1)
+    dev = normals.device
+    parts = [normals.reshape(B, H, W, 3), pixel_positions.reshape(B, H, W, 3), diffuse_colors.reshape(B, H, W, 3)]
+    off_spec = off_shin = -1
+    shin_img = None
     if camera_position is not None:
-        spec = specular_colors.reshape(B, -1, 3)
-        mirror = _l2n(2.0 * ndl.unsqueeze(3) * normals.unsqueeze(1) - to_l, 3)
-        to_cam = _l2n(camera_position.reshape(B, 1, 3) - pos, 2)
-        rdc = (to_cam.unsqueeze(1) * mirror).sum(3)
-        rdc = torch.clamp(_l2n(rdc, 2), 0.0, 1.0)              # normalised over the pixel axis, as the reference does
-        rdc = torch.where(ndl != 0.0, rdc, torch.zeros_like(rdc)).reshape(B, L, H, W)
-        shin = torch.as_tensor(shininess_coefficients, dtype=normals.dtype, device=normals.device)
-        shin = shin if shin.dim() == 3 else shin.reshape(-1, 1, 1)
-        specularity = torch.pow(rdc, shin.unsqueeze(1)).reshape(B, L, H * W, 1)
-        out = out + (spec.unsqueeze(1) * specularity * light_intensities.unsqueeze(2)).sum(1)
-    rgb = out.reshape(B, H, W, 3)
-    a = alphas.reshape(B, H, W, 1)
-    rgb = torch.where((a > 0.5).expand(-1, -1, -1, 3), rgb, torch.zeros_like(rgb))
-    return torch.flip(torch.cat([rgb, a], dim=3), dims=[1])
+        parts.append(specular_colors.reshape(B, H, W, 3))
+        off_spec = 9
+        shin = torch.as_tensor(shininess_coefficients, dtype=torch.float32, device=dev)
+        if shin.dim() == 3 and tuple(shin.shape[1:]) == (H, W):
+            parts.append(shin.expand(B, H, W).unsqueeze(3))                      # per pixel
+            off_shin = 12
+        else:
+            shin_img = shin.reshape(-1).expand(B).contiguous()                   # [B,1,1] | [1,1,1] | scalar
+    attr = torch.cat([p.to(torch.float32) for p in parts], dim=3)
+    return shade.phong_shade(attr, light_positions, light_intensities, 0, 3, 6, off_spec, off_shin,
+                             alphas=alphas.reshape(B, H, W), shininess=shin_img, camera_position=camera_position,
+                             ambient_color=ambient_color)
 
 
 def tone_mapper(image, gamma):
@@ -136,12 +127,12 @@ def mesh_renderer(vertices, triangles, normals, diffuse_colors, camera_position,
         attrs = torch.cat([normals, vertices, diffuse_colors], dim=2)                          # :361
     px = rt.rasterize_triangles(vertices, attrs, mesh, clip_tf, image_width, image_height,
                                 [-1.0] * attrs.shape[2])                                      # :371-373
-    pn = _l2n(px[..., 0:3], 3)                                                                 # :376
-    ppos, pdiff = px[..., 3:6], px[..., 6:9]
-    pspec = shin = None
-    if specular_colors is not None:
-        pspec = px[..., 9:12]
-        shin = px[..., 12] if per_vertex_shin else shininess_coefficients.reshape(-1, 1, 1)    # :381-385
-    mask = (pdiff >= 0).any(dim=3).to(torch.float32)                                           # :387
-    return phong_shader(pn, mask, ppos, light_positions, light_intensities, pdiff,
-                        camera_position if specular_colors is not None else None, pspec, shin, ambient_color)
+    # :375-400: normalise the interpolated normals, alpha = any(diffuse >= 0), Phong shading -- one kernel pass over the
+    # attribute image as rasterize_triangles returned it (csrc/shade.cu), differentiable through smplb_phong_shade_backward
+    has_spec = specular_colors is not None
+    shin_img = None
+    if has_spec and not per_vertex_shin:
+        shin_img = shininess_coefficients.reshape(-1).expand(B).contiguous()                   # :381-385
+    return shade.phong_shade(px, light_positions, light_intensities, 0, 3, 6, 9 if has_spec else -1,
+                             12 if per_vertex_shin else -1, alphas=None, normalize_normals=True, shininess=shin_img,
+                             camera_position=camera_position if has_spec else None, ambient_color=ambient_color)

@@ -291,6 +291,35 @@ int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const float* verts,
                              const float* light_intensities, int32_t L, const float* ambient, int32_t W, int32_t H,
                              float* rgba, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Phong shading of interpolated attribute images with the specular term, and its adjoint (SURVEY.md 8f N1:
+ * deps/tf_mesh_renderer/mesh_renderer.py:23-162 phong_shader, and the part of mesh_renderer :375-400 between the
+ * rasterised attribute image and the lit image; TF differentiates this graph, so does the backward entry point).
+ * attr [B,H,W,C]: the attribute image exactly as rasterize_triangles returns it, channels addressed by offsets:
+ * off_normal (3), off_position (3), off_diffuse (3), off_specular (3, or -1: no specular term), off_shininess (1, or -1:
+ * shininess [B] per image).  normalize_normals != 0: the normals are l2-normalised first (mesh_renderer.py:376).
+ * alphas [B,H,W] or NULL: alpha = any(diffuse >= 0) (mesh_renderer.py:387).  camera [B,3] is needed with a specular term.
+ * The reference normalises reflection . camera over the PIXEL axis (:134-136, tf.nn.l2_normalize(axis=2)); that
+ * quirk is reproduced, which makes the specular term a two-pass computation.  rgba [B,H,W,4], rows reversed (:162).
+ * Lights are constants (no gradient).  L <= 8.  scratch: smplb_phong_scratch_bytes(B, H, W, L) bytes; the backward call
+ * must get the scratch of the forward call of the same inputs untouched (it holds the per-image norms).
+ * g_attr [B,H,W,C] receives the gradient of every channel (unused channels: 0); g_alphas [B,H,W] or NULL. */
+typedef struct {
+  int32_t B, H, W, C, L;
+  int32_t off_normal, off_position, off_diffuse, off_specular, off_shininess;
+  int32_t normalize_normals;
+  const float* attr;
+  const float* alphas;
+  const float* shininess;        /* [B], used when off_shininess < 0 and off_specular >= 0 */
+  const float* light_positions;  /* [B,L,3] */
+  const float* light_intensities;/* [B,L,3] */
+  const float* camera;           /* [B,3] */
+  const float* ambient;          /* [B,3] or NULL */
+} smplb_phong_io;
+size_t smplb_phong_scratch_bytes(int32_t B, int32_t H, int32_t W, int32_t L);
+int32_t smplb_phong_shade(const smplb_phong_io* io, float* rgba, void* scratch, size_t scratch_bytes, void* stream);
+int32_t smplb_phong_shade_backward(const smplb_phong_io* io, const float* g_rgba, float* g_attr, float* g_alphas,
+                                   void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- Per-sample operators either side of the path ---------------------------------
  * add_axis_angle_rotations (deps/pose_3d/utils.py:170-199): rv1, rv2 [N,3] -> axis-angle of "rv2 then rv1". */
 int32_t smplb_add_axis_angle(int32_t N, const float* rv1, const float* rv2, float* out, void* stream);

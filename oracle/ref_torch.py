@@ -213,3 +213,41 @@ def cam_reg_losses(cam_pos, cam_rot, f_raw):
     nrm = torch.linalg.norm(cam_rot.reshape(-1, 3), dim=1)
     big = torch.where(nrm > math.pi * 0.125, nrm, torch.zeros_like(nrm))
     return (neg * neg).mean(), 10.0 * (big * big).mean()
+
+
+def _l2n(x, dim):
+    """tf.nn.l2_normalize: x * rsqrt(max(sum(x^2), 1e-12))."""
+    return x / torch.sqrt(torch.clamp((x * x).sum(dim, keepdim=True), min=1e-12))
+
+
+def phong_shader(normals, alphas, pixel_positions, light_positions, light_intensities, diffuse_colors=None,
+                 camera_position=None, specular_colors=None, shininess_coefficients=None, ambient_color=None):
+    """deps/tf_mesh_renderer/mesh_renderer.py:23-162 on torch tensors (any dtype; autograd gives the gradients TF's
+    would): [B,H,W,*] buffers -> lit RGBA [B,H,W,4], rows reversed.  Checker of csrc/shade.cu."""
+    B, H, W = normals.shape[:3]
+    L = light_positions.shape[1]
+    normals = normals.reshape(B, -1, 3)
+    alphas = alphas.reshape(B, -1, 1)
+    diffuse_colors = diffuse_colors.reshape(B, -1, 3)
+    out = torch.zeros((B, H * W, 3), dtype=normals.dtype, device=normals.device)
+    if ambient_color is not None:
+        out = out + ambient_color.unsqueeze(1) * diffuse_colors                                # :92-94
+    pos = pixel_positions.reshape(B, -1, 3)
+    to_l = _l2n(light_positions.unsqueeze(2) - pos.unsqueeze(1), 3)                            # :100-102
+    ndl = torch.clamp((normals.unsqueeze(1) * to_l).sum(3), 0.0, 1.0)                          # :106-109
+    out = out + (diffuse_colors.unsqueeze(1) * ndl.unsqueeze(3) * light_intensities.unsqueeze(2)).sum(1)   # :112-118
+    if camera_position is not None:
+        spec = specular_colors.reshape(B, -1, 3)
+        mirror = _l2n(2.0 * ndl.unsqueeze(3) * normals.unsqueeze(1) - to_l, 3)                 # :123-126
+        to_cam = _l2n(camera_position.reshape(B, 1, 3) - pos, 2)                               # :127-128
+        rdc = (to_cam.unsqueeze(1) * mirror).sum(3)                                            # :129-132
+        rdc = torch.clamp(_l2n(rdc, 2), 0.0, 1.0)                                              # :134-136 (over pixels!)
+        rdc = torch.where(ndl != 0.0, rdc, torch.zeros_like(rdc)).reshape(B, L, H, W)          # :140-146
+        shin = torch.as_tensor(shininess_coefficients, dtype=normals.dtype, device=normals.device)
+        shin = shin if shin.dim() == 3 else shin.reshape(-1, 1, 1)
+        specularity = torch.pow(rdc, shin.unsqueeze(1)).reshape(B, L, H * W, 1)                # :148-152
+        out = out + (spec.unsqueeze(1) * specularity * light_intensities.unsqueeze(2)).sum(1)  # :153-157
+    rgb = out.reshape(B, H, W, 3)
+    a = alphas.reshape(B, H, W, 1)
+    rgb = torch.where((a > 0.5).expand(-1, -1, -1, 3), rgb, torch.zeros_like(rgb))             # :160-161
+    return torch.flip(torch.cat([rgb, a], dim=3), dims=[1])                                    # :162
