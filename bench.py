@@ -705,8 +705,9 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
-        if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
-            os.environ['NCCL_DEBUG'] = 'WARN'      # keep NCCL's version banner out of the one-JSON-line stdout
+        # NCCL prints its version banner (NCCL_DEBUG=VERSION and WARN both do) to stdout: send its log to stderr so that
+        # stdout stays the one JSON line
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
 
     import smplb200
