@@ -114,6 +114,14 @@ SYMBOLS = {
     'smplb_render_diffuse': (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'smplb_clip_transform': (C.c_int32, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'smplb_clip_transform_backward': (C.c_int32, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                  C.c_void_p, C.c_void_p]),
+    'smplb_interpolate': (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    'smplb_interpolate_backward': (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]),
     'smplb_phong_scratch_bytes': (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
     'smplb_phong_shade': (C.c_int32, [C.POINTER(PhongIO), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     'smplb_phong_shade_backward': (C.c_int32, [C.POINTER(PhongIO), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -138,3 +138,79 @@ class _Rasterize(torch.autograd.Function):
 
 def rasterize_ndc(ndc, mesh, W, H):
     return _Rasterize.apply(ndc, mesh, W, H)
+
+
+def _stream(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+class _ClipTransform(torch.autograd.Function):
+    """rasterize_triangles.py:73-86 (csrc/interp.cu): verts [B,V,3], clip matrices [B,4,4] -> ndc [B,V,3], clip_w [B,V]."""
+
+    @staticmethod
+    def forward(ctx, verts, clip_tf):
+        dev = verts.device
+        verts, clip_tf = verts.to(torch.float32).contiguous(), clip_tf.to(dev, torch.float32).contiguous()
+        B, V = verts.shape[0], verts.shape[1]
+        ndc = torch.empty((B, V, 3), dtype=torch.float32, device=dev)
+        cw = torch.empty((B, V), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(_lib.lib().smplb_clip_transform(B, V, _ptr(verts), _ptr(clip_tf), _ptr(ndc), _ptr(cw), _stream(dev)))
+        ctx.save_for_backward(verts, clip_tf)
+        return ndc, cw
+
+    @staticmethod
+    def backward(ctx, g_ndc, g_cw):
+        verts, clip_tf = ctx.saved_tensors
+        dev = verts.device
+        B, V = verts.shape[0], verts.shape[1]
+        g_ndc = torch.zeros_like(verts) if g_ndc is None else g_ndc.to(torch.float32).contiguous()
+        g_cw = None if g_cw is None else g_cw.to(torch.float32).contiguous()
+        g = torch.empty_like(verts)
+        with torch.cuda.device(dev):
+            check(_lib.lib().smplb_clip_transform_backward(B, V, _ptr(verts), _ptr(clip_tf), _ptr(g_ndc), _ptr(g_cw), _ptr(g),
+                                                           _stream(dev)))
+        return g, None
+
+
+class _Interpolate(torch.autograd.Function):
+    """rasterize_triangles.py:119-164 (csrc/interp.cu): attributes [B,V,C], clip_w [B,V], bary [B,H,W,3], ids [B,H,W],
+    background [C] -> images [B,H,W,C]; differentiable wrt attributes, clip_w and bary."""
+
+    @staticmethod
+    def forward(ctx, attr, clip_w, bary, ids, bg, mesh):
+        dev = attr.device
+        f = lambda x: x.to(dev, torch.float32).contiguous()
+        attr, clip_w, bary, bg = f(attr), f(clip_w), f(bary), f(bg)
+        ids = ids.to(dev, torch.int32).contiguous()
+        B, H, W = ids.shape
+        Cn = attr.shape[2]
+        out = torch.empty((B, H, W, Cn), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(_lib.lib().smplb_interpolate(mesh._h, B, Cn, _ptr(attr), _ptr(clip_w), _ptr(bary), _ptr(ids), _ptr(bg), W, H,
+                                               _ptr(out), _stream(dev)))
+        ctx.mesh = mesh
+        ctx.save_for_backward(attr, clip_w, bary, ids, bg)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        attr, clip_w, bary, ids, bg = ctx.saved_tensors
+        dev = attr.device
+        B, H, W = ids.shape
+        Cn = attr.shape[2]
+        g_out = g_out.to(torch.float32).contiguous()
+        g_attr, g_cw, g_bary = torch.empty_like(attr), torch.empty_like(clip_w), torch.empty_like(bary)
+        with torch.cuda.device(dev):
+            check(_lib.lib().smplb_interpolate_backward(ctx.mesh._h, B, Cn, _ptr(attr), _ptr(clip_w), _ptr(bary), _ptr(ids),
+                                                        _ptr(bg), W, H, _ptr(g_out), _ptr(g_attr), _ptr(g_cw), _ptr(g_bary),
+                                                        _stream(dev)))
+        return g_attr, g_cw, g_bary, None, None, None
+
+
+def clip_transform(verts, clip_tf):
+    return _ClipTransform.apply(verts, clip_tf)
+
+
+def interpolate(attr, clip_w, bary, ids, background, mesh):
+    return _Interpolate.apply(attr, clip_w, bary, ids, background, mesh)

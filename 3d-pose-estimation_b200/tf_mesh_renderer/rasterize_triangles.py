@@ -3,12 +3,12 @@
 Same call: rasterize_triangles(vertices, attributes, triangles, projection_matrices, image_width,
 image_height, background_value) -> [batch, H, W, attribute_count].  The rasterisation itself
 (RasterizeTriangles / RasterizeTrianglesGrad custom ops of the reference) runs in csrc/raster.cu for the whole
-batch at once; the clip-space transform and the perspective-correct attribute interpolation around it are the
-reference's own element-wise graph (rasterize_triangles.py:73-178) restated on torch CUDA tensors, so autograd
-reaches vertices and attributes exactly as TF's does."""
+batch at once; the clip-space transform and the perspective-correct attribute interpolation around it
+(rasterize_triangles.py:73-178) are kernels with hand-written adjoints too (csrc/interp.cu), so autograd reaches
+vertices and attributes exactly as TF's does and every pixel and every gradient is computed by this library."""
 import torch
 
-from smplb200.raster import Mesh, rasterize_ndc
+from smplb200.raster import Mesh, clip_transform, interpolate, rasterize_ndc
 
 _MINIMUM_REWEIGHTING_THRESHOLD = 1e-6
 _MINIMUM_PERSPECTIVE_DIVIDE_THRESHOLD = 1e-6
@@ -42,25 +42,11 @@ def rasterize_triangles(vertices, attributes, triangles, projection_matrices, im
     B, V = vertices.shape[0], vertices.shape[1]
     mesh = _mesh_for(triangles, V, dev)
 
-    # rasterize_triangles.py:73-86: homogeneous clip space, guarded perspective divide
-    vh = torch.cat([vertices, torch.ones((B, V, 1), dtype=torch.float32, device=dev)], 2)
-    clip = torch.matmul(vh, projection_matrices.transpose(1, 2))
-    w = clip[:, :, 3:4]
-    clip_w = torch.clamp(w.abs(), min=_MINIMUM_PERSPECTIVE_DIVIDE_THRESHOLD) * torch.sign(w)
-    ndc = clip[:, :, 0:3] / clip_w
-
-    bary, ids, _ = rasterize_ndc(ndc.contiguous(), mesh, image_width, image_height)   # :88-117 (whole batch)
-
-    # :119-152 perspective-correct barycentrics and attribute interpolation
-    vids = mesh.triangles[ids.reshape(B, -1).long()] + (torch.arange(B, device=dev) * V).view(B, 1, 1)
-    vids = vids.reshape(-1, 3)
-    bary = bary.reshape(-1, 3)
-    corner_attr = attributes.reshape(B * V, -1)[vids]
-    corner_w = torch.reciprocal(clip_w.reshape(-1))[vids]
-    weighted = bary * corner_w
-    factor = weighted.sum(1)
-    corrected = weighted / torch.clamp(factor, min=_MINIMUM_REWEIGHTING_THRESHOLD).unsqueeze(1)
-    images = (corner_attr * corrected.unsqueeze(2)).sum(1).reshape(B, image_height, image_width, -1)
-    # :157-178 alpha from the barycentric sum, background compositing
-    alphas = torch.clamp((2.0 * corrected).sum(1), 0.0, 1.0).reshape(B, image_height, image_width, 1)
-    return alphas * images + (1.0 - alphas) * background_value
+    # rasterize_triangles.py:73-86 (clip transform, guarded perspective divide), :88-117 (rasteriser, whole batch),
+    # :119-164 (perspective-correct interpolation, alpha, background): three kernels with their adjoints
+    # (csrc/interp.cu, csrc/raster.cu), chained by autograd exactly where TF's graph chains the ops
+    ndc, clip_w = clip_transform(vertices.contiguous(), projection_matrices)
+    bary, ids, _ = rasterize_ndc(ndc, mesh, image_width, image_height)
+    if background_value.dim() == 0:
+        background_value = background_value.expand(attributes.shape[2])
+    return interpolate(attributes.contiguous(), clip_w, bary, ids, background_value.reshape(-1), mesh)

@@ -221,6 +221,8 @@ int32_t smplb_adam_step_dev(int64_t n, float* x, const float* g, float* m, float
  * B*24*2 so that the shares of several GPUs add up under an all-reduce), loss[1] = min(cap, loss[0]),
  * loss[2] = 1 when the cap is inactive else 0 (the gradient gate of tf.minimum, :237), loss[3] = Adam's lr_t of this
  * step.  The cap acts on the GLOBAL mean, so reproj_cap > 0 requires n_total == B*48 (SMPLB_E_UNSUPPORTED otherwise).
+ * Two launches when the cap is off (forward chain + projection + residual + adjoint + the Adam update of the sample in
+ * one per-sample kernel, then the loss / step-counter kernel), four when it is on (Adam waits for the global loss).
  * Stream-ordered, allocation-free: capturable in a CUDA graph when step_dev is given (the step counter then lives on
  * the device and every replay advances the bias correction; with step_dev == NULL the host value `step` is used and
  * a captured launch would freeze it). */
@@ -290,6 +292,26 @@ int32_t smplb_render_diffuse(const smplb_mesh* m, int32_t B, const float* verts,
                              const float* diffuse, const float* clip_transforms, const float* light_positions,
                              const float* light_intensities, int32_t L, const float* ambient, int32_t W, int32_t H,
                              float* rgba, void* workspace, size_t workspace_bytes, void* stream);
+
+/* The element-wise graph of deps/tf_mesh_renderer/rasterize_triangles.py around the rasteriser op, forward and adjoint
+ * (the gradients TF's autodiff derives for these ops), so that a differentiable render runs on kernels end to end:
+ * clip transform (:73-86) -> smplb_rasterize -> interpolation (:119-164) -> smplb_phong_shade.
+ * smplb_clip_transform: verts [B,V,3], clip_transforms [B,4,4] row-major -> ndc [B,V,3] (guarded perspective divide) and
+ * clip_w [B,V] (the guarded w).  Backward: g_ndc, g_clip_w (nullable) -> g_verts; the matrices are constants.
+ * smplb_interpolate: attributes [B,V,C], clip_w, the rasteriser's bary [B,H,W,3] / ids [B,H,W], background [C] ->
+ * images [B,H,W,C] (perspective-correct interpolation, alpha from the barycentric sum, background compositing).
+ * Backward: g_images -> g_attributes [B,V,C], g_clip_w [B,V] (both zero-filled here, then float atomicAdd: their last bits
+ * depend on the order in which pixels arrive) and g_bary [B,H,W,3] (feeds smplb_rasterize_backward). */
+int32_t smplb_clip_transform(int32_t B, int32_t V, const float* verts, const float* clip_transforms, float* ndc,
+                             float* clip_w, void* stream);
+int32_t smplb_clip_transform_backward(int32_t B, int32_t V, const float* verts, const float* clip_transforms,
+                                      const float* g_ndc, const float* g_clip_w, float* g_verts, void* stream);
+int32_t smplb_interpolate(const smplb_mesh* m, int32_t B, int32_t C, const float* attributes, const float* clip_w,
+                          const float* bary, const int32_t* ids, const float* background, int32_t W, int32_t H,
+                          float* images, void* stream);
+int32_t smplb_interpolate_backward(const smplb_mesh* m, int32_t B, int32_t C, const float* attributes, const float* clip_w,
+                                   const float* bary, const int32_t* ids, const float* background, int32_t W, int32_t H,
+                                   const float* g_images, float* g_attributes, float* g_clip_w, float* g_bary, void* stream);
 
 /* Phong shading of interpolated attribute images with the specular term, and its adjoint (SURVEY.md 8f N1:
  * deps/tf_mesh_renderer/mesh_renderer.py:23-162 phong_shader, and the part of mesh_renderer :375-400 between the

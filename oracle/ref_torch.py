@@ -251,3 +251,32 @@ def phong_shader(normals, alphas, pixel_positions, light_positions, light_intens
     a = alphas.reshape(B, H, W, 1)
     rgb = torch.where((a > 0.5).expand(-1, -1, -1, 3), rgb, torch.zeros_like(rgb))             # :160-161
     return torch.flip(torch.cat([rgb, a], dim=3), dims=[1])                                    # :162
+
+
+def clip_transform(vertices, projection_matrices):
+    """deps/tf_mesh_renderer/rasterize_triangles.py:73-86 on torch tensors: -> (ndc [B,V,3], guarded clip w [B,V])."""
+    B, V = vertices.shape[:2]
+    vh = torch.cat([vertices, torch.ones((B, V, 1), dtype=vertices.dtype, device=vertices.device)], 2)   # :73-76
+    clip = torch.matmul(vh, projection_matrices.transpose(1, 2))                                          # :77-79
+    w = clip[:, :, 3:4]
+    clip_w = torch.clamp(w.abs(), min=1e-6) * torch.sign(w)                                               # :81-84
+    return clip[:, :, 0:3] / clip_w, clip_w[:, :, 0]                                                      # :85-86
+
+
+def interpolate(attributes, clip_w, triangles, bary, ids, background_value):
+    """rasterize_triangles.py:119-164 on torch tensors: perspective-correct barycentrics, attribute interpolation, alpha
+    from the barycentric sum, background compositing.  triangles [T,3] long, bary [B,H,W,3], ids [B,H,W] long."""
+    B, V = attributes.shape[:2]
+    H, W = ids.shape[1:]
+    dev = attributes.device
+    vids = triangles[ids.reshape(B, -1)] + (torch.arange(B, device=dev) * V).view(B, 1, 1)               # :119-124
+    vids = vids.reshape(-1, 3)
+    b = bary.reshape(-1, 3)
+    corner_attr = attributes.reshape(B * V, -1)[vids]
+    corner_w = torch.reciprocal(clip_w.reshape(-1))[vids]                                                # :125-129
+    weighted = b * corner_w                                                                              # :133-135
+    factor = weighted.sum(1)
+    corrected = weighted / torch.clamp(factor, min=1e-6).unsqueeze(1)                                    # :139-144
+    images = (corner_attr * corrected.unsqueeze(2)).sum(1).reshape(B, H, W, -1)                          # :147-152
+    alphas = torch.clamp((2.0 * corrected).sum(1), 0.0, 1.0).reshape(B, H, W, 1)                         # :157-159
+    return alphas * images + (1.0 - alphas) * background_value                                           # :161-164
