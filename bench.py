@@ -705,10 +705,20 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
-        # NCCL prints its version banner (NCCL_DEBUG=VERSION and WARN both do) to stdout: send its log to stderr so that
-        # stdout stays the one JSON line
-        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
-        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+        # NCCL prints its version banner to stdout when the first communicator comes up (NCCL_DEBUG=VERSION and WARN both
+        # do): create the communicator here, with file descriptor 1 pointing at stderr meanwhile, so that stdout stays
+        # the one JSON line
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
 
     import smplb200
     from smplb200 import synthetic as syn, _lib
