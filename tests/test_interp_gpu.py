@@ -65,3 +65,36 @@ def test_interpolate_forward_and_adjoint():
     gb, gb64 = b32.grad.cpu().double(), bary64.grad
     assert maxrel(gb[~bgmask].numpy(), gb64[~bgmask].numpy()) <= 1e-4
     assert maxrel(gb[bgmask].numpy(), gb64[bgmask].numpy()) <= 1e-4
+
+
+def test_new_render_entry_points_reject_bad_arguments():
+    """Error behaviour of the round-2 renderer entry points through the raw C ABI: a status code and a message, never a
+    launch on bad arguments."""
+    import ctypes as C
+    from smplb200 import _lib, synthetic as syn
+    from smplb200.raster import Mesh
+    L = _lib.lib()
+    vv, tri = syn.uv_sphere_mesh(8, 6)
+    mesh = Mesh(tri, vv.shape[0], 0)
+    buf = torch.zeros(4096, device='cuda')
+    p = C.c_void_p(buf.data_ptr())
+    assert L.smplb_clip_transform(-1, 4, p, p, p, p, None) == _lib.E_BAD_SHAPE
+    assert L.smplb_clip_transform(1, 4, None, p, p, p, None) == _lib.E_INVALID_ARG
+    assert L.smplb_clip_transform(0, 4, None, None, None, None, None) == 0          # empty batch: nothing to do
+    assert L.smplb_clip_transform_backward(1, 4, p, p, None, None, p, None) == _lib.E_INVALID_ARG
+    assert L.smplb_interpolate(None, 1, 3, p, p, p, p, p, 4, 4, p, None) == _lib.E_INVALID_ARG
+    assert L.smplb_interpolate(mesh._h, 1, 0, p, p, p, p, p, 4, 4, p, None) == _lib.E_BAD_SHAPE
+    assert L.smplb_interpolate(mesh._h, 1, 3, p, p, None, p, p, 4, 4, p, None) == _lib.E_INVALID_ARG
+    assert L.smplb_interpolate_backward(mesh._h, 1, 3, p, p, p, p, p, 4, 4, p, p, None, p, None) == _lib.E_INVALID_ARG
+    io = _lib.PhongIO(1, 4, 4, 9, 9, 0, 3, 6, -1, -1, 0, p, None, None, p, p, None, None)          # 9 lights > 8
+    assert L.smplb_phong_shade(C.byref(io), p, p, 1 << 14, None) == _lib.E_BAD_SHAPE
+    io = _lib.PhongIO(1, 4, 4, 9, 1, 0, 3, 8, -1, -1, 0, p, None, None, p, p, None, None)          # diffuse offset outside C
+    assert L.smplb_phong_shade(C.byref(io), p, p, 1 << 14, None) == _lib.E_BAD_SHAPE
+    io = _lib.PhongIO(1, 4, 4, 12, 1, 0, 3, 6, 9, -1, 0, p, None, None, p, p, None, None)          # specular without camera
+    assert L.smplb_phong_shade(C.byref(io), p, p, 1 << 14, None) == _lib.E_INVALID_ARG
+    io = _lib.PhongIO(1, 4, 4, 9, 1, 0, 3, 6, -1, -1, 0, p, None, None, p, p, None, None)
+    assert L.smplb_phong_shade(C.byref(io), p, p, 8, None) == _lib.E_INVALID_ARG                   # scratch too small
+    assert b'scratch' in L.smplb_last_error()
+    need = L.smplb_phong_scratch_bytes(1, 4, 4, 1)
+    assert L.smplb_phong_shade(C.byref(io), p, p, need, None) == 0
+    torch.cuda.synchronize()
