@@ -14,7 +14,8 @@ namespace smplb {
 
 constexpr int PREP_WARPS = 8;          // samples per block: 8 x 16 bytes = one full line of the X operand image per k-chunk
 constexpr int PREP_XPITCH = KPAD + 4;  // X rows in shared memory (pitch 228: the 8 samples' float4 reads hit distinct banks)
-constexpr int PREP_STAGE = 2 * 4 * 12 * 8 / 2;   // floats per warp: the A operand image of one sample (1536 B) >= A (1152 B)
+constexpr int PREP_STAGE = 2 * 4 * 13 * 8 / 2;   // floats per warp: the A operand image of one sample (1536 B, each of its 8
+                                                 // (part, chunk) blocks padded by one 16-byte unit against bank conflicts) >= A (1152 B)
 static_assert(PREP_STAGE >= NJ * 12, "staging buffer holds the largest per-joint output");
 static_assert(BL_BM % PREP_WARPS == 0 && KPAD % 8 == 0, "a block's samples share one X tile");
 
@@ -26,8 +27,14 @@ template <int N>
 __device__ __forceinline__ void store_staged(float* stage, float* dst, const float (&v)[N], int lane, bool act) {
   __syncwarp();
   if (act) {
+    if (N % 4 == 0) {   // 16-byte stores: a 48-byte lane stride is conflict-free per quarter warp, 4-byte stores are 4-way
 #pragma unroll
-    for (int e = 0; e < N; ++e) stage[lane * N + e] = v[e];
+      for (int e = 0; e < N / 4; ++e)
+        reinterpret_cast<float4*>(stage + lane * N)[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < N; ++e) stage[lane * N + e] = v[e];
+    }
   }
   __syncwarp();
   constexpr int NQ = NJ * N / 4;   // 16-byte units of the block
@@ -184,8 +191,8 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       for (int c = 0; c < 4; ++c) {
         const float val = lane < NJ ? row[c] : 0.f;
         const unsigned short h = f16_rne_bits(val);
-        st16[(((lane >> 3)) * 12 + r * 4 + c) * 8 + (lane & 7)] = h;
-        st16[((4 + (lane >> 3)) * 12 + r * 4 + c) * 8 + (lane & 7)] = f16_rne_bits(val - f16_bits_to_float(h));
+        st16[(((lane >> 3)) * 13 + r * 4 + c) * 8 + (lane & 7)] = h;
+        st16[((4 + (lane >> 3)) * 13 + r * 4 + c) * 8 + (lane & 7)] = f16_rne_bits(val - f16_bits_to_float(h));
       }
     }
     __syncwarp();
@@ -193,7 +200,8 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       const int u = lane + 32 * i, part = u / 48, chunk = (u % 48) / 12, e = u % 12;
-      *reinterpret_cast<uint4*>(a16 + aimg16_off(b, chunk * 8, e, part)) = reinterpret_cast<const uint4*>(st16)[u];
+      *reinterpret_cast<uint4*>(a16 + aimg16_off(b, chunk * 8, e, part)) =
+          reinterpret_cast<const uint4*>(st16)[(part * 4 + chunk) * 13 + e];
     }
   }
   float uvv[2] = {0.f, 0.f}, pxv[2] = {0.f, 0.f};
