@@ -1,7 +1,7 @@
 // K2 blend-shape GEMM on the 5th-generation tensor cores (batch_smpl.py:91-95, :113-115):
 //     v_posed[B, 20670] = [beta | pose_feature][B, 217] . [shapedirs; posedirs][217, 20670] + v_template
 // fp32-faithful on the tensor cores from 16-bit operands (operand images and error analysis: common.cuh):
-//     acc += f16(X).f16(D) + f16(X - f16(X)).f16(D) + bf16(X).bf16(D - f16(D))
+//     acc += f16(X).f16(D') + f16(X - f16(X)).f16(D') + f16(X).f16(D' - f16(D')),   D' = 2^e D (the epilogue multiplies by 2^-e)
 // three kind::f16 MMAs (K = 16) per 16-element k-block, fp32 accumulation in TMEM.  History of this kernel at
 // B = 65536: 3xTF32, 6 MMA slots and 8 B per element: 2.50 ms (tensor pipe 83 % busy);  TF32 main product + two
 // bf16 corrections, 4 slots, 8 B: 2.41 ms, bound by the EPILOGUE (an L2 round trip for v_template in every
@@ -11,7 +11,10 @@
 // fp16 main product (same 11 significant bits as TF32): 3 slots, 6 B per element, 8 x 24 KB stages: 1.67 ms;
 // the ring depth, not the L2 bandwidth, is what that version waited on (ring bytes / consumption rate = 3000
 // cycles of cover; the X-stationary variants traded ring for stream one for one), so the second product now
-// reuses the f16(D) part (f16(Xl) instead of bf16(Xl).bf16(f16 D)): D slabs 12 -> 8 KB, 10 x 20 KB stages.
+// reuses the f16(D) part (f16(Xl) instead of bf16(Xl).bf16(f16 D)): D slabs 12 -> 8 KB, 10 x 20 KB stages: 1.55 ms, tensor pipe
+// 71 % active, the pair asking L2 for 53 B/clk/SM at the full tensor rate against the ~43 it delivers;  D stored scaled by a
+// power of two so that its residual is a normal fp16 number too: the bf16(X) part goes, X slabs 12 -> 8 KB (41 B/clk/SM),
+// 12 x 16 KB stages.
 //
 // v2 organisation: CTA PAIRS (cluster of 2 = one TPC, tcgen05 cta_group::2), persistent over 256 x 256
 // output tiles.  v1 (one CTA per 128 x 256 tile, 2 x 96 KB stages) pulled 688 KB of operands from L2 per
@@ -35,8 +38,8 @@ namespace smplb {
 
 using namespace tc;
 
-constexpr int TC_STAGES = 10;
-constexpr int TC_X_STAGE_FLOATS = BL_SLAB;   // one X slab: 3 parts x 4 KB
+constexpr int TC_STAGES = 12;
+constexpr int TC_X_STAGE_FLOATS = BL_SLAB;   // one X slab: 2 parts x 4 KB
 constexpr int TC_D_STAGE_FLOATS = BL_DSLAB;  // one D half slab: 2 parts x 4 KB
 constexpr uint32_t TC_STAGE_BYTES = (TC_X_STAGE_FLOATS + TC_D_STAGE_FLOATS) * 4;
 constexpr int TC_THREADS = 192;
@@ -57,7 +60,7 @@ struct TcSmem {
 
 // One 32-row x 32-column block of the accumulator: registers (thread = row) -> smem -> coalesced stores.
 __device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* stage, int lane, const float4 tv,
-                                               float* obase, int rows_valid) {
+                                               float* obase, int rows_valid, float sc) {
 #pragma unroll
   for (int j = 0; j < 8; ++j)
     *reinterpret_cast<float4*>(stage + lane * TC_EP_PITCH + j * 4) =
@@ -69,10 +72,10 @@ __device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* s
   for (int it = 0; it < 8; ++it) {
     const int row = it * 4 + rsub;
     float4 v = *reinterpret_cast<const float4*>(stage + row * TC_EP_PITCH + c4);
-    v.x += tv.x;
-    v.y += tv.y;
-    v.z += tv.z;
-    v.w += tv.w;
+    v.x = fmaf(v.x, sc, tv.x);   // sc = 2^-e undoes the scale of the D image (exact), + v_template
+    v.y = fmaf(v.y, sc, tv.y);
+    v.z = fmaf(v.z, sc, tv.z);
+    v.w = fmaf(v.w, sc, tv.w);
     if (row < rows_valid) __stcs(reinterpret_cast<float4*>(obase + (size_t)row * VPP + c4), v);
   }
   __syncwarp();
@@ -80,7 +83,7 @@ __device__ __forceinline__ void tc_store_block(const uint32_t (&r)[32], float* s
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
 blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float* __restrict__ Dimg,
-                const float* __restrict__ vt, float* __restrict__ vposed) {
+                const float* __restrict__ vt, float* __restrict__ vposed, float d_scale_inv) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   TcSmem& sm = *reinterpret_cast<TcSmem*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -143,7 +146,6 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
     } else {
       // ================= MMA issuer (leader CTA) =================
       constexpr uint32_t idesc_h = umma_idesc(0, 2 * BL_BM, BL_BN);   // kind::f16, f16 operands
-      constexpr uint32_t idesc_b = umma_idesc(1, 2 * BL_BM, BL_BN);   // kind::f16, bf16 operands
       constexpr uint32_t LBO = BL_BM * 16, SBO = 128;                 // bytes; X and D halves are both 128 rows
       constexpr uint32_t PART = BL_PART16 * 2 / 16;                   // one 4 KB part in descriptor units
       static_assert(BL_BM == BL_BH, "one descriptor template for both operands");
@@ -165,7 +167,7 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
           const uint64_t dd = dtempl + (uint64_t)(db0 + s * (TC_D_STAGE_FLOATS * 4 / 16));
           umma_f16_ss_pair(dcol, xd, dd, idesc_h, kb != 0, issue);                                  // f16(X).f16(D)
           umma_f16_ss_pair(dcol, xd + (uint64_t)PART, dd, idesc_h, 1, issue);                       // f16(Xl).f16(D)
-          umma_f16_ss_pair(dcol, xd + (uint64_t)(2 * PART), dd + (uint64_t)PART, idesc_b, 1, issue);   // bf16(X).bf16(Dl)
+          umma_f16_ss_pair(dcol, xd, dd + (uint64_t)PART, idesc_h, 1, issue);                       // f16(X).f16(Dl)
           umma_commit_pair(empty0 + s * 8, 3, issue);                                        // stage free in both CTAs
           if (kb == BL_NKB - 1) umma_commit_pair(smem_u32(&sm.acc_full[a]), 3, issue);       // accumulator complete
           if (++s == TC_STAGES) { s = 0; ph ^= 1; }
@@ -200,7 +202,7 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
       for (int c0 = 0; c0 < BL_BN; c0 += 64) {
         tmem_ld_wait();
         tmem_ld32(tbase + c0 + 32, rb);
-        tc_store_block(ra, stage, lane, tv[c0 / 32], obase + c0, rows_valid);
+        tc_store_block(ra, stage, lane, tv[c0 / 32], obase + c0, rows_valid, d_scale_inv);
         tmem_ld_wait();
         if (c0 + 64 < BL_BN) {
           tmem_ld32(tbase + c0 + 64, ra);
@@ -210,7 +212,7 @@ blend_tc_kernel(int B, int n_mtiles, const float* __restrict__ Ximg, const float
           __syncwarp();
           if (lane == 0) mbar_arrive_remote(&sm.acc_empty[a], 0);
         }
-        tc_store_block(rb, stage, lane, tv[c0 / 32 + 1], obase + c0 + 32, rows_valid);
+        tc_store_block(rb, stage, lane, tv[c0 / 32 + 1], obase + c0 + 32, rows_valid, d_scale_inv);
       }
     }
   }
@@ -233,7 +235,7 @@ int32_t launch_blend_tc(const smplb_model* m, int B, const float* Ximg, float* v
   const int n_tiles = ((n_mtiles + 1) / 2) * BL_NT;
   const int n_cl = n_tiles < n_sm / 2 ? n_tiles : n_sm / 2;
   const int grid = 2 * n_cl;   // CTA pairs
-  blend_tc_kernel<<<grid, TC_THREADS, smem, st>>>(B, n_mtiles, Ximg, m->Dimg, m->v_template_pad, vposed);
+  blend_tc_kernel<<<grid, TC_THREADS, smem, st>>>(B, n_mtiles, Ximg, m->Dimg, m->v_template_pad, vposed, m->d_scale_inv);
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

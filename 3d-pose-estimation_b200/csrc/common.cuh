@@ -31,8 +31,8 @@
 #define BL_KB 16                // K elements per pipeline stage (k-block) = 4 chunks of 4
 #define BL_NKB (KPAD / BL_KB)   // 14 k-blocks
 #define BL_NT (VPP / BL_BN)     // 81 N tiles
-#define BL_SLAB (3 * BL_KB * BL_BM / 2)   // floats per (k-block, 128 rows) operand slab: 3 sixteen-bit parts = 12 KB
-#define BL_XTILE (BL_NKB * BL_SLAB)       // floats per X m-tile image (43008)
+#define BL_SLAB (2 * BL_KB * BL_BM / 2)   // floats per (k-block, 128 rows) operand slab: 2 sixteen-bit parts = 8 KB
+#define BL_XTILE (BL_NKB * BL_SLAB)       // floats per X m-tile image (28672)
 #define BL_DSLAB (2 * BL_KB * BL_BH / 2)  // floats per (k-block, 128 columns) D slab: 2 sixteen-bit parts = 8 KB
 #define BL_DTILE (BL_NKB * 2 * BL_DSLAB)  // floats per D n-tile image (57344): [k-block][column half] slabs
 
@@ -116,7 +116,8 @@ struct smplb_model {
   float* v_template_pad;  // [VPP]   v_template flattened (3v+c), zero padded
   // blend-shape basis D = [shapedirs; posedirs] : K=217 rows, padded to KPAD x VPP
   float* D32;             // [KPAD][VPP] fp32 (SIMT verification path, backward)
-  float* Dimg;            // [BL_NT][BL_DTILE] f16/bf16 operand image of D (tcgen05 B operand, dimg16_off)
+  float* Dimg;            // [BL_NT][BL_DTILE] fp16 split operand image of 2^e D (tcgen05 B operand, dimg16_off)
+  float d_scale_inv;      // 2^-e: the blend GEMM's epilogue multiplies the accumulator by it (exact)
   // folded joint regression: J = Jbar + JS * beta  (batch_smpl.py:91-101)
   float* Jbar;            // [24*3]
   float* JS;              // [24*3*10]
@@ -177,7 +178,7 @@ struct PrepParams {
   const float* Jbar;
   const float* JS;
   const float* JSt;   // smplb_model::JSt
-  float* Ximg;    // [ceil(B/128)][BL_XTILE] f16/bf16 operand image of [beta | pose feature] (ximg16_off), nullable
+  float* Ximg;    // [ceil(B/128)][BL_XTILE] fp16 split operand image of [beta | pose feature] (ximg16_off), nullable
   float* joints;  // [B][24][3] nullable
   float* Rs;      // [B][24][9] nullable
   float* A;       // [B][24][12] nullable
@@ -277,17 +278,20 @@ __host__ __device__ inline size_t dtimg16_off(int k, int n, int part) {
          (size_t)(((n % BB_KB) / 8) * (BB_NH / 8) + r / 8) * 64 + (size_t)((r & 7) * 8 + (n & 7));
 }
 
-// Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated fp32-faithfully from 16-bit operands:
-//     X.D ~= f16(X).f16(D)  +  f16(Xl).f16(D)  +  bf16(X).bf16(Dl),    Xl = X - f16(X), Dl = D - f16(D)
-// (kind::f16 MMAs, K = 16 each, fp32 accumulation).  fp16 carries the same 11 significant bits as TF32 at twice
-// the tensor rate and half the bytes; the two correction products are 2^-11 of the main one.  Xl (inputs are O(1))
-// stays an fp16 number: normal for |X| >= 0.12, below that its absolute error is <= 2^-25, which is what matters
-// against the vertex scale; so the second product reuses the f16(D) part.  Dl (~5e-6 for SMPL's bases) is below the
-// fp16 normal range and is carried in bf16 (8 bits, fp32 exponent range), with bf16(X) as its partner.
-// Error ~2^-20 of the blend offsets (tests/test_blend_split.py).  3 MMA slots, 6 B per X element and 4 B per D element
-// against 6 slots and 8 B for 3xTF32 (Xh.Dh + Xl.Dh + Xh.Dl, the first version of this round).
+// Operand images of the blend GEMM (blend_tc.cu).  The product is evaluated fp32-faithfully from fp16 operands:
+//     X.D ~= 2^-e [ f16(X).f16(D')  +  f16(Xl).f16(D')  +  f16(X).f16(Dl') ],   D' = 2^e D, Xl = X - f16(X), Dl' = D' - f16(D')
+// (kind::f16 MMAs, K = 16 each, fp32 accumulation).  fp16 carries the same 11 significant bits as TF32 at twice the
+// tensor rate and half the bytes; the two correction products are 2^-11 of the main one.  Xl (inputs are O(1)) stays an
+// fp16 number: normal for |X| >= 0.12, below that its absolute error is <= 2^-25, which is what matters against the vertex
+// scale.  The residual of SMPL's bases (~5e-6) would sit below the fp16 normal range, so the model is stored scaled by the
+// power of two that puts max|D| just under 2^15 (smplb_model::d_scale_inv = 2^-e, applied exactly in the epilogue): both
+// parts of D' are then normal fp16 numbers down to entries 2^-17 of the largest one, and all three products read the
+// same two X parts -- the kernel is bound by the operand stream from L2 (~43 B/clk/SM delivered), and the bf16(X) part
+// the first version of this round needed for a bf16(Dl) partner was a third of the X bytes.
+// Error ~2^-21 of the blend offsets (tests/test_blend_split.py).  3 MMA slots, 4 B per X element and 4 B per D element
+// against 6 slots and 8 B for 3xTF32 (Xh.Dh + Xl.Dh + Xh.Dl).
 // Per 16-element k-block a 128-row slab is made of 4 KB parts, each 2 K-chunks x 128 rows x 16 B:
-//     X (12 KB): f16(X) | f16(Xl) | bf16(X)          D (8 KB): f16(D) | bf16(Dl)
+//     X (8 KB): f16(X) | f16(Xl)          D (8 KB): f16(D') | f16(Dl')
 #define BL_PART16 (BL_KB * BL_BM)   // 16-bit elements per part (2048)
 // 16-bit-element offset of part `part` of element (row b, k) of the X operand image
 __host__ __device__ inline size_t ximg16_off(int b, int k, int part) {

@@ -176,15 +176,26 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
       for (int k = 0; k < NB; ++k) D32[(size_t)k * VPP + col] = shapedirs[(size_t)k * NV3 + 3 * v + c];
       for (int k = 0; k < NP; ++k) D32[(size_t)(NB + k) * VPP + col] = posedirs[(size_t)k * NV3 + 3 * v + c];
     }
+  // D is stored scaled by 2^e, the power of two that puts max|D| in [2^14, 2^15): both fp16 parts of every entry down to
+  // 2^-17 of the largest are then normal numbers (common.cuh); the epilogue of the GEMM multiplies by 2^-e
+  float dmax = 0.f;
+  for (size_t i = 0; i < D32.size(); ++i) dmax = std::max(dmax, std::fabs(D32[i]));
+  int e2 = 0;
+  if (dmax > 0.f) {
+    int ex;
+    std::frexp(dmax, &ex);      // dmax = f * 2^ex, f in [0.5, 1)
+    e2 = 15 - ex;               // 2^e2 * dmax in [2^14, 2^15)
+  }
+  const float d_scale = std::ldexp(1.0f, e2), d_scale_inv = std::ldexp(1.0f, -e2);
   std::vector<float> Dimg((size_t)BL_NT * BL_DTILE, 0.f);
   unsigned short* d16 = reinterpret_cast<unsigned short*>(Dimg.data());
   for (int k = 0; k < KDIM; ++k)
     for (int n = 0; n < VPP; ++n) {
-      const float x = D32[(size_t)k * VPP + n];
+      const float x = D32[(size_t)k * VPP + n] * d_scale;   // exact
       const unsigned short h = f16_rne_bits(x);
       const float hi = f16_bits_to_float(h);
       d16[dimg16_off(n, k, 0)] = h;
-      d16[dimg16_off(n, k, 1)] = bf16_rne_bits(x - hi);
+      d16[dimg16_off(n, k, 1)] = f16_rne_bits(x - hi);
     }
   std::vector<float> vt(VPP, 0.f);
   for (int v = 0; v < NV; ++v)
@@ -305,6 +316,7 @@ extern "C" int32_t smplb_model_create(smplb_model** out, int32_t device, const f
   m->device = device;
   m->NK = NK;
   m->tree = tree;
+  m->d_scale_inv = d_scale_inv;
   m->kp_nnz = (int)kvtx.size();
   m->has_compressed = has_compressed;
   cudaError_t e = cudaSuccess;

@@ -1,6 +1,6 @@
 // K1 pose_prep: one warp per sample, lane = joint.
 //   Rodrigues x24 (batch_lbs.py:38-57)  ->  207-d pose feature (batch_smpl.py:107-110) written as the
-//   f16 / f16-residual / bf16 split A-operand image of the blend GEMM (ximg16_off), beta in columns 0..9;
+//   f16 / f16-residual split A-operand image of the blend GEMM (ximg16_off), beta in columns 0..9;
 //   folded joint regression J = Jbar + JS beta (batch_smpl.py:91-101);
 //   kinematic chain by pointer jumping with warp shuffles (batch_lbs.py:84-144);
 //   J_transformed, relative skinning transforms A[B,24,3,4];
@@ -99,19 +99,17 @@ __global__ void __launch_bounds__(PREP_WARPS * 32) pose_prep_kernel(const PrepPa
       const float4 v0 = *reinterpret_cast<const float4*>(&xrow[s8][q * 8]);
       const float4 v1 = *reinterpret_cast<const float4*>(&xrow[s8][q * 8 + 4]);
       const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-      uint32_t h[4], l[4], bf[4];
+      uint32_t h[4], l[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const unsigned short ha = f16_rne_bits(v[2 * i]), hb = f16_rne_bits(v[2 * i + 1]);
         h[i] = (uint32_t)ha | ((uint32_t)hb << 16);
         l[i] = (uint32_t)f16_rne_bits(v[2 * i] - f16_bits_to_float(ha)) |
                ((uint32_t)f16_rne_bits(v[2 * i + 1] - f16_bits_to_float(hb)) << 16);
-        bf[i] = (uint32_t)bf16_rne_bits(v[2 * i]) | ((uint32_t)bf16_rne_bits(v[2 * i + 1]) << 16);
       }
       unsigned short* x16 = reinterpret_cast<unsigned short*>(p.Ximg);
       *reinterpret_cast<uint4*>(x16 + ximg16_off(b0 + s8, q * 8, 0)) = make_uint4(h[0], h[1], h[2], h[3]);
       *reinterpret_cast<uint4*>(x16 + ximg16_off(b0 + s8, q * 8, 1)) = make_uint4(l[0], l[1], l[2], l[3]);
-      *reinterpret_cast<uint4*>(x16 + ximg16_off(b0 + s8, q * 8, 2)) = make_uint4(bf[0], bf[1], bf[2], bf[3]);
     }
   }
   if (p.Ximg2 && valid) {

@@ -864,7 +864,7 @@ def run_forward(args, rank, local_rank, world, dist):
         cfg = workload_config(args, world)
         cfg.update({
             'samples_per_gpu': B, 'global_batch': B_global, 'cuda_graph': graph is not None,
-            'blend_gemm': 'tcgen05 kind::f16: f16 main product + f16/bf16 residual products, fp32 accumulate (fp32-faithful, 2e-7 of the vertex scale; |beta| and model constants <= 65504)' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
+            'blend_gemm': 'tcgen05 kind::f16: f16 main product + two f16 residual products on a power-of-two scaled basis, fp32 accumulate (fp32-faithful, 2e-7 of the vertex scale; |beta| and model constants <= 65504)' if args.blend == 'tc' else 'fp32 SIMT (verification path)',
             'sharding': 'contiguous batch shards, one rank per GPU, no forward collective',
             'l2': 'working set %.2f GB per GPU per step exceeds the 126 MB L2 (no flush needed)' % (
                 B * (82944 + 82680) / 1e9),

@@ -126,7 +126,7 @@ int32_t smplb_model_nk(const smplb_model* m);
 size_t smplb_workspace_bytes(const smplb_model* m, int32_t B, int32_t flags);
 
 /* SMPL.__call__ (+ optional projection).  Kernels: pose_prep -> blend GEMM -> skinning.
- * The two GEMMs run on tcgen05 from 16-bit split operands (fp16 main part + fp16 / bf16 residuals, fp32 accumulation,
+ * The two GEMMs run on tcgen05 from 16-bit split operands (fp16 main part + fp16 residuals in the forward, bf16 pairs in the backward, fp32 accumulation,
  * fp32-faithful: ~2e-7 of the vertex scale): |beta| and the model constants must stay inside the fp16 range
  * (<= 65504; smplb_model_create rejects a model outside it with SMPLB_E_UNSUPPORTED). */
 int32_t smplb_forward(const smplb_model* m, const smplb_forward_io* io, void* workspace,

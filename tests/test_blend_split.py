@@ -1,5 +1,6 @@
 """Host-side check of the operand split the blend GEMM uses (csrc/blend_tc.cu, common.cuh):
-    X.D ~= f16(X).f16(D) + f16(X - f16(X)).f16(D) + bf16(X).bf16(D - f16(D))
+    X.D ~= 2^-e [ f16(X).f16(D') + f16(X - f16(X)).f16(D') + f16(X).f16(D' - f16(D')) ],  D' = 2^e D with max|D'| in [2^14, 2^15)
+(and the first version of this round, f16 main product + bf16 corrections on the unscaled D, for comparison)
 emulated in NumPy with the same rounding rules (fp16 and bf16 round to nearest even, fp16 subnormals included;
 the TF32 helpers model cvt.rna.tf32 for the 1x / 3xTF32 comparison rows) against float64, on operands shaped like [beta | R - I] x [shapedirs; posedirs]
 (batch_smpl.py:91-95, :107-115).  The bound asserted here is what DESIGN.md quotes."""
@@ -32,8 +33,19 @@ def test_split_error_bounds():
     Xf, Df = X.astype(np.float16).astype(np.float32), D.astype(np.float16).astype(np.float32)
     mixed = (f(Xf) @ f(Df) + f((X - Xf).astype(np.float16).astype(np.float32)) @ f(Df) +
              f(bf16_rne(X)) @ f(bf16_rne(D - Df)))
+    # the kernel's scheme: D scaled by a power of two so that both of its fp16 parts are normal numbers
+    e2 = 15 - int(np.frexp(np.abs(D).max())[1])
+    Dp = D * np.float32(2.0 ** e2)
+    assert 2.0 ** 14 <= np.abs(Dp).max() < 2.0 ** 15
+    Dph = Dp.astype(np.float16).astype(np.float32)
+    Dpl = (Dp - Dph).astype(np.float16).astype(np.float32)
+    Xl16 = (X - Xf).astype(np.float16).astype(np.float32)
+    scaled = (f(Xf) @ f(Dph) + f(Xl16) @ f(Dph) + f(Xf) @ f(Dpl)) * 2.0 ** -e2
     scale = np.abs(exact).max()
+    es = np.abs(scaled - exact).max() / scale
+    assert es < 2e-6            # all-fp16 split with the scaled basis (what blend_tc.cu computes)
     e1, e3, em = (np.abs(r - exact).max() / scale for r in (one, three, mixed))
+    assert es <= em * 1.05      # at least as good as the bf16-correction version it replaced
     assert e1 > 1e-4            # a single TF32 product is not enough (SURVEY.md header table)
     assert e3 < 5e-7            # 3xTF32
     assert em < 4e-6            # f16 main product + two bf16 corrections: relative to the OFFSET scale ...
