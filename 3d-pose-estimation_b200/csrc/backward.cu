@@ -323,6 +323,8 @@ __global__ void __launch_bounds__(JB_WARPS * 32, 7) joint_bwd_kernel(const Joint
   __shared__ double sq_sum[JB_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * JB_WARPS + warp;
+  pdl_wait();      // fitting step: the previous step's loss_finish_kernel (step counter, partials) has completed
+  pdl_trigger();   // ... and this step's loss_finish_kernel may be scheduled now (it waits for this grid itself)
   if (p.gt_px) {
     // fused fitting step: every warp of the block takes part in the loss partial sum (no early exit)
     if (lane == 0) sq_sum[warp] = 0.0;
@@ -451,7 +453,7 @@ int32_t launch_fit_fused(const smplb_model* m, int B, const float* beta, const f
   p.px_out = px;
   p.g_px_out = g_px;
   p.partial = partial;
-  joint_bwd_kernel<<<fit_fused_blocks(B), JB_WARPS * 32, 0, st>>>(p);
+  SMPLB_CUDA_CHECK(launch_pdl(joint_bwd_kernel, dim3(fit_fused_blocks(B)), dim3(JB_WARPS * 32), 0, st, p));
   SMPLB_CUDA_CHECK(cudaGetLastError());
   return SMPLB_OK;
 }

@@ -77,6 +77,27 @@ struct KernelSetup {
   }
 };
 
+// Programmatic dependent launch (PDL): a kernel launched with launch_pdl() may be scheduled while its predecessor on the
+// stream is still running; it must call pdl_wait() before it touches anything the predecessor wrote (or overwrites
+// anything the predecessor reads) and may call pdl_trigger() to let ITS successor be scheduled early.  Both are no-ops
+// for a kernel launched the ordinary way.  Used where a chain of short kernels is bound by launch gaps (the fitting step).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at;
+  at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // Kinematic tree, passed by value to the kernels (batch_smpl.py:54, batch_lbs.py:122-127).
 struct Tree {
   int parent[NJ];

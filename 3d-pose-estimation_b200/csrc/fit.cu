@@ -56,6 +56,8 @@ __global__ void __launch_bounds__(256) loss_finish_kernel(int nblocks, const dou
                                                           int* __restrict__ step_dev, int step_host, float lr, float b1,
                                                           float b2) {
   __shared__ double red[8];
+  pdl_trigger();   // the next step's per-sample kernel may be scheduled (it waits for this grid before it reads anything)
+  pdl_wait();      // the per-sample kernel of this step has completed: its partials are visible
   double acc = 0.0;
   for (int i = threadIdx.x; i < nblocks; i += 256) acc += partial[i];
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -163,9 +165,9 @@ extern "C" int32_t smplb_fit_step(const smplb_model* m, const smplb_fit_io* io, 
                                 io->cam_pos, io->cam_rot, io->focal, io->cfg.cam, io->px, io->g_px, partial, io->g_beta,
                                 io->g_theta, adam_inside ? &ad : nullptr, st);
   if (rc != SMPLB_OK) return rc;
-  loss_finish_kernel<<<1, 256, 0, st>>>(nblocks, partial, io->cfg.reproj_scale, inv_n, io->cfg.reproj_cap, io->loss,
-                                        io->step_dev, io->step, io->lr, io->beta1, io->beta2);
-  SMPLB_CUDA_CHECK(cudaGetLastError());
+  SMPLB_CUDA_CHECK(launch_pdl(loss_finish_kernel, dim3(1), dim3(256), 0, st, nblocks, (const double*)partial,
+                              io->cfg.reproj_scale, inv_n, io->cfg.reproj_cap, io->loss, io->step_dev, io->step, io->lr,
+                              io->beta1, io->beta2));
   if (!adam_inside) {
     const int64_t nt = (int64_t)B * NJ * 3;
     adam_gated_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(nt, io->theta, io->g_theta, io->m_theta, io->v_theta,
