@@ -39,6 +39,9 @@ struct TimingState {
   std::vector<cudaEvent_t> ev;   // 5 events per call: 4 intervals
   int max_calls = 0;
   int ncalls = 0;
+  ~TimingState() {
+    for (cudaEvent_t e : ev) cudaEventDestroy(e);   // thread exit
+  }
 };
 static thread_local TimingState g_timing;       // forward: prep | blend | skin | keypoints
 static thread_local TimingState g_timing_bwd;   // backward (vertex path): g_A reduction | g_vposed | transposed GEMM | joint path
@@ -239,8 +242,24 @@ extern "C" int32_t smplb_forward_host(const smplb_model* m, const smplb_forward_
   io.cfg = h->cfg;
   // Chunked pipeline: the kernels of chunk k+1 run on `st` while a second stream drains the outputs of chunk k
   // over PCIe (the D2H of verts is ~20x the kernel time, so everything but the first chunk's kernels is hidden).
-  static thread_local cudaStream_t cs[64] = {};
-  static thread_local cudaEvent_t ev[64] = {}, ev_done[64] = {};
+  // per host thread and device: created on first use, destroyed when the thread exits (calls that arrive after the CUDA
+  // runtime has shut down return an error, which is ignored there)
+  struct HostPipe {
+    cudaStream_t cs[64] = {};
+    cudaEvent_t ev[64] = {}, ev_done[64] = {};
+    ~HostPipe() {
+      for (int i = 0; i < 64; ++i)
+        if (cs[i]) {
+          cudaStreamDestroy(cs[i]);
+          cudaEventDestroy(ev[i]);
+          cudaEventDestroy(ev_done[i]);
+        }
+    }
+  };
+  static thread_local HostPipe pipe;
+  cudaStream_t(&cs)[64] = pipe.cs;
+  cudaEvent_t(&ev)[64] = pipe.ev;
+  cudaEvent_t(&ev_done)[64] = pipe.ev_done;
   const int dv = m ? (m->device & 63) : 0;
   if (!cs[dv]) {
     SMPLB_CUDA_CHECK(cudaStreamCreateWithFlags(&cs[dv], cudaStreamNonBlocking));
